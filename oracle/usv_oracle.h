@@ -1,0 +1,112 @@
+/*
+ * usv_oracle.h -- CPU restatement (plain C, float64) of the gym-usv env step.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Only tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs may load this library.  The product path
+ * (gym_usv_b200/) never links, imports or calls it.
+ *
+ * Pinned against the reference's own code executed in-process (oracle/gen_golden.py
+ * -> tests/golden/ (npz files), tests/test_oracle_golden.py) and against the three
+ * behavioural tests of reference tests/test_usv_asmc.py:8-37.
+ *
+ * Every function cites the reference file:line it restates (paths relative to the
+ * reference root).
+ */
+#ifndef USV_ORACLE_H
+#define USV_ORACLE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define USV_ORACLE_MAX_OBS 32
+#define USV_ORACLE_SENSORS 128
+#define USV_ORACLE_OBS_DIM 143
+
+/* gym_usv/control/usv_asmc.py:43-49 -- controller + integrator memory, plus the pose and
+ * body velocity the env hands in and gets back (usv_asmc.py:53,244). */
+typedef struct UsvOracleAsmc {
+    double eta[3];          /* x, y, psi                                   */
+    double nu[3];           /* u, v, r                                     */
+    double last[9];         /* x_dot,y_dot,psi_dot,u_dot,v_dot,r_dot,e_u,ka_dot_u,ka_dot_psi (last) */
+    double so[4];           /* psi_d_last, o_dot_dot_last, o_dot_last, o_last (usv_asmc.py:58,90-92) */
+    double aux[3];          /* e_u_int, ka_u, ka_psi                       */
+    int64_t perturb_step;   /* usv_asmc.py:49,199                          */
+} UsvOracleAsmc;
+
+/* gym_usv/envs/simple_env.py:10-60 + simple_env_asmc.py:10-16 + TimeLimit(1000). */
+typedef struct UsvOracleEnv {
+    UsvOracleAsmc asmc;
+    double path_start[2];
+    double path_end[2];
+    double target[2];
+    double max_action[3];
+    double max_accel[3];
+    double v_ref;
+    double progress;
+    double last_action[3];
+    double obs_x[USV_ORACLE_MAX_OBS];
+    double obs_y[USV_ORACLE_MAX_OBS];
+    double obs_r[USV_ORACLE_MAX_OBS];
+    double sensor[USV_ORACLE_SENSORS];   /* sensor_data[:,1], simple_env.py:47,329 */
+    double ep_return;
+    int32_t n_obs;
+    int32_t steps;                        /* TimeLimit elapsed steps */
+    int32_t episode;                      /* resets so far - 1       */
+    int32_t pad_;
+} UsvOracleEnv;
+
+typedef struct UsvOracleConfig {
+    int32_t ignore_obstacles;     /* simple_env.py:49                         */
+    int32_t do_perturb;           /* usv_asmc.py:53 (env passes False)        */
+    int32_t skip_kinematic;       /* NOT reference behaviour (opt-in)         */
+    int32_t max_episode_steps;    /* gym_usv/__init__.py:33 ; 0 = none        */
+    int32_t auto_reset;           /* SB3 VecEnv semantics                     */
+    int32_t obstacles_f32;        /* round reset obstacle tables to float32   */
+    int32_t n_threads;            /* OpenMP threads for the vec entry points  */
+    int32_t pad_;
+} UsvOracleConfig;
+
+int  usv_oracle_sizeof_env(void);
+int  usv_oracle_sizeof_asmc(void);
+
+/* usv_asmc.py:5-49 */
+void usv_oracle_asmc_init(UsvOracleAsmc* s);
+/* usv_asmc.py:53-244; info = psi_d,u_d,tport,tstbd of the LAST of the 10 sub-steps */
+void usv_oracle_asmc_compute(UsvOracleAsmc* s, const double action[2], int do_perturb, double info[4]);
+void usv_oracle_asmc_compute_batch(UsvOracleAsmc* s, int64_t n, const double* actions /*n x 2*/,
+                                   int do_perturb, int n_calls, int n_threads);
+
+/* usv_asmc_ca_env.py:411-461,500-519 (static compute_sensor_measurments and helpers) */
+void usv_oracle_sensors(const double position[3], int sensor_count, double sensor_max_range,
+                        const double* radius, double pitch, const double* posx, const double* posy,
+                        int num_obs, const double* distance, double* out_dist);
+
+/* simple_env.py:228-308 via simple_env_asmc.py:14-16, PCG64 replaced by Philox4x32-10
+ * (key = seed, counter = (global env id, episode, block)); writes obs[0..14], leaves the
+ * sensor part of the caller's obs row stale like simple_env.py:302 does. */
+void usv_oracle_simple_reset(UsvOracleEnv* e, const UsvOracleConfig* cfg, uint64_t seed,
+                             uint64_t global_id, float* obs);
+/* first construction: simple_env.py:32-54 defaults */
+void usv_oracle_simple_init(UsvOracleEnv* e);
+
+/* simple_env_asmc.py:18-27 -> simple_env.py:310-346 (+ TimeLimit) */
+void usv_oracle_simple_step(UsvOracleEnv* e, const UsvOracleConfig* cfg, const float action[2],
+                            float* obs, double* reward, uint8_t* terminated, uint8_t* truncated);
+
+/* N envs, SB3 VecEnv auto-reset semantics; terminal_obs may be NULL */
+void usv_oracle_vec_reset(UsvOracleEnv* envs, int64_t n, const UsvOracleConfig* cfg, uint64_t seed,
+                          int64_t global_offset, float* obs);
+void usv_oracle_vec_step(UsvOracleEnv* envs, int64_t n, const UsvOracleConfig* cfg, const float* actions,
+                         float* obs, double* reward, uint8_t* terminated, uint8_t* truncated,
+                         float* terminal_obs, uint64_t seed, int64_t global_offset);
+
+/* RNG primitives exposed for tests (Philox4x32-10) */
+void usv_oracle_philox(uint64_t seed, uint64_t global_id, uint32_t episode, uint32_t block, uint32_t out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
