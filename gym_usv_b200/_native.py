@@ -1,0 +1,128 @@
+"""ctypes binding of libusvgpu.so (the C ABI declared in include/usvgpu.h).
+
+There is no CPU fallback: if the shared library is missing or no CUDA device is present the
+calls raise.  ``build()`` compiles the library in-tree with nvcc for sm_100a.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import shutil
+import subprocess
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_PKG)
+LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
+CSRC = os.path.join(_PKG, "csrc")
+SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
+HEADERS = [os.path.join(CSRC, "usv_model.cuh"), os.path.join(CSRC, "usv_philox.cuh"),
+           os.path.join(_ROOT, "include", "usvgpu.h")]
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
+              "-Xcompiler", "-fPIC"]
+
+OBS_DIM = 143
+ACT_DIM = 2
+SENSORS = 128
+MAX_OBSTACLES = 32
+DYN_ROWS = 23
+EPI_ROWS = 7
+
+ENV_ASMC_SIMPLE = 0
+ENV_ASMC_V0 = 1
+PREC_F64 = 0
+PREC_MIXED = 1
+
+FIELD_DYN, FIELD_EPI, FIELD_OBSTACLES, FIELD_N_OBS, FIELD_STEPS, FIELD_EPISODE, FIELD_EP_RETURN = range(7)
+
+# row names of FIELD_DYN / FIELD_EPI (include/usvgpu.h)
+DYN_NAMES = ("x", "y", "psi", "u", "v", "r", "x_dot_last", "y_dot_last", "psi_dot_last", "u_dot_last", "v_dot_last",
+             "r_dot_last", "e_u_last", "ka_dot_u_last", "ka_dot_psi_last", "psi_d_last", "o_dot_dot_last",
+             "o_dot_last", "o_last", "e_u_int", "ka_u", "ka_psi", "progress")
+EPI_NAMES = ("path_start_x", "path_start_y", "path_end_x", "path_end_y", "max_action_0", "max_action_2",
+             "reference_velocity")
+
+
+class UsvError(RuntimeError):
+    pass
+
+
+class UsvConfig(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("env_kind", "ignore_obstacles", "do_perturb", "skip_kinematic",
+                                         "max_episode_steps", "auto_reset", "precision", "obstacles_f32")]
+
+
+class UsvStats(C.Structure):
+    _fields_ = [("return_sum", C.c_double), ("length_sum", C.c_double), ("episodes", C.c_uint64),
+                ("terminated", C.c_uint64), ("out_of_bounds", C.c_uint64), ("time_limit", C.c_uint64),
+                ("env_steps", C.c_uint64), ("nonfinite", C.c_uint64)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+def _stale() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    return any(os.path.exists(s) and os.path.getmtime(s) > t for s in SOURCES + HEADERS)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """nvcc -gencode arch=compute_100a,code=sm_100a ... -> gym_usv_b200/libusvgpu.so (in-tree)."""
+    if not force and not _stale():
+        return LIB_PATH
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        raise UsvError("nvcc not found and libusvgpu.so is missing or stale: cannot build the CUDA library")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + SOURCES
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise UsvError("nvcc failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stderr)
+    return LIB_PATH
+
+
+_lib = None
+
+_SIGNATURES = {
+    "usvgpu_version": (C.c_int, []),
+    "usvgpu_last_error": (C.c_char_p, [C.c_void_p]),
+    "usvgpu_create": (C.c_int, [C.POINTER(UsvConfig), C.c_int, C.c_int64, C.c_int64, C.c_uint64, C.POINTER(C.c_void_p)]),
+    "usvgpu_destroy": (C.c_int, [C.c_void_p]),
+    "usvgpu_reset": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "usvgpu_step": (C.c_int, [C.c_void_p] * 8),
+    "usvgpu_rollout": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                 C.c_void_p, C.c_void_p]),
+    "usvgpu_field_bytes": (C.c_int64, [C.c_void_p, C.c_int32]),
+    "usvgpu_get_state": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
+    "usvgpu_set_state": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
+    "usvgpu_episode_stats": (C.c_int, [C.c_void_p, C.POINTER(UsvStats), C.c_int32, C.c_void_p]),
+    "usvgpu_stats_device_ptr": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "usvgpu_asmc_compute": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64,
+                                      C.c_int32, C.c_void_p, C.c_void_p]),
+    "usvgpu_sensors": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+}
+
+EXPORTS = tuple(_SIGNATURES)
+
+
+def lib():
+    """Load libusvgpu.so (never builds implicitly on a box without the .so AND without nvcc)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc: int, handle=None) -> None:
+    if rc != 0:
+        msg = lib().usvgpu_last_error(handle)
+        raise UsvError(f"libusvgpu error {rc}: {msg.decode() if msg else '?'}")

@@ -1,0 +1,285 @@
+"""UsvGpuVecEnv -- drop-in SB3-style VecEnv for 'usv-asmc-simple' running on one B200.
+
+Mirrors what ``make_vec_env('usv-asmc-simple', n_envs)`` gives the scripts in
+train_test/sb3_train_vec.py:67-81: ``reset() -> obs``, ``step(actions) -> (obs, rewards, dones,
+infos)`` with SB3 auto-reset semantics (``infos[i]['terminal_observation']``,
+``['TimeLimit.truncated']``, ``['episode']``), same observation / action spaces
+(gym_usv/envs/simple_env.py:27,30) and the 1000-step TimeLimit of gym_usv/__init__.py:30-34.
+
+Two faces of the same env:
+  * ``step(np_actions)``  -- host numpy in / host numpy out (what stock SB3 calls);
+  * ``step_tensor(cuda_actions)`` -- device-resident torch tensors in and out, zero host copies.
+
+All arithmetic happens in libusvgpu.so (hand-written sm_100a kernels).  torch is used only for
+device memory and streams.  There is no CPU path: constructing the env without CUDA raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Any, Iterable, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _native as nat
+from . import spaces
+
+ENV_ID = "usv-asmc-simple"
+MAX_EPISODE_STEPS = {"usv-asmc-simple": 1000}  # gym_usv/__init__.py:30-34
+
+
+class LazyInfos(Sequence):
+    """infos of one step without building N dicts: only done envs carry content."""
+
+    def __init__(self, n, done_idx, payload):
+        self._n, self._payload = n, {int(i): p for i, p in zip(done_idx, payload)}
+
+    def __len__(self):
+        return self._n
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(self._n))]
+        if i < 0:
+            i += self._n
+        if not 0 <= i < self._n:
+            raise IndexError(i)
+        return self._payload.get(i, {})
+
+
+class UsvGpuVecEnv:
+    metadata = {"render_modes": ["human", "rgb_array"], "render_fps": 30}  # simple_env.py:8
+
+    def __init__(self, num_envs: int, device: int | str | torch.device = 0, seed: int = 0, *,
+                 ignore_obstacles: bool = False, do_perturb: bool = False, skip_kinematic: bool = False,
+                 max_episode_steps: Optional[int] = None, auto_reset: bool = True, precision: str = "f64",
+                 obstacles_f32: bool = False, global_env_offset: int = 0, info_mode: str = "list",
+                 render_mode: Optional[str] = None):
+        if not torch.cuda.is_available():
+            raise nat.UsvError("UsvGpuVecEnv needs a CUDA device: there is no CPU fallback")
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        if self.device.type != "cuda":
+            raise nat.UsvError("UsvGpuVecEnv needs a CUDA device: there is no CPU fallback")
+        self.num_envs = int(num_envs)
+        self.observation_space = spaces.simple_observation_space()
+        self.action_space = spaces.simple_action_space()
+        self.render_mode = render_mode
+        self.info_mode = info_mode
+        if max_episode_steps is None:
+            max_episode_steps = MAX_EPISODE_STEPS[ENV_ID]
+        self.cfg = nat.UsvConfig(nat.ENV_ASMC_SIMPLE, int(ignore_obstacles), int(do_perturb), int(skip_kinematic),
+                                 int(max_episode_steps), int(auto_reset), {"f64": 0, "mixed": 1}[precision],
+                                 int(obstacles_f32))
+        self._seed = int(seed)
+        self.global_env_offset = int(global_env_offset)
+        self._lib = nat.lib()
+        self._h = C.c_void_p()
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self._dev_index = dev_index
+        nat.check(self._lib.usvgpu_create(C.byref(self.cfg), dev_index, self.num_envs, self.global_env_offset,
+                                          self._seed, C.byref(self._h)))
+        n = self.num_envs
+        with torch.cuda.device(self.device):
+            self.obs = torch.zeros((n, nat.OBS_DIM), dtype=torch.float32, device=self.device)
+            self.terminal_obs = torch.zeros((n, nat.OBS_DIM), dtype=torch.float32, device=self.device)
+            self.reward = torch.zeros(n, dtype=torch.float32, device=self.device)
+            self.terminated = torch.zeros(n, dtype=torch.uint8, device=self.device)
+            self.truncated = torch.zeros(n, dtype=torch.uint8, device=self.device)
+            self._actions_dev = torch.zeros((n, nat.ACT_DIM), dtype=torch.float32, device=self.device)
+        # pinned host mirrors for the numpy face
+        self._h_actions = torch.zeros((n, nat.ACT_DIM), dtype=torch.float32).pin_memory()
+        self._h_obs = torch.zeros((n, nat.OBS_DIM), dtype=torch.float32).pin_memory()
+        self._h_reward = torch.zeros(n, dtype=torch.float32).pin_memory()
+        self._h_term = torch.zeros(n, dtype=torch.uint8).pin_memory()
+        self._h_trunc = torch.zeros(n, dtype=torch.uint8).pin_memory()
+        self._pending = None
+        self._ep_ret = np.zeros(n, dtype=np.float64)   # host-side episode bookkeeping for infos['episode']
+        self._ep_len = np.zeros(n, dtype=np.int64)
+        self._closed = False
+
+    # ------------------------------------------------------------------ plumbing
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _check(self, rc):
+        nat.check(rc, self._h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def close(self):
+        if not self._closed and self._h:
+            self._lib.usvgpu_destroy(self._h)
+            self._closed = True
+
+    # ------------------------------------------------------------------ device-resident face
+    def reset_tensor(self, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Env.reset() for all envs (or those with mask != 0).  Returns the device obs tensor [N,143]
+        (columns 15.. keep their previous content: simple_env.py:302 reuses stale sensor data)."""
+        mptr = None
+        if mask is not None:
+            mask = mask.to(device=self.device, dtype=torch.uint8).contiguous()
+            mptr = C.c_void_p(mask.data_ptr())
+        self._check(self._lib.usvgpu_reset(self._h, mptr, C.c_void_p(self.obs.data_ptr()), self._stream()))
+        return self.obs
+
+    def step_tensor(self, actions: torch.Tensor):
+        """actions: float32 CUDA tensor [N,2].  Returns (obs, reward, terminated, truncated) device
+        tensors owned by the env (overwritten by the next step).  No host copy, no sync."""
+        if actions.device != self.device or actions.dtype != torch.float32 or not actions.is_contiguous():
+            actions = actions.to(device=self.device, dtype=torch.float32).contiguous()
+        if actions.shape != (self.num_envs, nat.ACT_DIM):
+            raise ValueError(f"actions must have shape {(self.num_envs, nat.ACT_DIM)}, got {tuple(actions.shape)}")
+        self._check(self._lib.usvgpu_step(
+            self._h, C.c_void_p(actions.data_ptr()), C.c_void_p(self.obs.data_ptr()),
+            C.c_void_p(self.reward.data_ptr()), C.c_void_p(self.terminated.data_ptr()),
+            C.c_void_p(self.truncated.data_ptr()), C.c_void_p(self.terminal_obs.data_ptr()), self._stream()))
+        return self.obs, self.reward, self.terminated, self.truncated
+
+    def rollout_tensor(self, actions: torch.Tensor, n_steps: int, action_wrap: int = 0):
+        """n_steps launches with pre-staged actions [K,N,2] (tools/profile_env.py:5-7 style loop)."""
+        assert actions.is_cuda and actions.dtype == torch.float32 and actions.is_contiguous()
+        self._check(self._lib.usvgpu_rollout(
+            self._h, C.c_void_p(actions.data_ptr()), int(n_steps), int(action_wrap), C.c_void_p(self.obs.data_ptr()),
+            C.c_void_p(self.reward.data_ptr()), C.c_void_p(self.terminated.data_ptr()),
+            C.c_void_p(self.truncated.data_ptr()), self._stream()))
+        return self.obs, self.reward, self.terminated, self.truncated
+
+    # ------------------------------------------------------------------ SB3 VecEnv face (host numpy)
+    def reset(self) -> np.ndarray:
+        self.reset_tensor()
+        self._ep_ret[:] = 0
+        self._ep_len[:] = 0
+        return self.obs.cpu().numpy()
+
+    def step_async(self, actions) -> None:
+        a = np.asarray(actions, dtype=np.float32).reshape(self.num_envs, nat.ACT_DIM)
+        self._h_actions.numpy()[...] = a
+        self._actions_dev.copy_(self._h_actions, non_blocking=True)
+        self.step_tensor(self._actions_dev)
+        self._h_obs.copy_(self.obs, non_blocking=True)
+        self._h_reward.copy_(self.reward, non_blocking=True)
+        self._h_term.copy_(self.terminated, non_blocking=True)
+        self._h_trunc.copy_(self.truncated, non_blocking=True)
+        self._pending = True
+
+    def step_wait(self):
+        assert self._pending, "step_wait() without step_async()"
+        torch.cuda.current_stream(self.device).synchronize()
+        self._pending = None
+        obs = self._h_obs.numpy().copy()
+        rew = self._h_reward.numpy().copy()
+        term = self._h_term.numpy().astype(bool)
+        trunc = self._h_trunc.numpy().astype(bool)
+        dones = term | trunc
+        self._ep_ret += rew
+        self._ep_len += 1
+        done_idx = np.flatnonzero(dones)
+        payload = []
+        if done_idx.size:
+            if self.cfg.auto_reset:
+                tob = self.terminal_obs[torch.as_tensor(done_idx, device=self.device)].cpu().numpy()
+            for k, i in enumerate(done_idx):
+                info = {"TimeLimit.truncated": bool(trunc[i] and not term[i]),
+                        "episode": {"r": float(self._ep_ret[i]), "l": int(self._ep_len[i])}}
+                if self.cfg.auto_reset:
+                    info["terminal_observation"] = tob[k]
+                payload.append(info)
+            self._ep_ret[done_idx] = 0
+            self._ep_len[done_idx] = 0
+        if self.info_mode == "lazy":
+            infos: Any = LazyInfos(self.num_envs, done_idx, payload)
+        else:
+            infos = [{} for _ in range(self.num_envs)]
+            for i, p in zip(done_idx, payload):
+                infos[int(i)] = p
+        return obs, rew, dones, infos
+
+    def step(self, actions):
+        self.step_async(actions)
+        return self.step_wait()
+
+    # ------------------------------------------------------------------ VecEnv odds and ends
+    def seed(self, seed: Optional[int] = None) -> List[Optional[int]]:
+        """Re-keys the reset RNG: takes effect for envs reset from now on (new handle state is kept)."""
+        if seed is not None:
+            self._seed = int(seed)
+            # the key lives in the handle: recreate it, keeping nothing (SB3 calls seed() before reset())
+            self._lib.usvgpu_destroy(self._h)
+            self._h = C.c_void_p()
+            nat.check(self._lib.usvgpu_create(C.byref(self.cfg), self._dev_index, self.num_envs,
+                                              self.global_env_offset, self._seed, C.byref(self._h)))
+        return [None if seed is None else seed + i for i in range(self.num_envs)]
+
+    def _indices(self, indices) -> Iterable[int]:
+        if indices is None:
+            return range(self.num_envs)
+        if isinstance(indices, int):
+            return [indices]
+        return indices
+
+    def get_attr(self, attr_name: str, indices=None) -> List[Any]:
+        idx = list(self._indices(indices))
+        if attr_name in ("render_mode", "observation_space", "action_space", "metadata"):
+            return [getattr(self, attr_name)] * len(idx)
+        fields = self.get_state()
+        if attr_name in ("position", "velocity"):
+            rows = fields["dyn"][0:3] if attr_name == "position" else fields["dyn"][3:6]
+            return [rows[:, i].copy() for i in idx]
+        raise AttributeError(attr_name)
+
+    def set_attr(self, attr_name: str, value: Any, indices=None) -> None:
+        raise AttributeError(f"cannot set '{attr_name}' on a GPU env; use set_state()")
+
+    def env_method(self, method_name: str, *args, indices=None, **kwargs) -> List[Any]:
+        raise AttributeError(f"'{method_name}' is not available on a GPU env")
+
+    def env_is_wrapped(self, wrapper_class, indices=None) -> List[bool]:
+        return [False] * len(list(self._indices(indices)))
+
+    def render(self, mode: Optional[str] = None):
+        return None  # no graphics stack on this box; a CUDA rasteriser is SURVEY 8f rank 4
+
+    def get_images(self):
+        return [None] * self.num_envs
+
+    # ------------------------------------------------------------------ state access (checkpoint / parity)
+    _FIELDS = {"dyn": (nat.FIELD_DYN, np.float64, (nat.DYN_ROWS,)), "epi": (nat.FIELD_EPI, np.float64, (nat.EPI_ROWS,)),
+               "obstacles": (nat.FIELD_OBSTACLES, None, (nat.MAX_OBSTACLES, 3)),
+               "n_obs": (nat.FIELD_N_OBS, np.int32, ()), "steps": (nat.FIELD_STEPS, np.int32, ()),
+               "episode": (nat.FIELD_EPISODE, np.int32, ()), "ep_return": (nat.FIELD_EP_RETURN, np.float64, ())}
+
+    def _field_array(self, name):
+        fid, dt, lead = self._FIELDS[name]
+        if dt is None:
+            dt = np.float32 if self.cfg.obstacles_f32 else np.float64
+        return fid, np.zeros(lead + (self.num_envs,), dtype=dt)
+
+    def get_state(self, names: Optional[Sequence[str]] = None) -> dict:
+        """Host copies of the SoA field groups ([rows][N]); see include/usvgpu.h UsvField."""
+        out = {}
+        for name in (names or self._FIELDS):
+            fid, arr = self._field_array(name)
+            self._check(self._lib.usvgpu_get_state(self._h, fid, arr.ctypes.data_as(C.c_void_p), arr.nbytes,
+                                                   self._stream()))
+            out[name] = arr
+        return out
+
+    def set_state(self, state: dict) -> None:
+        for name, val in state.items():
+            fid, arr = self._field_array(name)
+            arr[...] = val
+            self._check(self._lib.usvgpu_set_state(self._h, fid, arr.ctypes.data_as(C.c_void_p), arr.nbytes,
+                                                   self._stream()))
+
+    def episode_stats(self, reset: bool = False) -> dict:
+        st = nat.UsvStats()
+        self._check(self._lib.usvgpu_episode_stats(self._h, C.byref(st), int(reset), self._stream()))
+        return st.as_dict()
+
+    def stats_tensor(self) -> torch.Tensor:
+        """The device-side UsvStats block viewed as 8 x 8 bytes (for an optional NCCL all-reduce)."""
+        raise NotImplementedError

@@ -1,0 +1,161 @@
+/*
+ * usvgpu.h -- C ABI of libusvgpu.so: the batched gym-usv environment step on one B200.
+ *
+ * One handle owns the structure-of-arrays state of N lock-step environments on one
+ * device.  The CALLER owns the action / observation / reward / flag buffers (device
+ * memory, e.g. torch CUDA tensors passed as raw pointers).  All work is stream-ordered on
+ * the cudaStream_t the caller passes; nothing here synchronises unless it says so.
+ * Every function returns 0 on success or a negative UsvStatus; usvgpu_last_error() gives
+ * the text.  There is NO CPU fallback: without a CUDA device every call fails.
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the
+ * reference root, romi2002/gym-usv).
+ */
+#ifndef USVGPU_H
+#define USVGPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define USVGPU_VERSION 100         /* 0.1.0 */
+#define USVGPU_OBS_DIM 143         /* gym_usv/envs/simple_env.py:27  (15 + 128 sensors)      */
+#define USVGPU_ACT_DIM 2           /* gym_usv/envs/simple_env.py:30                           */
+#define USVGPU_SENSORS 128         /* gym_usv/envs/simple_env.py:11                           */
+#define USVGPU_MAX_OBSTACLES 32    /* reset draws 15..29 (simple_env.py:257); padded to 32    */
+#define USVGPU_LEGACY_OBS_DIM 6    /* gym_usv/envs/usv_asmc_env.py:89-96                      */
+
+typedef struct UsvGpu* usvgpu_handle;
+
+typedef enum UsvStatus {
+    USV_OK = 0,
+    USV_ERR_INVALID = -1,   /* bad argument                          */
+    USV_ERR_CUDA = -2,      /* CUDA runtime error (text in last_error) */
+    USV_ERR_NO_DEVICE = -3, /* no usable CUDA device: there is no CPU path */
+    USV_ERR_ALLOC = -4
+} UsvStatus;
+
+typedef enum UsvEnvKind {
+    USV_ENV_ASMC_SIMPLE = 0, /* 'usv-asmc-simple' gym_usv/__init__.py:30-34 -> envs/simple_env_asmc.py */
+    USV_ENV_ASMC_V0 = 1      /* 'usv-asmc-v0'     gym_usv/__init__.py:3-6   -> envs/usv_asmc_env.py    */
+} UsvEnvKind;
+
+typedef enum UsvPrecision {
+    USV_PREC_F64 = 0,  /* float64 state + arithmetic, as the reference (numpy float64)                 */
+    USV_PREC_MIXED = 1 /* float64 integrator state, float32 force/transcendental terms */
+} UsvPrecision;
+
+/* Mirrors the knobs of the reference envs; literals that the reference hard-codes
+ * (vessel coefficients, gains, sensor fan, bounds) are compile-time constants. */
+typedef struct UsvConfig {
+    int32_t env_kind;          /* UsvEnvKind                                                      */
+    int32_t ignore_obstacles;  /* simple_env.py:49,155,222-224,334                                */
+    int32_t do_perturb;        /* usv_asmc.py:53,184-199 (UsvSimpleASMCEnv passes False)          */
+    int32_t skip_kinematic;    /* simple_env.py:310 update_position=False; NOT the default        */
+    int32_t max_episode_steps; /* TimeLimit: 1000 for usv-asmc-simple; 0 = none                   */
+    int32_t auto_reset;        /* SB3 VecEnv semantics: done envs are reset inside step()         */
+    int32_t precision;         /* UsvPrecision                                                    */
+    int32_t obstacles_f32;     /* in-kernel reset draws obstacle tables on the float32 grid and   *
+                                * stores them as float32 (halves the table traffic)               */
+} UsvConfig;
+
+/* Episode statistics accumulated on the device (what SB3 Monitor / RecordEpisodeStatistics
+ * would log); sums are over episodes finished since the last usvgpu_episode_stats(reset=1). */
+typedef struct UsvStats {
+    double   return_sum;
+    double   length_sum;
+    uint64_t episodes;
+    uint64_t terminated;      /* collisions   simple_env.py:334 */
+    uint64_t out_of_bounds;   /* simple_env.py:336              */
+    uint64_t time_limit;      /* TimeLimit truncations          */
+    uint64_t env_steps;       /* total env-steps executed       */
+    uint64_t nonfinite;       /* env-steps that produced a non-finite pose (guard counter) */
+} UsvStats;
+
+/* State field groups for usvgpu_get_state / usvgpu_set_state.  Layout of every group is
+ * [rows][n_envs] (structure of arrays, env index fastest). */
+typedef enum UsvField {
+    /* float64 [23][N]: x y psi | u v r | x_dot y_dot psi_dot u_dot v_dot r_dot e_u ka_dot_u ka_dot_psi (last,
+     * usv_asmc.py:57) | psi_d_last o_dot_dot_last o_dot_last o_last (usv_asmc.py:58) |
+     * e_u_int ka_u ka_psi (usv_asmc.py:63) | progress (simple_env.py:53) */
+    USV_FIELD_DYN = 0,
+    /* float64 [7][N]: path_start x y | path_end x y | max_action[0] max_action[2] | reference_velocity */
+    USV_FIELD_EPI = 1,
+    /* float64 (float32 when obstacles_f32) [32][3][N]: per slot x, y, radius (simple_env.py:258,290) */
+    USV_FIELD_OBSTACLES = 2,
+    USV_FIELD_N_OBS = 3,     /* int32 [N]   simple_env.py:268                    */
+    USV_FIELD_STEPS = 4,     /* int32 [N]   TimeLimit elapsed steps              */
+    USV_FIELD_EPISODE = 5,   /* int32 [N]   resets so far (Philox counter word)  */
+    USV_FIELD_EP_RETURN = 6, /* float64 [N] running episode return               */
+    /* legacy env (USV_ENV_ASMC_V0) float32 [25][N]: state[6] velocity[3] position[3] aux[3] last[9] action_last? see DESIGN.md */
+    USV_FIELD_LEGACY = 7,
+    USV_FIELD_LEGACY_TARGET = 8 /* float64 [6][N]: x_0 y_0 desired_speed ak x_d y_d (usv_asmc_env.py:296) */
+} UsvField;
+
+#define USV_DYN_ROWS 23
+#define USV_EPI_ROWS 7
+
+int usvgpu_version(void);
+/* text of the last error on this handle (or of the last failed usvgpu_create when h == NULL) */
+const char* usvgpu_last_error(usvgpu_handle h);
+
+/* Replaces N x `gym.make('usv-asmc-simple')` / SB3 make_vec_env (train_test/sb3_train_vec.py:67):
+ * allocates the SoA state for n_envs on `device`.  global_env_offset is the index of this
+ * shard's first env in the whole job: the reset RNG is Philox4x32-10 keyed by (seed, global
+ * env id, episode), so trajectories do not depend on how envs are sharded over GPUs. */
+int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t global_env_offset, uint64_t seed,
+                  usvgpu_handle* out);
+int usvgpu_destroy(usvgpu_handle h);
+
+/* Replaces Env.reset() (simple_env_asmc.py:14-16 -> simple_env.py:228-308) for the envs whose
+ * mask byte is non-zero (all envs when mask == NULL).  Writes observation columns 0..14 of the
+ * selected rows of obs[N][143] and leaves columns 15..142 untouched -- the reference builds
+ * the reset observation from the previous episode's stale sensor data (simple_env.py:302). */
+int usvgpu_reset(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream);
+
+/* Replaces VecEnv.step(): for every env 2 x UsvAsmc.compute (usv_asmc.py:53-244, 20 sub-steps)
+ * then UsvSimpleEnv.step(zeros) (simple_env.py:310-346) then TimeLimit.  actions float32 [N][2],
+ * obs float32 [N][143], reward float32 [N], terminated/truncated uint8 [N] (all device pointers).
+ * With auto_reset, done envs are reset in the same launch: obs then holds the reset observation
+ * and, when terminal_obs != NULL, rows of done envs in terminal_obs[N][143] hold the last
+ * observation of the finished episode (SB3 infos[i]["terminal_observation"]). */
+int usvgpu_step(usvgpu_handle h, const float* actions, float* obs, float* reward, uint8_t* terminated,
+                uint8_t* truncated, float* terminal_obs, void* stream);
+
+/* K back-to-back steps (one launch each; state round-trips HBM every step) with pre-staged
+ * actions float32 [K][N][2]; outputs are overwritten every step.  action_wrap > 0 re-uses the
+ * first action_wrap slabs cyclically.  This is the loop of tools/profile_env.py:5-7. */
+int usvgpu_rollout(usvgpu_handle h, const float* actions, int32_t n_steps, int32_t action_wrap, float* obs,
+                   float* reward, uint8_t* terminated, uint8_t* truncated, void* stream);
+
+/* Copy a whole field group out of / into the handle.  buf may be host or device memory
+ * (cudaMemcpyDefault); size is checked against usvgpu_field_bytes(). */
+int64_t usvgpu_field_bytes(usvgpu_handle h, int32_t field);
+int usvgpu_get_state(usvgpu_handle h, int32_t field, void* buf, int64_t bytes, void* stream);
+int usvgpu_set_state(usvgpu_handle h, int32_t field, const void* buf, int64_t bytes, void* stream);
+
+/* Device-side statistics -> host struct (synchronises `stream`).  reset != 0 zeroes them after. */
+int usvgpu_episode_stats(usvgpu_handle h, UsvStats* out, int32_t reset, void* stream);
+/* device address of the UsvStats block (for an NCCL all-reduce issued by the caller) */
+int usvgpu_stats_device_ptr(usvgpu_handle h, void** out);
+
+/* Unit-parity entry point: UsvAsmc.compute (usv_asmc.py:53-244) for n independent
+ * controller+vessel states.  state float64 [23][n] uses the USV_FIELD_DYN row order (row 22
+ * is ignored); actions float64 [n][2]; n_calls consecutive calls of 10 sub-steps each;
+ * first_substep is UsvAsmc.perturb_step at entry; info (may be NULL) float64 [4][n] receives
+ * psi_d, u_d, tport, tstbd of the last sub-step (usv_asmc.py:78,125,168-169). */
+int usvgpu_asmc_compute(int device, int64_t n, double* state, const double* actions, int32_t n_calls,
+                        int32_t do_perturb, int64_t first_substep, int32_t precision, double* info, void* stream);
+
+/* Unit-parity entry point: UsvAsmcCaEnv.compute_sensor_measurments (usv_asmc_ca_env.py:411-437)
+ * with the 128-ray fan of simple_env.py:11-14.  pose float64 [3][n]; obstacles float64
+ * [32][3][n]; n_obs int32 [n]; out float64 [128][n] distances. */
+int usvgpu_sensors(int device, int64_t n, const double* pose, const double* obstacles, const int32_t* n_obs,
+                   double* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* USVGPU_H */

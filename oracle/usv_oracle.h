@@ -89,6 +89,8 @@ void usv_oracle_sensors(const double position[3], int sensor_count, double senso
  * sensor part of the caller's obs row stale like simple_env.py:302 does. */
 void usv_oracle_simple_reset(UsvOracleEnv* e, const UsvOracleConfig* cfg, uint64_t seed,
                              uint64_t global_id, float* obs);
+/* simple_env.py:302: reset observation of the current (e.g. injected) state, all 143 columns */
+void usv_oracle_simple_reset_obs(const UsvOracleEnv* e, float* obs);
 /* first construction: simple_env.py:32-54 defaults */
 void usv_oracle_simple_init(UsvOracleEnv* e);
 

@@ -96,6 +96,8 @@ def lib():
         L.usv_oracle_sensors.argtypes = [vp, i32, dbl, vp, dbl, vp, vp, i32, vp, vp]
         L.usv_oracle_simple_init.argtypes = [vp]
         L.usv_oracle_simple_reset.argtypes = [vp, vp, u64, u64, vp]
+        L.usv_oracle_simple_reset_obs.argtypes = [vp, vp]
+        L.usv_oracle_simple_reset_obs.restype = None
         L.usv_oracle_simple_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.usv_oracle_vec_reset.argtypes = [vp, i64, vp, u64, i64, vp]
         L.usv_oracle_vec_step.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, vp, u64, i64]
