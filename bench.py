@@ -1,0 +1,385 @@
+#!/usr/bin/env python
+"""bench.py -- env-steps/s of the batched 'usv-asmc-simple' step (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]          # our CUDA path
+    python bench.py --impl reference [...]                        # the reference's CPU algorithm (oracle port)
+    torchrun --nproc-per-node N ... bench.py --gpus N ...         # one rank per GPU, envs sharded by index range
+
+A "step" is one VecEnv.step() over one batch of envs on every rank (one kernel launch per rank: 20
+ASMC + 3-DOF sub-steps, kinematic post-step, closest point, 128-ray sensor pass, reward, flags, in-kernel
+auto-reset, observation rows).  Workload: BASELINE.json configs[2] -- 65 536 envs per GPU with randomised
+obstacles and range-sensor observations (weak scaling: 8 GPUs = 524 288 envs; --envs-per-gpu 131072 gives
+the 1 M-env configs[3]).  The timed loop rotates over --batches independent env batches so that the state a
+step reads was evicted from the 126 MB L2 by the other batches' steps (working set > L2).
+
+Printed JSON (one line, rank 0): see the keys below.  `value` = whole-job env-steps/s with actions and state
+resident in HBM; `e2e` = the same metric through the host-numpy VecEnv.step() face (pinned H2D of actions,
+D2H of observations / rewards / flags inside the timed region); `roofline` = algorithmic bytes per launch /
+CUDA-event launch time against the measured HBM copy bandwidth; `cpu_baseline` = the CPU oracle (C port of the
+reference's numpy algorithm) timed on this box's host cores on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "env_steps_per_sec"
+UNIT = "env-steps/s"
+# Algorithmic HBM bytes per env-step (DESIGN.md "Algorithmic bytes"; SURVEY.md 8d with float64 dynamic state):
+#   read : 23 f64 dynamic state + 7 f64 episode constants + n_obs/steps (2 i32) + f64 episode return
+#          + 32 x 3 obstacle table + 2 f32 action
+#   write: 23 f64 dynamic state + steps i32 + f64 episode return + 143 f32 observation + f32 reward + 2 flag bytes
+def algorithmic_bytes(obstacles: bool, obstacles_f32: bool) -> int:
+    rd = 23 * 8 + 7 * 8 + 2 * 4 + 8 + 2 * 4
+    if obstacles:
+        rd += 32 * 3 * (4 if obstacles_f32 else 8)
+    wr = 23 * 8 + 4 + 8 + 143 * 4 + 4 + 2
+    return rd + wr
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:  # noqa: BLE001
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples SM clock / throttle reasons of one GPU during the timed region (NVML, 20 ms period;
+    nvidia-smi query as a fallback)."""
+
+    def __init__(self, index: int, uuid: str | None = None):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        self._nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = None
+            if uuid:
+                try:
+                    self._h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+                except Exception:  # noqa: BLE001
+                    self._h = None
+            if self._h is None:
+                self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:  # noqa: BLE001
+            self._nv = None
+
+    _BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+             0x80: "hw_power_brake", 0x2: "app_clocks_setting", 0x10: "sync_boost", 0x100: "display_clocks"}
+
+    def _sample_once(self):
+        if self._nv is not None:
+            nv = self._nv
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                except Exception:  # noqa: BLE001
+                    r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+                for bit, name in self._BITS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            return
+        try:
+            out = subprocess.run(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=clocks.sm,clocks.max.sm,"
+                 "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap",
+                 "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout.strip()
+            f = [x.strip() for x in out.split(",")]
+            self.samples.append(int(f[0]))
+            self.max_mhz = int(f[1])
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:]):
+                if v.lower().startswith("active"):
+                    self.reasons.add(name)
+        except Exception:  # noqa: BLE001
+            pass
+
+    def _run(self):
+        while not self._stop.is_set():
+            self._sample_once()
+            self._stop.wait(0.02 if self._nv is not None else 0.2)
+
+    def start(self):
+        self._thr = threading.Thread(target=self._run, daemon=True)
+        self._thr.start()
+
+    def stop(self):
+        self._sample_once()
+        self._stop.set()
+        if self._thr:
+            self._thr.join(timeout=5)
+        return {"sm_mhz": (statistics.median(self.samples) if self.samples else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_oracle_rate(n_envs: int, budget_s: float, threads: int, ignore_obstacles: bool, seed: int = 0):
+    """env-steps/s of the CPU oracle (all `threads` host threads) on n_envs lock-step envs, for ~budget_s."""
+    import numpy as np
+    import usv_oracle as uo
+    ov = uo.OracleVecEnv(n_envs, seed=seed, ignore_obstacles=ignore_obstacles, n_threads=threads)
+    ov.reset()
+    rng = np.random.default_rng(0)
+    acts = rng.uniform([0.2, -1], [1, 1], (8, n_envs, 2)).astype(np.float32)
+    for k in range(2):
+        ov.step(acts[k])
+    t0 = time.perf_counter()
+    steps = 0
+    while True:
+        ov.step(acts[steps % 8])
+        steps += 1
+        el = time.perf_counter() - t0
+        if el >= budget_s:
+            break
+    return n_envs * steps / el, steps, el
+
+
+def host_threads() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:  # noqa: BLE001
+        return os.cpu_count() or 1
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU algorithm for the path (the C oracle port of its numpy code; the
+    reference itself is Python + gymnasium and cannot travel to the GPU box), all host threads, on a bounded
+    sample of the same workload.  Rank 0 only."""
+    if rank != 0:
+        return
+    import numpy as np
+    import usv_oracle as uo
+    threads = host_threads()
+    n = args.ref_envs
+    ov = uo.OracleVecEnv(n, seed=args.seed, ignore_obstacles=bool(args.no_obstacles), n_threads=threads)
+    ov.reset()
+    rng = np.random.default_rng(0)
+    acts = rng.uniform([0.2, -1], [1, 1], (8, n, 2)).astype(np.float32)
+    for k in range(args.warmup):
+        ov.step(acts[k % 8])
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        ov.step(acts[k % 8])
+    el = time.perf_counter() - t0
+    value = n * args.steps / el
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * el / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, world, reference_sample=n),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{n} lock-step envs x {args.steps} steps, OpenMP over {threads} host threads"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world, reference_sample=None):
+    cfg = {
+        "workload": ("usv-asmc-simple (ASMC path following" + (", obstacles ignored" if args.no_obstacles else
+                     " with randomised obstacles + 128-ray range sensors") + f"), {args.envs_per_gpu} envs per GPU, "
+                     "BASELINE.json configs[2]" + ("" if args.envs_per_gpu == 65536 else " (resized)")),
+        "envs_per_gpu": args.envs_per_gpu, "envs_total": args.envs_per_gpu * world,
+        "sub_steps_per_env_step": 20, "max_episode_steps": 1000, "auto_reset": True,
+        "precision": args.precision, "obstacle_table": "f32" if args.obstacles_f32 else "f64",
+        "sharding": f"contiguous env-index ranges over {world} GPU(s), no data-path collective",
+        "actions": "uniform in the action box, pre-staged on device",
+        "l2": f"{args.batches} rotating env batches per GPU (consecutive steps touch different state; working set > 126 MB L2)",
+    }
+    if reference_sample is not None:
+        cfg["reference_sample_envs"] = reference_sample
+    return cfg
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args, rank, local_rank, world):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import gym_usv_b200 as usv
+    from gym_usv_b200.sharding import reduce_episode_stats, shard_range
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.envs_per_gpu
+    lo, hi = shard_range(n * world, rank, world)
+    envs = []
+    for b in range(args.batches):
+        e = usv.UsvGpuVecEnv(hi - lo, device=local_rank, seed=args.seed + b, global_env_offset=lo,
+                             ignore_obstacles=bool(args.no_obstacles), obstacles_f32=bool(args.obstacles_f32),
+                             precision=args.precision, info_mode="lazy")
+        e.reset_tensor()
+        envs.append(e)
+    A = 8
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    acts = torch.rand((A, n, 2), generator=gen, device=dev)
+    acts = (acts * torch.tensor([0.8, 2.0], device=dev) + torch.tensor([0.2, -1.0], device=dev)).contiguous()
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    def do_step(k):
+        envs[k % len(envs)].step_tensor(acts[k % A])
+
+    # pre-roll so that episodes are spread over their whole life (steady-state mix of resets and obstacle hits)
+    for k in range(args.preroll * len(envs)):
+        do_step(k)
+    for k in range(args.warmup):
+        do_step(k)
+    sync_all()
+    try:
+        uuid = "GPU-" + str(torch.cuda.get_device_properties(dev).uuid)
+    except Exception:  # noqa: BLE001
+        uuid = None
+    sampler = ClockSampler(local_rank, uuid)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.perf_counter()
+    ev0.record()
+    for k in range(args.steps):
+        do_step(k)
+    ev1.record()
+    sync_all()
+    t_wall = time.perf_counter() - t_wall0
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop()
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = n * world * args.steps / (ms_max * 1e-3)
+
+    # ---- e2e: host numpy in / host numpy out through VecEnv.step() -----------------------------------
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+    h_acts = np.ascontiguousarray(acts.cpu().numpy())
+    env0 = envs[0]
+    for k in range(2):
+        env0.step(h_acts[k % A])
+    sync_all()
+    t0 = time.perf_counter()
+    sink = 0.0
+    for k in range(e2e_steps):
+        obs, rew, dones, infos = envs[k % len(envs)].step(h_acts[k % A])
+        sink += float(rew[0])
+    torch.cuda.synchronize(dev)
+    te = time.perf_counter() - t0
+    tt = torch.tensor([te], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    e2e_value = n * world * e2e_steps / float(tt.item())
+    h2d = n * 2 * 4
+    d2h = n * (143 * 4 + 4 + 1 + 1)
+
+    stats = envs[0].episode_stats()
+    for e in envs[1:]:
+        s = e.episode_stats()
+        stats = {k: stats[k] + s[k] for k in stats}
+    stats = reduce_episode_stats(stats, device=dev)
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        abytes = algorithmic_bytes(not args.no_obstacles, bool(args.obstacles_f32))
+        launch_s = (ms * 1e-3) / args.steps  # rank-0 launch duration (one kernel per step)
+        achieved = abytes * n / launch_s / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64" if args.precision == "f64" else "f64 state / f32 force terms",
+            "data": "synthetic", "config": workload_config(args, world),
+            "sub_steps_per_sec": value * 20,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": e2e_steps, "api": "UsvGpuVecEnv.step(np.ndarray) -> np.ndarray obs/rew/dones + lazy infos"},
+            "gpu_launches": args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_env_step": abytes,
+                         "kernel": "usv::step_kernel", "launch_us": launch_s * 1e6,
+                         "note": "the kernel is FP64-issue bound, not HBM bound: see DESIGN.md and profiles/"},
+            "clocks": clocks,
+            "host_wall_s": t_wall,
+            "episode_stats": stats,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            threads = host_threads()
+            v, st, el = cpu_oracle_rate(args.ref_envs, args.cpu_budget_s, threads, bool(args.no_obstacles), args.seed)
+            v1, st1, el1 = cpu_oracle_rate(min(args.ref_envs, 1024), max(2.0, args.cpu_budget_s / 4), 1,
+                                           bool(args.no_obstacles), args.seed)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": f"{args.ref_envs} lock-step envs x {st} steps ({el:.1f} s), C oracle, OpenMP",
+                                    "single_core_value": v1}
+        print(json.dumps(line), flush=True)
+    for e in envs:
+        e.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=600)
+    ap.add_argument("--warmup", type=int, default=30)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs-per-gpu", type=int, default=65536)
+    ap.add_argument("--batches", type=int, default=3)
+    ap.add_argument("--preroll", type=int, default=40, help="untimed steps per batch before warm-up (episode mixing)")
+    ap.add_argument("--no-obstacles", action="store_true", help="configs[1] semantics (ignore_obstacles=True)")
+    ap.add_argument("--obstacles-f32", type=int, default=1)
+    ap.add_argument("--precision", default="f64", choices=["f64", "mixed"])
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--e2e-steps", type=int, default=30)
+    ap.add_argument("--ref-envs", type=int, default=4096, help="bounded CPU sample: lock-step envs per oracle step")
+    ap.add_argument("--cpu-budget-s", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: spawn one rank per GPU ourselves
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(29400 + os.getpid() % 500), os.path.abspath(__file__)]
+        raise SystemExit(subprocess.call(cmd + sys.argv[1:]))
+    run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,394 @@
+"""Parity of the CUDA path (libusvgpu.so through its C ABI) against the CPU oracle and against the
+golden vectors generated from the reference.  GPU only (-m gpu).
+
+Tolerances (float64 state + arithmetic on both sides; the GPU contracts a*b+c into FMA and expands
+the 3x3 products in closed form, so results differ from numpy by ulps that the closed loop carries
+along):  pose / velocity 1e-7 absolute over 1000-step rollouts, reward 1e-6, float32 observations
+2e-6; terminated / truncated flags and episode lengths EXACT.
+"""
+import numpy as np
+import pytest
+
+import usv_oracle as uo
+from _helpers import action_stream, golden_reset_maps, inject_gpu, load_golden, oracle_to_gpu_state
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+POSE_ATOL = 1e-7
+REW_ATOL = 1e-6
+OBS_ATOL = 2e-6
+
+
+@pytest.fixture(scope="module")
+def usv():
+    if not torch.cuda.is_available():
+        pytest.fail("gpu-marked test collected without a CUDA device")
+    import gym_usv_b200 as m
+    return m
+
+
+def _dyn_from_oracle(s):
+    n = len(s)
+    dyn = np.zeros((23, n))
+    dyn[0:3], dyn[3:6], dyn[6:15], dyn[15:19], dyn[19:22] = s["eta"].T, s["nu"].T, s["last"].T, s["so"].T, s["aux"].T
+    return dyn
+
+
+# ------------------------------------------------------------------------------------------
+# UsvAsmc.compute
+# ------------------------------------------------------------------------------------------
+def test_asmc_compute_golden_anchor_and_fixed_actions(usv):
+    g = load_golden("asmc_compute.npz")
+    dev = torch.device("cuda", 0)
+    # anchor: zero state, action [1.0, 0.5], three calls
+    st = torch.zeros((23, 1), dtype=torch.float64, device=dev)
+    act = torch.tensor(g["anchor_action"][None], dtype=torch.float64, device=dev)
+    for c in range(3):
+        info = usv.asmc_compute(st, act, n_calls=1, want_info=True).cpu().numpy()[:, 0]
+        got = np.hstack([st[:6, 0].cpu().numpy(), info[2], info[3]])
+        np.testing.assert_allclose(got, g["anchor"][c], rtol=1e-11, atol=1e-14)
+    # the three actions of reference tests/test_usv_asmc.py, N copies each: all copies identical,
+    # checkpoints match the reference, inequalities of the reference tests hold
+    N = 1024
+    for k, a in enumerate(g["fixed_actions"]):
+        st = torch.zeros((23, N), dtype=torch.float64, device=dev)
+        act = torch.tensor(np.repeat(a[None], N, 0), dtype=torch.float64, device=dev)
+        done = 0
+        for j, c in enumerate(g["fixed_checkpoints"]):
+            usv.asmc_compute(st, act, n_calls=int(c) - done)
+            done = int(c)
+            h = st.cpu().numpy()
+            assert np.all(h == h[:, :1]), "lock-step copies of one env must be bit-identical"
+            if k == 2 and c > 500:  # ill-conditioned zero-speed case, see tests/test_oracle_golden.py
+                np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=0, atol=0.05)
+                continue
+            np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=1e-9, atol=1e-11)
+            np.testing.assert_allclose(h[3:6, 0], g["fixed_vel"][k, j], rtol=1e-9, atol=1e-11)
+        x, y, psi, u, v, r = h[:6, 0]
+        if k == 0:
+            assert np.allclose(h[:6], 0)
+        elif k == 1:
+            assert x > 10 and abs(y) < 1 and abs(psi) < 1 and u > 1 and abs(v) < 1 and abs(r) < 1
+        else:
+            assert psi > 5
+
+
+@pytest.mark.parametrize("perturb", [False, True])
+def test_asmc_compute_random_rollout_vs_golden(usv, perturb):
+    g = load_golden("asmc_compute.npz")
+    name = "perturb" if perturb else "rand"
+    acts = g[f"{name}_actions"]
+    dev = torch.device("cuda", 0)
+    st = torch.zeros((23, 1), dtype=torch.float64, device=dev)
+    worst = 0.0
+    for c in range(len(acts)):
+        a = torch.tensor(acts[c][None].astype(np.float64), device=dev)
+        info = usv.asmc_compute(st, a, n_calls=1, do_perturb=perturb, first_substep=10 * c, want_info=True)
+        h = st[:6, 0].cpu().numpy()
+        worst = max(worst, float(np.max(np.abs(h[:3] - g[f"{name}_pos"][c]))),
+                    float(np.max(np.abs(h[3:] - g[f"{name}_vel"][c]))))
+        np.testing.assert_allclose(info.cpu().numpy()[:, 0], g[f"{name}_info"][c], rtol=1e-6, atol=1e-6)
+    assert worst < POSE_ATOL, worst
+
+
+def test_asmc_compute_batch_vs_oracle(usv):
+    """4096 random states x 50 calls (500 sub-steps) free-running against the C oracle."""
+    N, calls = 4096, 50
+    rng = np.random.default_rng(3)
+    o = uo.OracleAsmc(N)
+    o.s["eta"] = rng.uniform([0, 0, -np.pi], [20, 20, np.pi], (N, 3))
+    o.s["nu"] = rng.uniform(0, 0.15, (N, 3))
+    acts = rng.uniform([0.2, -1], [1, 1], (N, 2)).astype(np.float32).astype(np.float64)
+    dev = torch.device("cuda", 0)
+    st = torch.tensor(_dyn_from_oracle(o.s), device=dev)
+    usv.asmc_compute(st, torch.tensor(acts, device=dev), n_calls=calls)
+    o.compute(acts, n_calls=calls, n_threads=0)
+    want = _dyn_from_oracle(o.s)
+    got = st.cpu().numpy()
+    err = np.abs(got - want)[:22]
+    # pose / velocity
+    assert err[:6].max() < POSE_ATOL, err[:6].max()
+    # controller memory (derivative terms are O(1..100) and carry the sign() chatter)
+    assert np.quantile(err[6:], 0.999) < 1e-6
+
+
+# ------------------------------------------------------------------------------------------
+# range sensors
+# ------------------------------------------------------------------------------------------
+def _sensor_batch(usv, pos, ox, oy, rad, n):
+    m = len(n)
+    dev = torch.device("cuda", 0)
+    obst = np.zeros((32, 3, m))
+    obst[:, 0], obst[:, 1], obst[:, 2] = ox.T, oy.T, rad.T
+    out = usv.sensor_distances(torch.tensor(pos.T.copy(), device=dev), torch.tensor(obst, device=dev),
+                               torch.tensor(n.astype(np.int32), device=dev))
+    return out.cpu().numpy().T
+
+
+def test_sensors_vs_golden(usv):
+    g = load_golden("sensors.npz")
+    sel = np.flatnonzero(g["S"] == 128)
+    got = _sensor_batch(usv, g["pos"][sel], g["ox"][sel], g["oy"][sel], g["rad"][sel], g["n"][sel])
+    want = g["dist"][sel]
+    assert np.array_equal(got < 100, want < 100)
+    np.testing.assert_allclose(got, want, rtol=0, atol=1e-9)
+    assert (want < 0).sum() > 10
+
+
+def test_sensors_random_vs_oracle(usv):
+    """20k random scenes incl. boats inside circles, overlapping circles and large |psi|."""
+    rng = np.random.default_rng(11)
+    m = 20000
+    n = rng.integers(1, 30, m)
+    pos = np.stack([rng.uniform(0, 20, m), rng.uniform(0, 20, m), rng.uniform(-400, 400, m)], 1)
+    ox, oy = rng.uniform(0, 20, (m, 32)), rng.uniform(0, 20, (m, 32))
+    rad = rng.uniform(0.15, 0.5, (m, 32))
+    inside = rng.random(m) < 0.05
+    ox[inside, 0] = pos[inside, 0] + 0.1
+    oy[inside, 0] = pos[inside, 1] - 0.05
+    close = rng.random(m) < 0.3  # a cluster of overlapping obstacles near the bow
+    for j in range(3):
+        ox[close, j + 1] = pos[close, 0] + np.cos(pos[close, 2]) * (0.8 + 0.3 * j) + rng.normal(0, 0.1, close.sum())
+        oy[close, j + 1] = pos[close, 1] + np.sin(pos[close, 2]) * (0.8 + 0.3 * j) + rng.normal(0, 0.1, close.sum())
+    got = _sensor_batch(usv, pos, ox, oy, rad, n)
+    want = np.stack([uo.sensors(pos[i], rad[i, :n[i]], ox[i, :n[i]], oy[i, :n[i]]) for i in range(m)])
+    mism = (got < 100) != (want < 100)
+    # a hit/miss flip needs a ray tangent to a circle to within rounding: allow none on this seed
+    assert mism.sum() == 0, int(mism.sum())
+    np.testing.assert_allclose(got, want, rtol=0, atol=1e-8)
+    assert (want < 100).mean() > 0.02
+
+
+# ------------------------------------------------------------------------------------------
+# env step: golden replay (reference states injected) and oracle lock-step
+# ------------------------------------------------------------------------------------------
+def _gpu_replay(usv, gname, ignore_obstacles):
+    g = load_golden(gname)
+    acts = g["actions"]
+    E, T = g["obs"].shape[:2]
+    rmap = golden_reset_maps(g)
+    env = usv.UsvGpuVecEnv(E, device=0, ignore_obstacles=ignore_obstacles, auto_reset=False)
+    st = env.get_state()
+    for e in range(E):
+        inject_gpu(st, e, g, rmap[e][0])
+    env.set_state(st)
+    worst = dict(pos=0.0, vel=0.0, rew=0.0, obs=0.0)
+    ndone = 0
+    for t in range(T):
+        a = torch.tensor(np.repeat(acts[t][None], E, 0), device=env.device)
+        obs, rew, term, trunc = env.step_tensor(a)
+        term, trunc = term.cpu().numpy(), trunc.cpu().numpy()
+        assert np.array_equal(term, g["terminated"][:, t]), t
+        assert np.array_equal(trunc, g["truncated"][:, t]), t
+        dyn = env.get_state(["dyn"])["dyn"]
+        worst["pos"] = max(worst["pos"], float(np.abs(dyn[0:3].T - g["pos"][:, t]).max()))
+        worst["vel"] = max(worst["vel"], float(np.abs(dyn[3:6].T - g["vel"][:, t]).max()))
+        worst["rew"] = max(worst["rew"], float(np.abs(rew.cpu().numpy() - g["reward"][:, t]).max()))
+        worst["obs"] = max(worst["obs"], float(np.abs(obs.cpu().numpy() - g["obs"][:, t]).max()))
+        done = np.flatnonzero(term | trunc)
+        if done.size:
+            st = env.get_state()
+            for e in done:
+                inject_gpu(st, int(e), g, rmap[int(e)][t + 1])
+                ndone += 1
+            env.set_state(st)
+    env.close()
+    return worst, ndone
+
+
+def test_env_golden_replay_with_obstacles(usv):
+    w, ndone = _gpu_replay(usv, "simple_asmc_env.npz", False)
+    assert ndone >= 8
+    assert w["pos"] < POSE_ATOL and w["vel"] < POSE_ATOL and w["rew"] < 2e-5 and w["obs"] < OBS_ATOL, w
+
+
+def test_env_golden_replay_ignore_obstacles(usv):
+    w, _ = _gpu_replay(usv, "simple_asmc_env_noobs.npz", True)
+    assert w["pos"] < POSE_ATOL and w["vel"] < POSE_ATOL and w["rew"] < 2e-5 and w["obs"] < OBS_ATOL, w
+
+
+@pytest.mark.parametrize("ignore_obstacles,obstacles_f32", [(False, False), (False, True), (True, False)])
+def test_vec_env_lockstep_vs_oracle_with_autoreset(usv, ignore_obstacles, obstacles_f32):
+    """N envs, in-kernel Philox reset on both sides, SB3 auto-reset, 400 steps: flags and episode
+    lengths exact, observations (incl. 128 sensor columns), rewards and terminal observations to tolerance."""
+    N, T, seed, off = 1536, 400, 5, 1000
+    kw = dict(ignore_obstacles=ignore_obstacles, obstacles_f32=obstacles_f32, max_episode_steps=150)
+    env = usv.UsvGpuVecEnv(N, device=0, seed=seed, global_env_offset=off, **kw)
+    ov = uo.OracleVecEnv(N, seed=seed, global_offset=off, **kw)
+    o_gpu = env.reset_tensor().cpu().numpy()
+    o_cpu = ov.reset()
+    np.testing.assert_allclose(o_gpu[:, :15], o_cpu[:, :15], rtol=0, atol=OBS_ATOL)
+    rng = np.random.default_rng(17)
+    ep_len_gpu, ep_len_cpu = np.zeros(N, int), np.zeros(N, int)
+    lens_gpu, lens_cpu = [], []
+    ndone = 0
+    for t in range(T):
+        a = rng.uniform([0.2, -1], [1, 1], (N, 2)).astype(np.float32)
+        og, rg, tg, ug = [x.cpu().numpy() for x in env.step_tensor(torch.tensor(a, device=env.device))]
+        oc, rc, tc, uc = ov.step(a)
+        assert np.array_equal(tg, tc), (t, np.flatnonzero(tg != tc))
+        assert np.array_equal(ug, uc), (t, np.flatnonzero(ug != uc))
+        np.testing.assert_allclose(og, oc, rtol=0, atol=OBS_ATOL, err_msg=f"obs step {t}")
+        np.testing.assert_allclose(rg, rc, rtol=0, atol=2e-5, err_msg=f"reward step {t}")  # float32 reward out
+        d = (tc | uc).astype(bool)
+        ep_len_gpu += 1
+        ep_len_cpu += 1
+        if d.any():
+            ndone += int(d.sum())
+            tob = env.terminal_obs.cpu().numpy()
+            np.testing.assert_allclose(tob[d], ov.terminal_obs[d], rtol=0, atol=OBS_ATOL)
+            lens_gpu += list(ep_len_gpu[d])
+            lens_cpu += list(ep_len_cpu[d])
+            ep_len_gpu[d] = 0
+            ep_len_cpu[d] = 0
+    assert ndone > N  # every env finished at least once on average
+    assert lens_gpu == lens_cpu
+    st = env.get_state()
+    want = oracle_to_gpu_state(ov.envs, np.float32 if obstacles_f32 else np.float64)
+    assert np.array_equal(st["steps"], want["steps"]) and np.array_equal(st["episode"], want["episode"])
+    assert np.array_equal(st["n_obs"], want["n_obs"])
+    np.testing.assert_allclose(st["dyn"][:6], want["dyn"][:6], rtol=0, atol=POSE_ATOL)
+    np.testing.assert_allclose(st["epi"], want["epi"], rtol=1e-13, atol=1e-13)
+    k = np.arange(32)[:, None] < want["n_obs"][None]
+    for f in range(3):
+        np.testing.assert_allclose(st["obstacles"][:, f][k], want["obstacles"][:, f][k], rtol=1e-13 if not obstacles_f32 else 1e-6)
+    # device-side episode statistics agree with the flag stream
+    s = env.episode_stats()
+    assert s["episodes"] == ndone and s["nonfinite"] == 0 and s["env_steps"] == N * T
+    assert abs(s["length_sum"] - float(np.sum(lens_cpu))) < 0.5
+    env.close()
+
+
+def test_do_perturb_and_skip_kinematic_vs_oracle(usv):
+    N, T = 512, 120
+    for kw in (dict(do_perturb=True), dict(skip_kinematic=True), dict(do_perturb=True, skip_kinematic=True)):
+        env = usv.UsvGpuVecEnv(N, device=0, seed=9, **kw)
+        ov = uo.OracleVecEnv(N, seed=9, **kw)
+        env.reset_tensor()
+        ov.reset()
+        rng = np.random.default_rng(2)
+        for t in range(T):
+            a = rng.uniform([0.2, -1], [1, 1], (N, 2)).astype(np.float32)
+            og, rg, tg, ug = [x.cpu().numpy() for x in env.step_tensor(torch.tensor(a, device=env.device))]
+            oc, rc, tc, uc = ov.step(a)
+            assert np.array_equal(tg, tc) and np.array_equal(ug, uc), (kw, t)
+            np.testing.assert_allclose(og, oc, rtol=0, atol=OBS_ATOL, err_msg=f"{kw} obs step {t}")
+            np.testing.assert_allclose(rg, rc, rtol=0, atol=2e-5)
+        env.close()
+
+
+# ------------------------------------------------------------------------------------------
+# full-size, size-independent properties (BASELINE.json configs 2-4)
+# ------------------------------------------------------------------------------------------
+def test_sharding_invariance_and_determinism_full_size(usv):
+    """65 536 envs (config 3).  (i) two runs are bit-identical; (ii) a shard [off, off+n) of the job
+    reproduces exactly those rows of the whole job (Philox keyed by global env id): this is what
+    makes the 2/4/8-GPU split of config 4 trajectory-preserving; (iii) observation invariants."""
+    N, T = 65536, 60
+    dev = torch.device("cuda", 0)
+    gen = torch.Generator(device=dev).manual_seed(1)
+    acts = torch.rand((T, N, 2), generator=gen, device=dev) * torch.tensor([0.8, 2.0], device=dev) + \
+        torch.tensor([0.2, -1.0], device=dev)
+
+    def run(n, off, a):
+        env = usv.UsvGpuVecEnv(n, device=0, seed=3, global_env_offset=off, max_episode_steps=25)
+        env.reset_tensor()
+        outs = []
+        for t in range(T):
+            o, r, te, tr = env.step_tensor(a[t].contiguous())
+            outs.append((o.clone(), r.clone(), te.clone(), tr.clone()))
+        s = env.episode_stats()
+        env.close()
+        return outs, s
+
+    full, s_full = run(N, 0, acts)
+    again, _ = run(N, 0, acts)
+    for a, b in zip(full, again):
+        for x, y in zip(a, b):
+            assert torch.equal(x, y)
+    lo, n = 40000, 8192 + 3  # ragged shard (not a multiple of the CTA size)
+    part, _ = run(n, lo, acts[:, lo:lo + n])
+    for a, b in zip(full, part):
+        for x, y in zip(a, b):
+            assert torch.equal(x[lo:lo + n], y)
+    o, r, te, tr = full[-1]
+    assert torch.isfinite(o).all() and torch.isfinite(r).all()
+    sens = o[:, 15:]
+    assert float(sens.max()) <= 1.0 and float(sens.min()) > -0.02  # readings in (-r_max, 100] / 100
+    assert torch.all(o[:, 13] == 0) and torch.all(o[:, 10] == 0) and torch.all(o[:, 7:9] == 0)
+    assert torch.allclose(o[:, 12], torch.tensor(0.175, device=dev)) and torch.allclose(o[:, 14], torch.tensor(0.3, device=dev))
+    assert s_full["env_steps"] == N * T and s_full["episodes"] >= N * (T // 25) and s_full["nonfinite"] == 0
+
+
+def test_ragged_and_tiny_batches(usv):
+    for n in (1, 3, 127, 129, 1000):
+        env = usv.UsvGpuVecEnv(n, device=0, seed=1)
+        ov = uo.OracleVecEnv(n, seed=1)
+        env.reset_tensor()
+        ov.reset()
+        a = action_stream(n, seed=n)
+        for _ in range(5):
+            og, rg, tg, ug = [x.cpu().numpy() for x in env.step_tensor(torch.tensor(a, device=env.device))]
+            oc, rc, tc, uc = ov.step(a)
+            assert np.array_equal(tg, tc) and np.array_equal(ug, uc)
+            np.testing.assert_allclose(og, oc, rtol=0, atol=OBS_ATOL)
+        env.close()
+
+
+# ------------------------------------------------------------------------------------------
+# the SB3 VecEnv face
+# ------------------------------------------------------------------------------------------
+def test_vecenv_host_face_sb3_semantics(usv):
+    N = 64
+    env = usv.UsvGpuVecEnv(N, device=0, seed=4, max_episode_steps=7)
+    assert env.observation_space.shape == (143,) and env.action_space.shape == (2,)
+    obs = env.reset()
+    assert isinstance(obs, np.ndarray) and obs.shape == (N, 143) and obs.dtype == np.float32
+    seen_done = 0
+    for t in range(15):
+        a = np.stack([env.action_space.sample() for _ in range(N)])
+        obs, rew, dones, infos = env.step(a)
+        assert obs.shape == (N, 143) and rew.shape == (N,) and dones.dtype == bool and len(infos) == N
+        for i in np.flatnonzero(dones):
+            seen_done += 1
+            assert infos[i]["terminal_observation"].shape == (143,)
+            assert infos[i]["episode"]["l"] <= 7
+            if infos[i]["episode"]["l"] == 7:
+                assert infos[i]["TimeLimit.truncated"] in (True, False)
+        if t == 6:
+            assert dones.all()  # TimeLimit at 7 steps (or earlier termination + 7 more is impossible)
+    assert seen_done >= 2 * N - 5
+    assert env.env_is_wrapped(object) == [False] * N
+    assert len(env.get_attr("position")) == N
+    env.close()
+
+
+def test_rollout_entry_matches_step_loop(usv):
+    N, K = 4096, 12
+    dev = torch.device("cuda", 0)
+    acts = torch.tensor(np.stack([action_stream(N, seed=s) for s in range(K)]), device=dev)
+    e1 = usv.UsvGpuVecEnv(N, device=0, seed=2)
+    e2 = usv.UsvGpuVecEnv(N, device=0, seed=2)
+    e1.reset_tensor()
+    e2.reset_tensor()
+    for k in range(K):
+        e1.step_tensor(acts[k])
+    e2.rollout_tensor(acts, K)
+    assert torch.equal(e1.obs, e2.obs) and torch.equal(e1.reward, e2.reward)
+    s1, s2 = e1.get_state(), e2.get_state()
+    for k in s1:
+        assert np.array_equal(s1[k], s2[k]), k
+    e1.close()
+    e2.close()
+
+
+def test_errors_are_loud(usv):
+    with pytest.raises(usv.UsvError):
+        usv.UsvGpuVecEnv(0, device=0)
+    env = usv.UsvGpuVecEnv(8, device=0)
+    with pytest.raises(ValueError):
+        env.step_tensor(torch.zeros((7, 2), device=env.device))
+    with pytest.raises(usv.UsvError):
+        usv.asmc_compute(torch.zeros((23, 4), dtype=torch.float64), torch.zeros((4, 2), dtype=torch.float64))
+    env.close()

@@ -1,0 +1,201 @@
+"""Pins the CPU oracle (oracle/usv_oracle.c) against golden vectors produced by running the
+UNMODIFIED reference in the build container (oracle/gen_golden.py -> tests/golden/).
+
+CPU only (-m "not gpu").  Tolerances are written next to each comparison; the reference runs
+numpy float64 and so does the oracle, so they are a few ulp on pose/velocity and exact on flags.
+"""
+import numpy as np
+import pytest
+
+import usv_oracle as uo
+from _helpers import golden_reset_maps, inject_oracle, load_golden
+
+
+# ------------------------------------------------------------------------------------------
+# UsvAsmc.compute (gym_usv/control/usv_asmc.py:53-244)
+# ------------------------------------------------------------------------------------------
+def test_asmc_anchor_from_survey():
+    """SURVEY 8a anchor: zero state, action [1.0, 0.5], values printed by the reference."""
+    g = load_golden("asmc_compute.npz")
+    o = uo.OracleAsmc(1)
+    for c in range(3):
+        info = o.compute_one(0, g["anchor_action"])
+        got = np.hstack([o.s["eta"][0], o.s["nu"][0], info[2], info[3]])
+        np.testing.assert_allclose(got, g["anchor"][c], rtol=1e-12, atol=1e-15)
+    # the literal digits recorded in SURVEY.md section 8a
+    np.testing.assert_allclose(g["anchor"][0][:3], [1.02730953e-04, -4.75419754e-05, 1.92467344e-03], rtol=1e-8)
+    np.testing.assert_allclose(g["anchor"][0][6:], [5.123241689555302, -5.440173994602346], rtol=1e-14)
+
+
+def test_asmc_fixed_actions_match_reference_checkpoints():
+    """The three actions of the reference's tests/test_usv_asmc.py at 1,3,10,100,500,1000 calls."""
+    g = load_golden("asmc_compute.npz")
+    for k, act in enumerate(g["fixed_actions"]):
+        o = uo.OracleAsmc(1)
+        done = 0
+        for j, c in enumerate(g["fixed_checkpoints"]):
+            o.compute(act, n_calls=int(c) - done)
+            done = int(c)
+            if k == 2 and c > 500:
+                # action [0, 10] (u_d = 0, 10 rad heading offset, far outside the action box): the boat sits
+                # at ~zero speed where beta = asin(v / (0.001 + hypot(u, v))) (usv_asmc.py:72) is
+                # ill-conditioned, and ulp-level libm differences are amplified by the sign() switches after
+                # ~600 calls.  The reference's own test only asserts psi > 5 (tests/test_usv_asmc.py:37).
+                np.testing.assert_allclose(o.s["eta"][0], g["fixed_pos"][k, j], rtol=0, atol=0.05)
+                np.testing.assert_allclose(o.s["nu"][0], g["fixed_vel"][k, j], rtol=0, atol=0.5)
+                continue
+            np.testing.assert_allclose(o.s["eta"][0], g["fixed_pos"][k, j], rtol=1e-9, atol=1e-12)
+            np.testing.assert_allclose(o.s["nu"][0], g["fixed_vel"][k, j], rtol=1e-9, atol=1e-12)
+
+
+def test_asmc_reference_behavioural_tests():
+    """reference tests/test_usv_asmc.py:8-37 (call signature fixed: do_perturb=False, [:2])."""
+    o = uo.OracleAsmc(1)
+    o.compute([0.0, 0.0], n_calls=1000)  # :8-16
+    assert np.allclose(o.s["eta"][0], 0) and np.allclose(o.s["nu"][0], 0)
+    o = uo.OracleAsmc(1)
+    o.compute([10.0, 0.0], n_calls=1000)  # :18-28
+    x, y, psi = o.s["eta"][0]
+    u, v, r = o.s["nu"][0]
+    assert x > 10 and abs(y) < 1 and abs(psi) < 1 and u > 1 and abs(v) < 1 and abs(r) < 1
+    o = uo.OracleAsmc(1)
+    o.compute([0.0, 10.0], n_calls=1000)  # :30-37
+    assert o.s["eta"][0][2] > 5
+
+
+@pytest.mark.parametrize("name,perturb", [("rand", False), ("perturb", True)])
+def test_asmc_random_action_rollout(name, perturb):
+    g = load_golden("asmc_compute.npz")
+    acts = g[f"{name}_actions"]
+    o = uo.OracleAsmc(1)
+    worst = 0.0
+    for c in range(len(acts)):
+        info = o.compute_one(0, acts[c].astype(np.float64), do_perturb=perturb)
+        # free-running closed loop with sign() switches: compare with a tolerance that grows
+        # slowly; measured worst relative error is ~1e-10 (differences are libm-vs-numpy ulps)
+        np.testing.assert_allclose(o.s["eta"][0], g[f"{name}_pos"][c], rtol=1e-7, atol=1e-9)
+        np.testing.assert_allclose(o.s["nu"][0], g[f"{name}_vel"][c], rtol=1e-7, atol=1e-9)
+        np.testing.assert_allclose(info, g[f"{name}_info"][c], rtol=1e-6, atol=1e-7)
+        worst = max(worst, float(np.max(np.abs(o.s["eta"][0] - g[f"{name}_pos"][c]))))
+    np.testing.assert_allclose(o.s["last"][0], g[f"{name}_last"], rtol=1e-6, atol=1e-8)
+    np.testing.assert_allclose(o.s["aux"][0], g[f"{name}_aux"], rtol=1e-7, atol=1e-9)
+    # so_filter = [psi_d_last, o_dot_dot_last, o_dot_last, o_last, o, o_dot, o_dot_dot]
+    np.testing.assert_allclose(o.s["so"][0], g[f"{name}_so_filter"][:4], rtol=1e-6, atol=1e-8)
+    assert o.s["perturb_step"][0] == 10 * len(acts)
+    assert worst < 1e-8
+
+
+# ------------------------------------------------------------------------------------------
+# compute_sensor_measurments (usv_asmc_ca_env.py:411-461,500-519)
+# ------------------------------------------------------------------------------------------
+def test_sensors_match_reference():
+    g = load_golden("sensors.npz")
+    hits = neg = 0
+    for i in range(len(g["S"])):
+        S, n = int(g["S"][i]), int(g["n"][i])
+        got = uo.sensors(g["pos"][i], g["rad"][i, :n], g["ox"][i, :n], g["oy"][i, :n], sensor_count=S)
+        want = g["dist"][i, :S]
+        # identical hit/miss pattern, distances to 1e-9 (the reference inverts a 2x2 rotation numerically)
+        assert np.array_equal(got < 100, want < 100), i
+        np.testing.assert_allclose(got, want, rtol=0, atol=1e-9)
+        hits += int(np.sum(want < 100))
+        neg += int(np.sum(want < 0))
+    assert hits > 500 and neg > 10  # the fixture exercises hits and boat-inside-circle readings
+
+
+# ------------------------------------------------------------------------------------------
+# UsvSimpleASMCEnv.step (simple_env_asmc.py:18-27 -> simple_env.py:310-346) + TimeLimit
+# ------------------------------------------------------------------------------------------
+def _replay(gname, ignore_obstacles):
+    g = load_golden(gname)
+    acts = g["actions"]
+    E, T = g["obs"].shape[:2]
+    rmap = golden_reset_maps(g)
+    ov = uo.OracleVecEnv(E, ignore_obstacles=ignore_obstacles, auto_reset=False, max_episode_steps=1000)
+    for e in range(E):
+        inject_oracle(ov.envs, e, g, rmap[e][0])
+    # reset observation: header from the state, sensors stale (zeros on the very first reset)
+    for e in range(E):
+        ob = np.zeros(uo.OBS_DIM, np.float32)
+        uo.lib().usv_oracle_simple_reset_obs(ov.envs[e:e + 1].ctypes.data, ob.ctypes.data)
+        np.testing.assert_allclose(ob, g["reset_obs"][rmap[e][0]], rtol=0, atol=1e-6)
+    stats = dict(pos=0.0, vel=0.0, rew=0.0, obs=0.0, done=0)
+    for t in range(T):
+        a = np.repeat(acts[t][None], E, 0)
+        obs, rew, term, trunc = ov.step(a)
+        # exact flags
+        assert np.array_equal(term, g["terminated"][:, t]), t
+        assert np.array_equal(trunc, g["truncated"][:, t]), t
+        pos = ov.envs["asmc"]["eta"]
+        vel = ov.envs["asmc"]["nu"]
+        stats["pos"] = max(stats["pos"], float(np.max(np.abs(pos - g["pos"][:, t]))))
+        stats["vel"] = max(stats["vel"], float(np.max(np.abs(vel - g["vel"][:, t]))))
+        stats["rew"] = max(stats["rew"], float(np.max(np.abs(rew - g["reward"][:, t]))))
+        stats["obs"] = max(stats["obs"], float(np.max(np.abs(obs - g["obs"][:, t]))))
+        np.testing.assert_allclose(ov.envs["progress"], g["progress"][:, t], rtol=0, atol=1e-9)
+        for e in np.flatnonzero(term | trunc):
+            stats["done"] += 1
+            k = rmap[int(e)][t + 1]
+            inject_oracle(ov.envs, int(e), g, k)  # reference's next reset state (PCG64 stream is not replicated)
+            ob = np.zeros(uo.OBS_DIM, np.float32)
+            uo.lib().usv_oracle_simple_reset_obs(ov.envs[e:e + 1].ctypes.data, ob.ctypes.data)
+            np.testing.assert_allclose(ob, g["reset_obs"][k], rtol=0, atol=1e-6)
+    return stats
+
+
+def test_simple_asmc_env_with_obstacles_1000_steps():
+    s = _replay("simple_asmc_env.npz", ignore_obstacles=False)
+    assert s["done"] >= 8
+    # float64 vs float64: pose/velocity to 1e-9 m, reward to 1e-9, float32 observations to 1 ulp-ish
+    assert s["pos"] < 1e-9 and s["vel"] < 1e-9 and s["rew"] < 1e-9 and s["obs"] < 1e-6, s
+
+
+def test_simple_asmc_env_ignore_obstacles_1000_steps():
+    s = _replay("simple_asmc_env_noobs.npz", ignore_obstacles=True)
+    assert s["pos"] < 1e-9 and s["vel"] < 1e-9 and s["rew"] < 1e-9 and s["obs"] < 1e-6, s
+
+
+# ------------------------------------------------------------------------------------------
+# reset distributions (simple_env.py:228-308): Philox stream vs the reference's PCG64 samples
+# ------------------------------------------------------------------------------------------
+def test_reset_distributions_match_reference_samples():
+    from scipy import stats as st
+    g = load_golden("reset_samples.npz")
+    n = 4000
+    ov = uo.OracleVecEnv(n, seed=123)
+    ov.reset()
+    e = ov.envs
+
+    def ks(a, b):
+        return st.ks_2samp(np.asarray(a).ravel(), np.asarray(b).ravel()).pvalue
+
+    assert ks(e["asmc"]["eta"][:, 0], g["position"][:, 0]) > 1e-3
+    assert ks(e["asmc"]["eta"][:, 1], g["position"][:, 1]) > 1e-3
+    assert ks(e["asmc"]["eta"][:, 2], g["position"][:, 2]) > 1e-3
+    assert ks(e["asmc"]["nu"], g["velocity"]) > 1e-3
+    assert ks(e["max_action"][:, 0], g["max_action"][:, 0]) > 1e-3
+    assert ks(e["max_action"][:, 2], g["max_action"][:, 2]) > 1e-3
+    assert np.all(e["max_action"][:, 1] == 0) and np.all(g["max_action"][:, 1] == 0)
+    assert ks(e["v_ref"], g["v_ref"]) > 1e-3
+    assert ks(e["n_obs"], g["n_obs"]) > 1e-3
+    assert ks(np.hypot(*(e["path_end"] - e["path_start"]).T), np.hypot(*(g["path_end"] - g["path_start"]).T)) > 1e-3
+    assert ks(e["target"], g["target"]) > 1e-3
+    assert e["n_obs"].min() >= 1 and e["n_obs"].max() <= 29
+    # path_start == position[:2] (simple_env.py:238)
+    assert np.array_equal(e["asmc"]["eta"][:, :2], e["path_start"])
+    # rejection rule: no kept obstacle centre within 0.5 of position or target (simple_env.py:261-268)
+    for i in range(200):
+        k = int(e["n_obs"][i])
+        dp = np.hypot(e["obs_x"][i, :k] - e["asmc"]["eta"][i, 0], e["obs_y"][i, :k] - e["asmc"]["eta"][i, 1])
+        dt = np.hypot(e["obs_x"][i, :k] - e["target"][i, 0], e["obs_y"][i, :k] - e["target"][i, 1])
+        assert np.all(dp >= 0.5) and np.all(dt >= 0.5)
+        assert np.all((e["obs_r"][i, :k] >= 0.15) & (e["obs_r"][i, :k] <= 0.5))
+
+
+def test_philox_known_answer():
+    """Philox4x32-10 known-answer vectors from the Random123 distribution (kat_vectors)."""
+    # counter = 0, key = 0
+    assert [hex(x) for x in uo.philox(0, 0, 0, 0)] == ["0x6627e8d5", "0xe169c58d", "0xbc57ac4c", "0x9b00dbd8"]
+    # counter = ffffffff x4, key = ffffffff x2
+    out = uo.philox(0xFFFFFFFFFFFFFFFF, 0xFFFFFFFFFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF)
+    assert [hex(x) for x in out] == ["0x408f276d", "0x41c83b0e", "0xa20bc7c6", "0x6d5451fd"]
