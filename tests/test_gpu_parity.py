@@ -63,8 +63,10 @@ def test_asmc_compute_golden_anchor_and_fixed_actions(usv):
             if k == 2 and c > 500:  # ill-conditioned zero-speed case, see tests/test_oracle_golden.py
                 np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=0, atol=0.05)
                 continue
-            np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=1e-9, atol=1e-11)
-            np.testing.assert_allclose(h[3:6, 0], g["fixed_vel"][k, j], rtol=1e-9, atol=1e-11)
+            # y, psi, v, r stay ~1e-11 for these actions and beta = asin(v / (0.001 + speed)) amplifies their ulps
+            # (measured on B200: |dv|, |dr| up to 8e-9 around values of 1e-10 .. 1e-8); the module tolerance applies
+            np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=1e-9, atol=POSE_ATOL)
+            np.testing.assert_allclose(h[3:6, 0], g["fixed_vel"][k, j], rtol=1e-9, atol=POSE_ATOL)
         x, y, psi, u, v, r = h[:6, 0]
         if k == 0:
             assert np.allclose(h[:6], 0)
