@@ -5,9 +5,9 @@
     python bench.py --impl reference [...]                        # the reference's CPU algorithm (oracle port)
     torchrun --nproc-per-node N ... bench.py --gpus N ...         # one rank per GPU, envs sharded by index range
 
-A "step" is one VecEnv.step() over one batch of envs on every rank (one kernel launch per rank: 20
-ASMC + 3-DOF sub-steps, kinematic post-step, closest point, 128-ray sensor pass, reward, flags, in-kernel
-auto-reset, observation rows).  Workload: BASELINE.json configs[2] -- 65 536 envs per GPU with randomised
+A "step" is one VecEnv.step() over one batch of envs on every rank (two kernel launches per rank:
+dynamics_kernel = 20 ASMC + 3-DOF sub-steps, kinematic post-step, closest point, header, partial reward;
+sensor_kernel = 128-ray sensor pass, flags, reward, in-kernel auto-reset, observation rows).  Workload: BASELINE.json configs[2] -- 65 536 envs per GPU with randomised
 obstacles and range-sensor observations (weak scaling: 8 GPUs = 524 288 envs; --envs-per-gpu 131072 gives
 the 1 M-env configs[3]).  The timed loop rotates over --batches independent env batches so that the state a
 step reads was evicted from the 126 MB L2 by the other batches' steps (working set > L2).
@@ -46,6 +46,19 @@ def algorithmic_bytes(obstacles: bool, obstacles_f32: bool) -> int:
         rd += 32 * 3 * (4 if obstacles_f32 else 8)
     wr = 23 * 8 + 4 + 8 + 143 * 4 + 4 + 2
     return rd + wr
+
+
+# Per-kernel share of those bytes plus the 61 B hand-over block each side moves (cos/sin of the heading 16,
+# partial reward 8, 9 float32 header columns 36, flag byte 1): DESIGN.md "Kernels".
+HANDOVER = 16 + 8 + 36 + 1
+
+
+def kernel_bytes(obstacles: bool, obstacles_f32: bool) -> dict:
+    dyn = (23 * 8 + 7 * 8 + 4 + 2 * 4) + (23 * 8 + 4) + HANDOVER
+    sens = (2 * 8 + 4 + 8 + HANDOVER) + (143 * 4 + 4 + 2 + 8)
+    if obstacles:
+        sens += 32 * 3 * (4 if obstacles_f32 else 8)
+    return {"usv::dynamics_kernel": dyn, "usv::sensor_kernel": sens}
 
 
 def measured_peaks():
@@ -303,6 +316,14 @@ def run_ours(args, rank, local_rank, world):
     h2d = n * 2 * 4
     d2h = n * (143 * 4 + 4 + 1 + 1)
 
+    # ---- per-kernel device time (CUDA events inside the library, on the launching stream) --------------
+    kms = [0.0, 0.0]
+    ksteps = max(3, min(args.steps, 60))
+    for k in range(ksteps):
+        d_ms, s_ms = envs[k % len(envs)].step_tensor_timed(acts[k % A])
+        kms[0] += d_ms / ksteps
+        kms[1] += s_ms / ksteps
+
     stats = envs[0].episode_stats()
     for e in envs[1:]:
         s = e.episode_stats()
@@ -312,8 +333,12 @@ def run_ours(args, rank, local_rank, world):
     if rank == 0:
         peak, peak_src = measured_peaks()
         abytes = algorithmic_bytes(not args.no_obstacles, bool(args.obstacles_f32))
-        launch_s = (ms * 1e-3) / args.steps  # rank-0 launch duration (one kernel per step)
-        achieved = abytes * n / launch_s / 1e9
+        step_s = (ms * 1e-3) / args.steps  # rank-0 device time per step (two kernels)
+        kb = kernel_bytes(not args.no_obstacles, bool(args.obstacles_f32))
+        knames = list(kb)
+        dom = 0 if kms[0] >= kms[1] else 1
+        dom_s = kms[dom] * 1e-3
+        achieved = kb[knames[dom]] * n / dom_s / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -322,11 +347,15 @@ def run_ours(args, rank, local_rank, world):
             "sub_steps_per_sec": value * 20,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "api": "UsvGpuVecEnv.step(np.ndarray) -> np.ndarray obs/rew/dones + lazy infos"},
-            "gpu_launches": args.steps,
+            "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_env_step": abytes,
-                         "kernel": "usv::step_kernel", "launch_us": launch_s * 1e6,
-                         "note": "the kernel is FP64-issue bound, not HBM bound: see DESIGN.md and profiles/"},
+                         "traffic": None, "peak_source": peak_src, "kernel": knames[dom],
+                         "algorithmic_bytes_per_env_step": kb[knames[dom]], "launch_us": dom_s * 1e6,
+                         "kernels_us": {knames[0]: kms[0] * 1e3, knames[1]: kms[1] * 1e3},
+                         "kernels_bytes_per_env_step": kb,
+                         "whole_step": {"algorithmic_bytes_per_env_step": abytes, "us": step_s * 1e6,
+                                        "achieved": abytes * n / step_s / 1e9, "frac": abytes * n / step_s / 1e9 / peak},
+                         "note": "both kernels are float64-issue bound, not HBM bound: see DESIGN.md and profiles/"},
             "clocks": clocks,
             "host_wall_s": t_wall,
             "episode_stats": stats,

@@ -15,8 +15,9 @@ _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
-HEADERS = [os.path.join(CSRC, "usv_model.cuh"), os.path.join(CSRC, "usv_philox.cuh"),
-           os.path.join(_ROOT, "include", "usvgpu.h")]
+HEADERS = [os.path.join(CSRC, f) for f in ("usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
+                                             "usv_sensor.cuh", "usv_kernels.cuh")] + \
+          [os.path.join(_ROOT, "include", "usvgpu.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
               "-Xcompiler", "-fPIC"]
@@ -93,6 +94,7 @@ _SIGNATURES = {
     "usvgpu_destroy": (C.c_int, [C.c_void_p]),
     "usvgpu_reset": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_step": (C.c_int, [C.c_void_p] * 8),
+    "usvgpu_step_timed": (C.c_int, [C.c_void_p] * 9),
     "usvgpu_rollout": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p]),
     "usvgpu_field_bytes": (C.c_int64, [C.c_void_p, C.c_int32]),

@@ -1,0 +1,338 @@
+// usv_kernels.cuh -- the two kernels of one VecEnv.step() and the unit-parity kernels.
+//
+//   dynamics_kernel  one THREAD per env.  The 20 ASMC + 3-DOF sub-steps of UsvSimpleASMCEnv.step
+//                    (simple_env_asmc.py:18-27) run register-resident (usv_model.cuh), then the
+//                    kinematic post-step, closest point / cross-track maths, the env-dependent
+//                    observation header and the reward terms that do not need the sensors
+//                    (simple_env.py:310-346).  Every state field is a coalesced SoA column.
+//   sensor_kernel    one WARP per env.  Range-sensor pass (usv_sensor.cuh), termination and
+//                    collision tests, the [N][143] observation row (coalesced 128 B stores),
+//                    reward / flags, episode statistics and the SB3 auto-reset (usv_reset.cuh).
+// The split exists because the two halves want opposite shapes: the dynamics are one long serial
+// float64 chain per env (few fat threads), the sensor pass is 30 obstacles x 128 rays of short
+// independent tests (many thin threads).  The hand-over (heading cos/sin, header, partial reward,
+// flags: 61 B per env) is written and re-read through L2 within one launch pair.
+#pragma once
+#include "usv_reset.cuh"
+#include "usv_sensor.cuh"
+
+namespace usv {
+
+constexpr int DYN_B = 64;        // threads (= envs) per CTA of the dynamics kernel
+constexpr int SENS_WARPS = 8;    // warps (= envs) per CTA of the sensor kernel
+
+// ---------------------------------------------------------------------------------------------
+template <bool PERTURB>
+__global__ void __launch_bounds__(DYN_B)
+dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
+    const long long n = s.n;
+    const long long i = (long long)blockIdx.x * DYN_B + threadIdx.x;
+    if (i >= n) return;
+
+    // ---- load state (coalesced SoA columns) -------------------------------------------------
+    double* dyn = s.dyn + i;
+    Pose p;
+    Ctrl c;
+    p.x = dyn[(long long)D_X * n];
+    p.y = dyn[(long long)D_Y * n];
+    p.psi = dyn[(long long)D_PSI * n];
+    p.u = dyn[(long long)D_U * n];
+    p.v = dyn[(long long)D_V * n];
+    p.r = dyn[(long long)D_R * n];
+    c.xd_l = dyn[(long long)D_XD_L * n];
+    c.yd_l = dyn[(long long)D_YD_L * n];
+    c.psid_l = dyn[(long long)D_PSID_L * n];
+    c.ud_l = dyn[(long long)D_UD_L * n];
+    c.vd_l = dyn[(long long)D_VD_L * n];
+    c.rd_l = dyn[(long long)D_RD_L * n];
+    c.eu_l = dyn[(long long)D_EU_L * n];
+    c.kadu_l = dyn[(long long)D_KADU_L * n];
+    c.kadp_l = dyn[(long long)D_KADP_L * n];
+    c.psi_d_l = dyn[(long long)D_PSI_D_L * n];
+    c.odd_l = dyn[(long long)D_ODD_L * n];
+    c.od_l = dyn[(long long)D_OD_L * n];
+    c.o_l = dyn[(long long)D_O_L * n];
+    c.eu_int = dyn[(long long)D_EU_INT * n];
+    c.ka_u = dyn[(long long)D_KA_U * n];
+    c.ka_psi = dyn[(long long)D_KA_PSI * n];
+    double progress = dyn[(long long)D_PROGRESS * n];
+    const double* epi = s.epi + i;
+    const double psx = epi[(long long)E_PSX * n], psy = epi[(long long)E_PSY * n];
+    const double pex = epi[(long long)E_PEX * n], pey = epi[(long long)E_PEY * n];
+    const double ma0 = epi[(long long)E_MA0 * n], ma2 = epi[(long long)E_MA2 * n];
+    const double vref = epi[(long long)E_VREF * n];
+    int steps = s.steps[i];
+    const float2 af = reinterpret_cast<const float2*>(actions)[i];
+    const double a0 = (double)af.x, a1 = (double)af.y;
+
+    // ---- 2 x UsvAsmc.compute = 20 sub-steps (simple_env_asmc.py:19-25) -----------------------
+    const long long pstep0 = (long long)steps * 20;
+    for (int k = 0; k < 20; ++k) {
+        double sn, cs;
+        sincos(p.psi, &sn, &cs);
+        asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
+    }
+
+    // ---- UsvSimpleEnv.step(zeros(2)): kinematic post-step, simple_env.py:311-324 -------------
+    // action = 0.8*last_action + 0.2*(max_action*0) and last_action is 0 for the whole life of
+    // this env, so the commanded velocity is 0.
+    double sn, cs;
+    if (!fl.skip_kinematic) {
+        const double du = np_clip(0.0 - p.u, -MAX_ACC_U, MAX_ACC_U);
+        p.u = np_clip(p.u + du, -ma0, ma0);
+        p.v = 0.0;  // clip(v + clip(-v, -0, 0), -0, 0): max_acceleration[1] = max_action[1] = 0
+        const double dr = np_clip(0.0 - p.r, -MAX_ACC_R, MAX_ACC_R);
+        p.r = np_clip(p.r + dr, -ma2, ma2);
+        if (p.u != 0.0) {
+            sincos(p.psi, &sn, &cs);
+            p.x = p.x + (p.u * cs) * DT;
+            p.y = p.y + (p.u * sn) * DT;
+        }
+        p.psi = p.psi + p.r * DT;
+    }
+    sincos(p.psi, &sn, &cs);  // heading of the pose the sensors see (usv_asmc_ca_env.py:420-424)
+
+    // ---- closest point on the path, simple_env.py:139-148 ------------------------------------
+    const double pdx = pex - psx, pdy = pey - psy;
+    const double det = pdx * pdx + pdy * pdy;
+    double a = (pdy * (p.y - psy) + pdx * (p.x - psx)) / det;
+    a += (0.005 / 10) * ENV_HI;
+    a = np_clip(a, progress, 1.0);
+    const double tgx = psx + a * pdx, tgy = psy + a * pdy;
+    progress = a;
+
+    // ---- truncation, simple_env.py:336 + TimeLimit (gym_usv/__init__.py:33) ------------------
+    const bool oob = (p.x > ENV_HI) || (p.y > ENV_HI) || (p.x < 0.0) || (p.y < 0.0);
+    steps += 1;
+    const bool tlimit = (fl.max_episode_steps > 0) && (steps >= fl.max_episode_steps);
+
+    // ---- observation header, simple_env.py:72-96 ---------------------------------------------
+    const double inv_len = rsqrt(det);
+    const double ye = -(p.x - psx) * (pdy * inv_len) + (p.y - psy) * (pdx * inv_len);  // :133-137
+    const double ang = wrap_pi(atan2(tgy - p.y, tgx - p.x) - p.psi);                  // :67-69
+    const double tdx = p.x - tgx, tdy = p.y - tgy;
+    const double tdist = sqrt(fma(tdx, tdx, tdy * tdy));
+    float* hdr = s.hdr + i;
+    hdr[(long long)H_U * n] = (float)(p.u / 10);
+    hdr[(long long)H_V * n] = (float)(p.v / 10);
+    hdr[(long long)H_R * n] = (float)(p.r / 10);
+    hdr[(long long)H_ANG * n] = (float)(ang / PI);
+    hdr[(long long)H_DIST * n] = (float)(tdist / DIST_NORM);
+    hdr[(long long)H_YE * n] = (float)(ye / 10);
+    hdr[(long long)H_VREF * n] = (float)(vref / 10);
+    hdr[(long long)H_MA0 * n] = (float)(ma0 / 10);
+    hdr[(long long)H_MA2 * n] = (float)(ma2 / 10);
+
+    // ---- reward without the collision term, simple_env.py:150-201 ----------------------------
+    const double t = ye / 0.075;
+    const double at = fabs(t);
+    const double ye_reward = exp(-fmin(at, t * t));  // max(exp(-|t|), exp(-t^2)): exp is monotone
+    const double angle_reward = exp(-fabs(ang));
+    const double vel_reward = exp(-fabs(sqrt(fma(p.u, p.u, p.v * p.v)) - vref)) * 0.05;
+    s.rew_part[i] = ye_reward + angle_reward + vel_reward;  // delta_action_reward = -0, arrived = 0
+    s.cs[i] = cs;
+    s.cs[n + i] = sn;
+    s.flags[i] = (uint8_t)((oob ? FLG_OOB : 0u) | (tlimit ? FLG_TLIMIT : 0u));
+    if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.psi))) atomicAdd(&s.stats->nonfinite, 1ull);
+
+    // ---- store state ---------------------------------------------------------------------------
+    dyn[(long long)D_X * n] = p.x;
+    dyn[(long long)D_Y * n] = p.y;
+    dyn[(long long)D_PSI * n] = p.psi;
+    dyn[(long long)D_U * n] = p.u;
+    dyn[(long long)D_V * n] = p.v;
+    dyn[(long long)D_R * n] = p.r;
+    dyn[(long long)D_XD_L * n] = c.xd_l;
+    dyn[(long long)D_YD_L * n] = c.yd_l;
+    dyn[(long long)D_PSID_L * n] = c.psid_l;
+    dyn[(long long)D_UD_L * n] = c.ud_l;
+    dyn[(long long)D_VD_L * n] = c.vd_l;
+    dyn[(long long)D_RD_L * n] = c.rd_l;
+    dyn[(long long)D_EU_L * n] = c.eu_l;
+    dyn[(long long)D_KADU_L * n] = c.kadu_l;
+    dyn[(long long)D_KADP_L * n] = c.kadp_l;
+    dyn[(long long)D_PSI_D_L * n] = c.psi_d_l;
+    dyn[(long long)D_ODD_L * n] = c.odd_l;
+    dyn[(long long)D_OD_L * n] = c.od_l;
+    dyn[(long long)D_O_L * n] = c.o_l;
+    dyn[(long long)D_EU_INT * n] = c.eu_int;
+    dyn[(long long)D_KA_U * n] = c.ka_u;
+    dyn[(long long)D_KA_PSI * n] = c.ka_psi;
+    dyn[(long long)D_PROGRESS * n] = progress;
+    s.steps[i] = steps;
+}
+
+// ---------------------------------------------------------------------------------------------
+// observation column `lane` (< 15) from the hand-over block, simple_env.py:91-96
+__device__ __forceinline__ float header_column(const StatePtrs& s, long long i, int lane) {
+    // column -> hand-over row; -1: constant
+    int row = -1;
+    float v = 0.0f;                       // columns 7, 8 (last_action), 10 (max_action[1]), 13 (max_acc[1])
+    if (lane <= 6) row = lane;            // u v r | angle dist ye v_ref
+    else if (lane == 9) row = H_MA0;
+    else if (lane == 11) row = H_MA2;
+    else if (lane == 12) v = (float)(MAX_ACC_U / 10);
+    else if (lane == 14) v = (float)(MAX_ACC_R / 10);
+    if (row >= 0) v = s.hdr[(long long)row * s.n + i];
+    return v;
+}
+
+template <bool OBST, typename ObT>
+__global__ void __launch_bounds__(SENS_WARPS * 32)
+sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restrict__ reward,
+              uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated, float* __restrict__ terminal_obs) {
+    __shared__ double2 raytab[N_SENS];
+    __shared__ SensorScratch scratch[SENS_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (OBST) {
+        if (tid < N_SENS) raytab[tid] = s.raytab[tid];
+        __syncthreads();
+    }
+    const long long n = s.n;
+    const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
+    if (i >= n) return;
+
+    // ---- sensors, simple_env.py:203-226 --------------------------------------------------------
+    float sens[4] = {1.0f, 1.0f, 1.0f, 1.0f};  // max range / 100 (simple_env.py:83); ignore_obstacles: all rays (:222-224)
+    bool term = false, collided = false;
+    if (OBST) {
+        const double x = s.dyn[(long long)D_X * n + i], y = s.dyn[(long long)D_Y * n + i];
+        const double cps = s.cs[i], sps = s.cs[n + i];
+        const int nob = s.n_obs[i];
+        const ObT* row = obst_row<ObT>(s, i);
+        double ox = 0.0, oy = 0.0, rr = 0.0;
+        if (lane < nob) {
+            ox = (double)row[lane];
+            oy = (double)row[MAX_OBST + lane];
+            rr = (double)row[2 * MAX_OBST + lane];
+        }
+        double out[4];
+        bool hit[4];
+        sensor_warp(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, out, hit, 0.05, term, 0.2, collided);
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+            if (hit[p]) sens[p] = (float)(out[p] * 0.01);
+    }
+
+    // ---- flags (simple_env.py:334-336 + TimeLimit), reward (:150-201) ---------------------------
+    const unsigned flg = s.flags[i];
+    const bool oob = flg & FLG_OOB, tlimit = flg & FLG_TLIMIT;
+    const bool trunc = oob || tlimit;
+    const bool done = term || trunc;
+    const double rew = (collided ? -20.0 : 0.0) + s.rew_part[i];
+    const double ep_ret = s.ep_return[i] + rew;
+    float head = (lane < HDR) ? header_column(s, i, lane) : 0.0f;
+    if (lane == 0) {
+        reward[i] = (float)rew;
+        terminated[i] = term ? 1 : 0;
+        truncated[i] = trunc ? 1 : 0;
+        if (done) {
+            DeviceStats* st = s.stats;
+            atomicAdd(&st->return_sum, ep_ret);
+            atomicAdd(&st->length_sum, (double)s.steps[i]);
+            atomicAdd(&st->episodes, 1ull);
+            if (term) atomicAdd(&st->terminated, 1ull);
+            if (oob) atomicAdd(&st->out_of_bounds, 1ull);
+            if (tlimit && !term && !oob) atomicAdd(&st->time_limit, 1ull);
+        }
+    }
+
+    // ---- observation row(s): 15 header columns + 128 sensor columns, contiguous in obs[N][143] ----
+    float* orow = obs + i * OBS_DIM;
+    if (done && fl.auto_reset) {
+        if (terminal_obs) {
+            float* trow = terminal_obs + i * OBS_DIM;
+            if (lane < HDR) trow[lane] = head;
+#pragma unroll
+            for (int p = 0; p < 4; ++p) trow[HDR + lane + 32 * p] = sens[p];
+        }
+        head = reset_env_warp<ObT>(s, i, lane);  // header <- reset obs; sensor columns stay (simple_env.py:302)
+    } else if (lane == 0) {
+        s.ep_return[i] = ep_ret;
+    }
+    if (lane < HDR) orow[lane] = head;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) orow[HDR + lane + 32 * p] = sens[p];
+}
+
+// ---------------------------------------------------------------------------------------------
+// stand-alone reset
+// ---------------------------------------------------------------------------------------------
+template <typename ObT>
+__global__ void reset_kernel(StatePtrs s, const uint8_t* __restrict__ mask, float* __restrict__ obs) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s.n) return;
+    if (mask && !mask[i]) return;
+    float hdr[HDR];
+    reset_env<ObT>(s, i, hdr);
+    if (obs) {
+#pragma unroll
+        for (int k = 0; k < HDR; ++k) obs[i * OBS_DIM + k] = hdr[k];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Unit-parity kernels
+// ---------------------------------------------------------------------------------------------
+template <bool PERTURB>
+__global__ void asmc_compute_kernel(long long n, double* __restrict__ state, const double* __restrict__ actions,
+                                    int n_calls, long long first_substep, double* __restrict__ info) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double* dyn = state + i;
+    Pose p;
+    Ctrl c;
+    double* pf[6] = {&p.x, &p.y, &p.psi, &p.u, &p.v, &p.r};
+    double* cf[16] = {&c.xd_l, &c.yd_l, &c.psid_l, &c.ud_l, &c.vd_l, &c.rd_l, &c.eu_l, &c.kadu_l,
+                      &c.kadp_l, &c.psi_d_l, &c.odd_l, &c.od_l, &c.o_l, &c.eu_int, &c.ka_u, &c.ka_psi};
+#pragma unroll
+    for (int k = 0; k < 6; ++k) *pf[k] = dyn[(long long)k * n];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) *cf[k] = dyn[(long long)(6 + k) * n];
+    const double a0 = actions[2 * i], a1 = actions[2 * i + 1];
+    double inf[4] = {0, 0, 0, 0};
+    long long ps = first_substep;
+    for (int k = 0; k < n_calls * 10; ++k, ++ps) {
+        double sn, cs;
+        sincos(p.psi, &sn, &cs);
+        asmc_substep<PERTURB, true>(p, c, a0, a1, cs, sn, ps, inf);
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) dyn[(long long)k * n] = *pf[k];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) dyn[(long long)(6 + k) * n] = *cf[k];
+    if (info) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) info[(long long)k * n + i] = inf[k];
+    }
+}
+
+// pose [3][n], obstacles [32][3][n] float64 (the layout of the C ABI's unit entry point), out [128][n]
+__global__ void __launch_bounds__(SENS_WARPS * 32)
+sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const double* __restrict__ pose,
+                    const double* __restrict__ obstacles, const int* __restrict__ n_obs, double* __restrict__ out) {
+    __shared__ double2 raytab[N_SENS];
+    __shared__ SensorScratch scratch[SENS_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < N_SENS) raytab[tid] = g_raytab[tid];
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
+    if (i >= n) return;
+    const double x = pose[i], y = pose[n + i], psi = pose[2 * n + i];
+    double sps, cps;
+    sincos(psi, &sps, &cps);
+    const int nob = n_obs[i];
+    double ox = 0.0, oy = 0.0, rr = 0.0;
+    if (lane < nob) {
+        ox = obstacles[((long long)lane * 3 + 0) * n + i];
+        oy = obstacles[((long long)lane * 3 + 1) * n + i];
+        rr = obstacles[((long long)lane * 3 + 2) * n + i];
+    }
+    double o[4];
+    bool hit[4], a, b;
+    sensor_warp(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, o, hit, 0.05, a, 0.2, b);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) out[(long long)(lane + 32 * p) * n + i] = o[p];
+}
+
+}  // namespace usv

@@ -61,4 +61,21 @@ struct DrawStream {
     }
 };
 
+// Random access to the same stream: draw number k of (env, episode) is half (k & 1) of Philox block
+// (k >> 1).  The warp-cooperative reset of the sensor kernel uses this so that 32 lanes produce the
+// draws of one env in parallel and still reproduce DrawStream's sequence value for value.
+struct DrawKey {
+    uint2 key;
+    uint32_t gid_lo, gid_hi, episode;
+    __device__ DrawKey(uint64_t seed, uint64_t gid, uint32_t ep)
+        : key(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32))), gid_lo((uint32_t)gid), gid_hi((uint32_t)(gid >> 32)),
+          episode(ep) {}
+    // both uniforms of one block: draws 2*b and 2*b + 1
+    __device__ __forceinline__ void pair(uint32_t b, double& first, double& second) const {
+        const uint4 o = philox4x32_10(make_uint4(gid_lo, gid_hi, episode, b), key);
+        first = u53(o.x, o.y);
+        second = u53(o.z, o.w);
+    }
+};
+
 }  // namespace usv

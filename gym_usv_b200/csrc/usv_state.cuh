@@ -1,0 +1,97 @@
+// usv_state.cuh -- device-side state layout of one shard of 'usv-asmc-simple' envs.
+//
+// Structure of arrays, env index fastest, so that the thread-per-env dynamics kernel reads and
+// writes every field fully coalesced.  The obstacle table is the exception: the sensor kernel
+// gives one WARP to an env (lane = obstacle), so a row of the table is the 3 x 32 values of one
+// env, contiguous (384 B in float32): three coalesced 128 B loads per env.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/usvgpu.h"
+#include "usv_model.cuh"
+
+namespace usv {
+
+constexpr int OBS_DIM = USVGPU_OBS_DIM;
+constexpr int N_SENS = USVGPU_SENSORS;
+constexpr int MAX_OBST = USVGPU_MAX_OBSTACLES;
+constexpr int HDR = 15;                // observation columns before the sensors (simple_env.py:91-96)
+constexpr int RAYS_FULL_CIRCLE = 192;  // 2 pi / pitch, pitch = (4 pi / 3) / 128 (simple_env.py:12-14)
+constexpr int OBST_ROW = 3 * MAX_OBST; // elements per env in the obstacle table: x[32] y[32] r[32]
+
+// rows of USV_FIELD_DYN
+enum DynRow {
+    D_X = 0, D_Y, D_PSI, D_U, D_V, D_R,
+    D_XD_L, D_YD_L, D_PSID_L, D_UD_L, D_VD_L, D_RD_L, D_EU_L, D_KADU_L, D_KADP_L,
+    D_PSI_D_L, D_ODD_L, D_OD_L, D_O_L,
+    D_EU_INT, D_KA_U, D_KA_PSI,
+    D_PROGRESS,
+    N_DYN
+};
+static_assert(N_DYN == USV_DYN_ROWS, "header/kernel row count mismatch");
+// rows of USV_FIELD_EPI
+enum EpiRow { E_PSX = 0, E_PSY, E_PEX, E_PEY, E_MA0, E_MA2, E_VREF, N_EPI };
+static_assert(N_EPI == USV_EPI_ROWS, "header/kernel row count mismatch");
+
+// rows of the float32 hand-over block the dynamics kernel leaves for the sensor kernel: the
+// env-dependent observation header columns (simple_env.py:91-96) already divided and rounded
+enum HdrRow { H_U = 0, H_V, H_R, H_ANG, H_DIST, H_YE, H_VREF, H_MA0, H_MA2, N_HDR };
+constexpr unsigned FLG_OOB = 1u, FLG_TLIMIT = 2u;
+
+// simple_env.py:34-35,56,13
+constexpr double MAX_ACC_U = 1.75, MAX_ACC_R = 3.0, DT = 1.0 / 25, ENV_HI = 20.0, SENSOR_MAX_RANGE = 100.0;
+constexpr double SENSOR_PITCH = ((2.0 / 3) * (2 * PI)) / N_SENS;
+constexpr float INV_PITCH_F = (float)(1.0 / SENSOR_PITCH);
+constexpr double DIST_NORM = 28.284271247461902;  // hypot(20, 20), simple_env.py:80
+
+struct DeviceStats {
+    double return_sum;
+    double length_sum;
+    unsigned long long episodes, terminated, out_of_bounds, time_limit, env_steps, nonfinite;
+};
+static_assert(sizeof(DeviceStats) == sizeof(UsvStats), "UsvStats layout");
+
+struct StatePtrs {
+    double* dyn;        // [N_DYN][n]
+    double* epi;        // [N_EPI][n]
+    void* obst;         // [n][3][32]  double or float (x[32], y[32], radius[32] per env)
+    int* n_obs;         // [n]
+    int* steps;         // [n]
+    int* episode;       // [n]
+    double* ep_return;  // [n]
+    // hand-over from the dynamics kernel to the sensor kernel (same launch pair, lives in L2)
+    double* cs;         // [2][n]  cos / sin of the post-step heading
+    double* rew_part;   // [n]     reward without the collision term
+    float* hdr;         // [N_HDR][n]
+    uint8_t* flags;     // [n]     FLG_OOB | FLG_TLIMIT
+    DeviceStats* stats;
+    const double2* raytab;  // [128] cos/sin of the ray angles relative to the bow
+    long long n;
+    long long global_offset;
+    unsigned long long seed;
+};
+
+struct StepFlags {
+    int do_perturb, skip_kinematic, max_episode_steps, auto_reset;
+};
+
+template <typename ObT>
+__device__ __forceinline__ ObT* obst_row(const StatePtrs& s, long long i) {
+    return static_cast<ObT*>(s.obst) + i * OBST_ROW;
+}
+
+// sqrt for arguments that are sums of squares / discriminants (a >= 0, far from overflow):
+// float32 reciprocal-sqrt seed + two Newton steps in float64 (<= 1 ulp), ~9 instructions instead of
+// the ~25 of the IEEE-rounded sqrt().  a == 0 gives 0.
+__device__ __forceinline__ double sqrt_pos(double a) {
+    const float af = fmaxf((float)a, 1e-30f);
+    const double r = (double)rsqrtf(af);
+    const double h = 0.5 * r;
+    double g = a * r;
+    g = fma(fma(-g, g, a), h, g);
+    g = fma(fma(-g, g, a), h, g);
+    return g;
+}
+
+}  // namespace usv

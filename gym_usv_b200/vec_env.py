@@ -139,6 +139,17 @@ class UsvGpuVecEnv:
             C.c_void_p(self.truncated.data_ptr()), C.c_void_p(self.terminal_obs.data_ptr()), self._stream()))
         return self.obs, self.reward, self.terminated, self.truncated
 
+    def step_tensor_timed(self, actions: torch.Tensor):
+        """step_tensor() that synchronises and returns (dynamics_kernel_ms, sensor_kernel_ms) measured with CUDA
+        events on the launching stream (bench.py roofline line)."""
+        assert actions.is_cuda and actions.dtype == torch.float32 and actions.is_contiguous()
+        ms = (C.c_float * 2)()
+        self._check(self._lib.usvgpu_step_timed(
+            self._h, C.c_void_p(actions.data_ptr()), C.c_void_p(self.obs.data_ptr()),
+            C.c_void_p(self.reward.data_ptr()), C.c_void_p(self.terminated.data_ptr()),
+            C.c_void_p(self.truncated.data_ptr()), C.c_void_p(self.terminal_obs.data_ptr()), self._stream(), ms))
+        return float(ms[0]), float(ms[1])
+
     def rollout_tensor(self, actions: torch.Tensor, n_steps: int, action_wrap: int = 0):
         """n_steps launches with pre-staged actions [K,N,2] (tools/profile_env.py:5-7 style loop)."""
         assert actions.is_cuda and actions.dtype == torch.float32 and actions.is_contiguous()
@@ -247,19 +258,20 @@ class UsvGpuVecEnv:
         return [None] * self.num_envs
 
     # ------------------------------------------------------------------ state access (checkpoint / parity)
-    _FIELDS = {"dyn": (nat.FIELD_DYN, np.float64, (nat.DYN_ROWS,)), "epi": (nat.FIELD_EPI, np.float64, (nat.EPI_ROWS,)),
-               "obstacles": (nat.FIELD_OBSTACLES, None, (nat.MAX_OBSTACLES, 3)),
-               "n_obs": (nat.FIELD_N_OBS, np.int32, ()), "steps": (nat.FIELD_STEPS, np.int32, ()),
-               "episode": (nat.FIELD_EPISODE, np.int32, ()), "ep_return": (nat.FIELD_EP_RETURN, np.float64, ())}
+    # name -> (field id, dtype, leading dims before N, trailing dims after N)
+    _FIELDS = {"dyn": (nat.FIELD_DYN, np.float64, (nat.DYN_ROWS,), ()), "epi": (nat.FIELD_EPI, np.float64, (nat.EPI_ROWS,), ()),
+               "obstacles": (nat.FIELD_OBSTACLES, None, (), (3, nat.MAX_OBSTACLES)),
+               "n_obs": (nat.FIELD_N_OBS, np.int32, (), ()), "steps": (nat.FIELD_STEPS, np.int32, (), ()),
+               "episode": (nat.FIELD_EPISODE, np.int32, (), ()), "ep_return": (nat.FIELD_EP_RETURN, np.float64, (), ())}
 
     def _field_array(self, name):
-        fid, dt, lead = self._FIELDS[name]
+        fid, dt, lead, trail = self._FIELDS[name]
         if dt is None:
             dt = np.float32 if self.cfg.obstacles_f32 else np.float64
-        return fid, np.zeros(lead + (self.num_envs,), dtype=dt)
+        return fid, np.zeros(lead + (self.num_envs,) + trail, dtype=dt)
 
     def get_state(self, names: Optional[Sequence[str]] = None) -> dict:
-        """Host copies of the SoA field groups ([rows][N]); see include/usvgpu.h UsvField."""
+        """Host copies of the state field groups ([rows][N]; obstacles [N][3][32]); see include/usvgpu.h UsvField."""
         out = {}
         for name in (names or self._FIELDS):
             fid, arr = self._field_array(name)

@@ -75,7 +75,8 @@ typedef struct UsvStats {
 } UsvStats;
 
 /* State field groups for usvgpu_get_state / usvgpu_set_state.  Layout of every group is
- * [rows][n_envs] (structure of arrays, env index fastest). */
+ * [rows][n_envs] (structure of arrays, env index fastest) except the obstacle table, whose
+ * row is one env (the sensor kernel gives a warp to an env, lane = obstacle slot). */
 typedef enum UsvField {
     /* float64 [23][N]: x y psi | u v r | x_dot y_dot psi_dot u_dot v_dot r_dot e_u ka_dot_u ka_dot_psi (last,
      * usv_asmc.py:57) | psi_d_last o_dot_dot_last o_dot_last o_last (usv_asmc.py:58) |
@@ -83,7 +84,8 @@ typedef enum UsvField {
     USV_FIELD_DYN = 0,
     /* float64 [7][N]: path_start x y | path_end x y | max_action[0] max_action[2] | reference_velocity */
     USV_FIELD_EPI = 1,
-    /* float64 (float32 when obstacles_f32) [32][3][N]: per slot x, y, radius (simple_env.py:258,290) */
+    /* float64 (float32 when obstacles_f32) [N][3][32]: per env x[32], y[32], radius[32]; slots >= n_obs
+     * are ignored (simple_env.py:258,290) */
     USV_FIELD_OBSTACLES = 2,
     USV_FIELD_N_OBS = 3,     /* int32 [N]   simple_env.py:268                    */
     USV_FIELD_STEPS = 4,     /* int32 [N]   TimeLimit elapsed steps              */
@@ -124,7 +126,13 @@ int usvgpu_reset(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream)
 int usvgpu_step(usvgpu_handle h, const float* actions, float* obs, float* reward, uint8_t* terminated,
                 uint8_t* truncated, float* terminal_obs, void* stream);
 
-/* K back-to-back steps (one launch each; state round-trips HBM every step) with pre-staged
+/* usvgpu_step() that also reports the device time of its two kernels (CUDA events on `stream`):
+ * kernel_ms[0] = dynamics_kernel, kernel_ms[1] = sensor_kernel.  Synchronises `stream`.  For
+ * bench.py's roofline line; not for the training loop. */
+int usvgpu_step_timed(usvgpu_handle h, const float* actions, float* obs, float* reward, uint8_t* terminated,
+                      uint8_t* truncated, float* terminal_obs, void* stream, float* kernel_ms);
+
+/* K back-to-back steps (two launches each; state round-trips HBM every step) with pre-staged
  * actions float32 [K][N][2]; outputs are overwritten every step.  action_wrap > 0 re-uses the
  * first action_wrap slabs cyclically.  This is the loop of tools/profile_env.py:5-7. */
 int usvgpu_rollout(usvgpu_handle h, const float* actions, int32_t n_steps, int32_t action_wrap, float* obs,

