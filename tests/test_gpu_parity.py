@@ -65,10 +65,13 @@ def test_asmc_compute_golden_anchor_and_fixed_actions(usv):
                 continue
             # y, psi, v, r stay ~1e-11 for these actions and beta = asin(v / (0.001 + speed)) amplifies their ulps
             # and the yaw channel sits on its sliding surface where sign(sigma) chatters: sway / yaw rate are
-            # rounding noise of order 1e-7 on both sides (measured on B200: |dr| 2.5e-7 around |r| 1e-7).  The
-            # reference's own test only asks |v|, |r| < 1 (tests/test_usv_asmc.py:18-28).
+            # rounding noise of order 1e-6 on both sides whose SIGN is arbitrary (measured on B200: reference
+            # r = +1.18e-6, CUDA r = -1.10e-6 at call 500 of action [10, 0]).  The reference's own test only asks
+            # |v|, |r| < 1 (tests/test_usv_asmc.py:18-28).  Surge speed, the one non-degenerate velocity, is held
+            # to rtol 1e-9.
             np.testing.assert_allclose(h[0:3, 0], g["fixed_pos"][k, j], rtol=1e-9, atol=1e-6)
-            np.testing.assert_allclose(h[3:6, 0], g["fixed_vel"][k, j], rtol=1e-9, atol=1e-6)
+            np.testing.assert_allclose(h[3, 0], g["fixed_vel"][k, j][0], rtol=1e-9, atol=1e-9)
+            np.testing.assert_allclose(h[4:6, 0], g["fixed_vel"][k, j][1:], rtol=0, atol=1e-5)
         x, y, psi, u, v, r = h[:6, 0]
         if k == 0:
             assert np.allclose(h[:6], 0)
