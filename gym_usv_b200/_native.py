@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
 HEADERS = [os.path.join(CSRC, f) for f in ("usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
-                                             "usv_sensor.cuh", "usv_kernels.cuh")] + \
+                                             "usv_sensor.cuh", "usv_kernels.cuh", "usv_math.cuh")] + \
           [os.path.join(_ROOT, "include", "usvgpu.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
@@ -105,6 +105,8 @@ _SIGNATURES = {
     "usvgpu_asmc_compute": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64,
                                       C.c_int32, C.c_void_p, C.c_void_p]),
     "usvgpu_sensors": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "usvgpu_math_probe": (C.c_int, [C.c_int, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "usvgpu_fp64_peak": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.c_void_p]),
 }
 
 EXPORTS = tuple(_SIGNATURES)

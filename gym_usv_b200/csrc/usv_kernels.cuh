@@ -18,12 +18,14 @@
 
 namespace usv {
 
-constexpr int DYN_B = 64;        // threads (= envs) per CTA of the dynamics kernel
+constexpr int DYN_B = 32;        // threads (= envs) per CTA of the dynamics kernel: one warp, so that the 2048 warps of a
+                                 // 65 536-env shard spread evenly over the 148 SMs (13.8 per SM)
+constexpr int DYN_MIN_CTAS = 16; // all of them resident at once (<= 128 registers): no second, nearly empty wave
 constexpr int SENS_WARPS = 8;    // warps (= envs) per CTA of the sensor kernel
 
 // ---------------------------------------------------------------------------------------------
 template <bool PERTURB>
-__global__ void __launch_bounds__(DYN_B)
+__global__ void __launch_bounds__(DYN_B, DYN_MIN_CTAS)
 dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     const long long n = s.n;
     const long long i = (long long)blockIdx.x * DYN_B + threadIdx.x;
@@ -55,36 +57,35 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     c.eu_int = dyn[(long long)D_EU_INT * n];
     c.ka_u = dyn[(long long)D_KA_U * n];
     c.ka_psi = dyn[(long long)D_KA_PSI * n];
-    double progress = dyn[(long long)D_PROGRESS * n];
-    const double* epi = s.epi + i;
-    const double psx = epi[(long long)E_PSX * n], psy = epi[(long long)E_PSY * n];
-    const double pex = epi[(long long)E_PEX * n], pey = epi[(long long)E_PEY * n];
-    const double ma0 = epi[(long long)E_MA0 * n], ma2 = epi[(long long)E_MA2 * n];
-    const double vref = epi[(long long)E_VREF * n];
     int steps = s.steps[i];
     const float2 af = reinterpret_cast<const float2*>(actions)[i];
     const double a0 = (double)af.x, a1 = (double)af.y;
 
     // ---- 2 x UsvAsmc.compute = 20 sub-steps (simple_env_asmc.py:19-25) -----------------------
     const long long pstep0 = (long long)steps * 20;
-    for (int k = 0; k < 20; ++k) {
-        double sn, cs;
-        sincos(p.psi, &sn, &cs);
-        asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
-    }
+    double sn, cs;
+    sincos(p.psi, &sn, &cs);  // carried through the sub-steps by small rotations (usv_math.cuh)
+#pragma unroll 1
+    for (int k = 0; k < 20; ++k) asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
+
+    // episode constants are only needed from here on: loaded late to keep them out of the sub-step loop's registers
+    double progress = dyn[(long long)D_PROGRESS * n];
+    const double* epi = s.epi + i;
+    const double psx = epi[(long long)E_PSX * n], psy = epi[(long long)E_PSY * n];
+    const double pex = epi[(long long)E_PEX * n], pey = epi[(long long)E_PEY * n];
+    const double ma0 = epi[(long long)E_MA0 * n], ma2 = epi[(long long)E_MA2 * n];
+    const double vref = epi[(long long)E_VREF * n];
 
     // ---- UsvSimpleEnv.step(zeros(2)): kinematic post-step, simple_env.py:311-324 -------------
     // action = 0.8*last_action + 0.2*(max_action*0) and last_action is 0 for the whole life of
     // this env, so the commanded velocity is 0.
-    double sn, cs;
     if (!fl.skip_kinematic) {
         const double du = np_clip(0.0 - p.u, -MAX_ACC_U, MAX_ACC_U);
         p.u = np_clip(p.u + du, -ma0, ma0);
         p.v = 0.0;  // clip(v + clip(-v, -0, 0), -0, 0): max_acceleration[1] = max_action[1] = 0
         const double dr = np_clip(0.0 - p.r, -MAX_ACC_R, MAX_ACC_R);
         p.r = np_clip(p.r + dr, -ma2, ma2);
-        if (p.u != 0.0) {
-            sincos(p.psi, &sn, &cs);
+        if (p.u != 0.0) {  // only when |u| > 1.75: the carried cos/sin are good to ~1e-15
             p.x = p.x + (p.u * cs) * DT;
             p.y = p.y + (p.u * sn) * DT;
         }
@@ -95,7 +96,7 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     // ---- closest point on the path, simple_env.py:139-148 ------------------------------------
     const double pdx = pex - psx, pdy = pey - psy;
     const double det = pdx * pdx + pdy * pdy;
-    double a = (pdy * (p.y - psy) + pdx * (p.x - psx)) / det;
+    double a = div_k(pdy * (p.y - psy) + pdx * (p.x - psx), det);
     a += (0.005 / 10) * ENV_HI;
     a = np_clip(a, progress, 1.0);
     const double tgx = psx + a * pdx, tgy = psy + a * pdy;
@@ -107,28 +108,32 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     const bool tlimit = (fl.max_episode_steps > 0) && (steps >= fl.max_episode_steps);
 
     // ---- observation header, simple_env.py:72-96 ---------------------------------------------
-    const double inv_len = rsqrt(det);
+    double half_inv_len;
+    sqrt_k(det, half_inv_len);
+    const double inv_len = 2.0 * half_inv_len;
     const double ye = -(p.x - psx) * (pdy * inv_len) + (p.y - psy) * (pdx * inv_len);  // :133-137
     const double ang = wrap_pi(atan2(tgy - p.y, tgx - p.x) - p.psi);                  // :67-69
     const double tdx = p.x - tgx, tdy = p.y - tgy;
-    const double tdist = sqrt(fma(tdx, tdx, tdy * tdy));
+    const double tdist = sqrt_k(fma(tdx, tdx, tdy * tdy));
+    // the reference divides (x / 10, angle / pi, ...): multiplying by the rounded reciprocal differs by at
+    // most one float64 ulp before the float32 rounding
     float* hdr = s.hdr + i;
-    hdr[(long long)H_U * n] = (float)(p.u / 10);
-    hdr[(long long)H_V * n] = (float)(p.v / 10);
-    hdr[(long long)H_R * n] = (float)(p.r / 10);
-    hdr[(long long)H_ANG * n] = (float)(ang / PI);
-    hdr[(long long)H_DIST * n] = (float)(tdist / DIST_NORM);
-    hdr[(long long)H_YE * n] = (float)(ye / 10);
-    hdr[(long long)H_VREF * n] = (float)(vref / 10);
-    hdr[(long long)H_MA0 * n] = (float)(ma0 / 10);
-    hdr[(long long)H_MA2 * n] = (float)(ma2 / 10);
+    hdr[(long long)H_U * n] = (float)(p.u * 0.1);
+    hdr[(long long)H_V * n] = (float)(p.v * 0.1);
+    hdr[(long long)H_R * n] = (float)(p.r * 0.1);
+    hdr[(long long)H_ANG * n] = (float)(ang * (1.0 / PI));
+    hdr[(long long)H_DIST * n] = (float)(tdist * (1.0 / DIST_NORM));
+    hdr[(long long)H_YE * n] = (float)(ye * 0.1);
+    hdr[(long long)H_VREF * n] = (float)(vref * 0.1);
+    hdr[(long long)H_MA0 * n] = (float)(ma0 * 0.1);
+    hdr[(long long)H_MA2 * n] = (float)(ma2 * 0.1);
 
     // ---- reward without the collision term, simple_env.py:150-201 ----------------------------
-    const double t = ye / 0.075;
+    const double t = ye * (1.0 / 0.075);
     const double at = fabs(t);
     const double ye_reward = exp(-fmin(at, t * t));  // max(exp(-|t|), exp(-t^2)): exp is monotone
     const double angle_reward = exp(-fabs(ang));
-    const double vel_reward = exp(-fabs(sqrt(fma(p.u, p.u, p.v * p.v)) - vref)) * 0.05;
+    const double vel_reward = exp(-fabs(sqrt_k(fma(p.u, p.u, p.v * p.v)) - vref)) * 0.05;
     s.rew_part[i] = ye_reward + angle_reward + vel_reward;  // delta_action_reward = -0, arrived = 0
     s.cs[i] = cs;
     s.cs[n + i] = sn;
@@ -292,9 +297,10 @@ __global__ void asmc_compute_kernel(long long n, double* __restrict__ state, con
     const double a0 = actions[2 * i], a1 = actions[2 * i + 1];
     double inf[4] = {0, 0, 0, 0};
     long long ps = first_substep;
+    double sn, cs;
+    sincos(p.psi, &sn, &cs);
     for (int k = 0; k < n_calls * 10; ++k, ++ps) {
-        double sn, cs;
-        sincos(p.psi, &sn, &cs);
+        if (k % 20 == 0) sincos(p.psi, &sn, &cs);  // the env step re-seeds the carried cos/sin every 20 sub-steps
         asmc_substep<PERTURB, true>(p, c, a0, a1, cs, sn, ps, inf);
     }
 #pragma unroll
@@ -333,6 +339,38 @@ sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const dou
     sensor_warp(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, o, hit, 0.05, a, 0.2, b);
 #pragma unroll
     for (int p = 0; p < 4; ++p) out[(long long)(lane + 32 * p) * n + i] = o[p];
+}
+
+// ---------------------------------------------------------------------------------------------
+// probes (include/usvgpu.h: usvgpu_math_probe, usvgpu_fp64_peak)
+// ---------------------------------------------------------------------------------------------
+__global__ void math_probe_kernel(int which, long long n, const double* __restrict__ in, double* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (which == 0) out[i] = sqrt_k(in[i]);
+    else if (which == 1) out[i] = div_k(in[i], in[n + i]);
+    else if (which == 2) out[i] = asin_k(in[i]);
+    else {
+        double cs = in[n + i], sn = in[2 * n + i];
+        rot_small(in[i], cs, sn);
+        out[i] = cs;
+        out[n + i] = sn;
+    }
+}
+
+__global__ void __launch_bounds__(256) fp64_peak_kernel(int iters, double seed, double* __restrict__ sink) {
+    double a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = seed + (double)(threadIdx.x + k);
+    const double m = 1.0 - 1e-9 * seed, b = 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = fma(a[k], m, b);
+    }
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += a[k];
+    if (t == 123.456) sink[0] = t;  // never true: keeps the chains alive
 }
 
 }  // namespace usv

@@ -1,0 +1,121 @@
+// usv_math.cuh -- float64 device math for the step kernels, written for the sm_100a FP64 pipe.
+//
+// Why not the CUDA math library: on sm_100a every float64 literal that is not representable in its
+// high 32 bits costs two UMOV issue slots per use (the r01b profile of dynamics_kernel showed 26 % of
+// all issued instructions were UMOVs feeding the polynomial coefficients of sincos()/asin(), and the
+// general-purpose routines carry range / special-case branches this path never takes).  Here
+//   * coefficients live in __constant__ memory (one LDCU.128 brings two of them into uniform registers),
+//   * sqrt and reciprocal are a MUFU seed + Newton steps without the slow-path checks (arguments are
+//     sums of squares and bounded denominators),
+//   * the heading's cos/sin are carried through the 20 sub-steps by a small-angle rotation instead of
+//     20 full-range sincos() calls.
+// Accuracy (tests/test_gpu_parity.py::test_device_math_probe): sqrt_k, div_k <= 1 ulp, asin_k <= 2 ulp,
+// rot_small <= 1 ulp per application (|d| <= 1/32) -- the same order as the libm-vs-CUDA differences the parity
+// tolerance already covers.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+
+namespace usv {
+
+struct MathK {
+    double asin_c[13];  // tools/gen_asin_poly.py: (asin(sqrt z)/sqrt z - 1)/z on z in [0, 0.25], degree 12
+    double sin_c[3];    // -1/3!, 1/5!, -1/7!
+    double cos_c[3];    // 1/4!, -1/6!, 1/8!   (-1/2! is an immediate)
+    double pio2_hi, pio2_lo;
+};
+
+__constant__ MathK MATHK = {
+    {0.16666666666666669, 0.07499999999998433, 0.04464285714635543, 0.030381944138531247, 0.02237217294214989,
+     0.017352392720869973, 0.013971212973552933, 0.011479177415184906, 0.01032281435018578, 0.005457506718640358,
+     0.01740087944269402, -0.014851887071247204, 0.028757851367421566},
+    {-1.0 / 6, 1.0 / 120, -1.0 / 5040},
+    {1.0 / 24, -1.0 / 720, 1.0 / 40320},
+    1.5707963267948966, 6.123233995736766e-17};
+
+// MUFU.RSQ64H / MUFU.RCP64H: ~20-bit seeds computed from the high word
+__device__ __forceinline__ double rsqrt_seed(double a) {
+    double r;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(a));
+    return r;
+}
+__device__ __forceinline__ double rcp_seed(double a) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(a));
+    return r;
+}
+
+// sqrt(a) for 0 <= a << DBL_MAX (sums of squares, |sigma|, discriminants); exactly 0 for a == 0.
+// half_rinv receives ~1/(2 sqrt a) (garbage when a == 0), which callers reuse as a free reciprocal.
+__device__ __forceinline__ double sqrt_k(double a, double& half_rinv) {
+    const double r = rsqrt_seed(a);
+    double h = 0.5 * r;
+    double g = a * r;
+    g = fma(fma(-g, g, a), h, g);          // Newton on g: ~2^-40
+    h = fma(fma(-r, g, 1.0), h, h);        // refine h with the new g
+    g = fma(fma(-g, g, a), h, g);          // final correction: <= 1 ulp
+    half_rinv = h;
+    return (a > 0.0) ? g : 0.0;
+}
+__device__ __forceinline__ double sqrt_k(double a) {
+    double h;
+    return sqrt_k(a, h);
+}
+
+// 1/d for a normal, finite d bounded away from 0 (no special cases)
+__device__ __forceinline__ double rcp_k(double d) {
+    double r = rcp_seed(d);
+    double e = fma(-d, r, 1.0);
+    e = fma(e, e, e);
+    r = fma(r, e, r);  // cubic step
+    e = fma(-d, r, 1.0);
+    return fma(r, e, r);
+}
+// n/d with one residual correction (<= 1 ulp)
+__device__ __forceinline__ double div_k(double n, double d) {
+    const double r = rcp_k(d);
+    const double q = n * r;
+    return fma(fma(-d, q, n), r, q);
+}
+
+// asin(x), |x| <= 1.  One polynomial serves both ranges: |x| <= 0.5 directly, otherwise through
+// asin(x) = pi/2 - 2 asin(sqrt((1 - |x|)/2)).
+__device__ __forceinline__ double asin_k(double x) {
+    const double a = fabs(x);
+    const bool big = a > 0.5;
+    double z = a * a, s = a, corr = 0.0;
+    if (big) {
+        z = fma(-0.5, a, 0.5);  // exact for a in [0.5, 1]
+        double h;
+        s = sqrt_k(z, h);
+        corr = fma(-s, s, z) * h;  // sqrt(z) - s, so that s + corr carries the rounding error of s
+        if (!(z > 0.0)) corr = 0.0;
+    }
+    const double* c = MATHK.asin_c;
+    double p = c[12];
+#pragma unroll
+    for (int k = 11; k >= 0; --k) p = fma(p, z, c[k]);
+    const double t = fma(s * z, p, corr);  // asin(s) - s
+    double r = s + t;
+    if (big) r = (MATHK.pio2_hi - 2.0 * s) - (fma(2.0, t, -MATHK.pio2_lo));
+    return copysign(r, x);
+}
+
+// (cs, sn) <- rotation of (cs, sn) by d, |d| <= 1/32 (Taylor to d^7 / d^8: truncation < 1e-19 relative)
+__device__ __forceinline__ void rot_small(double d, double& cs, double& sn) {
+    const double z = d * d;
+    const double* S = MATHK.sin_c;
+    const double* C = MATHK.cos_c;
+    double ps = fma(S[2], z, S[1]);
+    ps = fma(ps, z, S[0]);
+    const double sd = fma(d * z, ps, d);  // sin d
+    double pc = fma(C[2], z, C[1]);
+    pc = fma(pc, z, C[0]);
+    pc = fma(pc, z, -0.5);
+    const double cm1 = z * pc;  // cos d - 1
+    const double c0 = cs, s0 = sn;
+    cs = fma(-s0, sd, fma(c0, cm1, c0));
+    sn = fma(c0, sd, fma(s0, cm1, s0));
+}
+
+}  // namespace usv

@@ -338,4 +338,40 @@ int usvgpu_sensors(int device, int64_t n, const double* pose, const double* obst
     return USV_OK;
 }
 
+int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, double* out, void* stream) {
+    if (!in || !out || n <= 0 || which < 0 || which > 3) return fail(nullptr, USV_ERR_INVALID, "bad math_probe arguments");
+    int rc = check_device(nullptr, device);
+    if (rc) return rc;
+    CU_TRY(nullptr, cudaSetDevice(device));
+    const int threads = 128;
+    math_probe_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(which, n, in, out);
+    CU_TRY(nullptr, cudaGetLastError());
+    return USV_OK;
+}
+
+int usvgpu_fp64_peak(int device, int32_t blocks, int32_t iters, double* dfma_per_sec, void* stream) {
+    if (!dfma_per_sec || blocks <= 0 || iters <= 0) return fail(nullptr, USV_ERR_INVALID, "bad fp64_peak arguments");
+    int rc = check_device(nullptr, device);
+    if (rc) return rc;
+    CU_TRY(nullptr, cudaSetDevice(device));
+    cudaStream_t st = (cudaStream_t)stream;
+    double* sink = nullptr;
+    CU_TRY(nullptr, cudaMalloc((void**)&sink, sizeof(double)));
+    cudaEvent_t ev[2];
+    CU_TRY(nullptr, cudaEventCreate(&ev[0]));
+    CU_TRY(nullptr, cudaEventCreate(&ev[1]));
+    fp64_peak_kernel<<<blocks, 256, 0, st>>>(iters / 8 + 1, 1.0, sink);  // warm-up
+    CU_TRY(nullptr, cudaEventRecord(ev[0], st));
+    fp64_peak_kernel<<<blocks, 256, 0, st>>>(iters, 1.0, sink);
+    CU_TRY(nullptr, cudaEventRecord(ev[1], st));
+    CU_TRY(nullptr, cudaEventSynchronize(ev[1]));
+    float ms = 0.f;
+    CU_TRY(nullptr, cudaEventElapsedTime(&ms, ev[0], ev[1]));
+    cudaEventDestroy(ev[0]);
+    cudaEventDestroy(ev[1]);
+    cudaFree(sink);
+    *dfma_per_sec = (double)blocks * 256.0 * 8.0 * (double)iters / ((double)ms * 1e-3);
+    return USV_OK;
+}
+
 }  // extern "C"

@@ -51,3 +51,25 @@ def sensor_distances(pose: torch.Tensor, obstacles: torch.Tensor, n_obs: torch.T
                                   C.c_void_p(out.data_ptr()), _stream(pose.device))
     nat.check(rc)
     return out
+
+
+def math_probe(which: str, x: torch.Tensor) -> torch.Tensor:
+    """Evaluate one float64 device routine of csrc/usv_math.cuh (test surface).  which: 'sqrt' x[n] | 'div' x[2,n] |
+    'asin' x[n] | 'rot' x[3,n] = (delta, cos, sin) -> [2,n]."""
+    code = {"sqrt": 0, "div": 1, "asin": 2, "rot": 3}[which]
+    if not x.is_cuda:
+        raise nat.UsvError("math_probe needs CUDA tensors: there is no CPU fallback")
+    assert x.dtype == torch.float64 and x.is_contiguous()
+    n = x.shape[-1]
+    out = torch.empty((2, n) if which == "rot" else (n,), dtype=torch.float64, device=x.device)
+    nat.check(nat.lib().usvgpu_math_probe(x.device.index or 0, code, n, C.c_void_p(x.data_ptr()),
+                                          C.c_void_p(out.data_ptr()), _stream(x.device)))
+    return out
+
+
+def fp64_peak(device: int = 0, blocks: int = 148 * 8, iters: int = 20000) -> float:
+    """Measured thread-level float64 FMA/s of the GPU (usvgpu_fp64_peak)."""
+    v = C.c_double()
+    nat.check(nat.lib().usvgpu_fp64_peak(int(device), int(blocks), int(iters), C.byref(v),
+                                         _stream(torch.device("cuda", device))))
+    return float(v.value)

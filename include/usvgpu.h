@@ -163,6 +163,17 @@ int usvgpu_asmc_compute(int device, int64_t n, double* state, const double* acti
 int usvgpu_sensors(int device, int64_t n, const double* pose, const double* obstacles, const int32_t* n_obs,
                    double* out, void* stream);
 
+/* Device-math probe (test / measurement surface, no reference counterpart): evaluates one of the float64
+ * routines of csrc/usv_math.cuh that replace libm calls of the reference (np.sqrt, '/', np.math.asin at
+ * usv_asmc.py:72,103,150; np.cos / np.sin at :179-181) on n inputs.  which: 0 sqrt_k(in[i]) | 1 div_k(in[i],
+ * in[n+i]) | 2 asin_k(in[i]) | 3 rot_small(in[i]) applied to (cos, sin) = (in[n+i], in[2n+i]) -> out[i], out[n+i]. */
+int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, double* out, void* stream);
+
+/* Measured float64 FMA rate of this GPU (the pipe that bounds both step kernels): a grid of
+ * `blocks` x 256 threads runs `iters` x 8 independent DFMA chains per thread; *dfma_per_sec receives
+ * thread-level FMAs per second (CUDA events on `stream`; synchronises). */
+int usvgpu_fp64_peak(int device, int32_t blocks, int32_t iters, double* dfma_per_sec, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,6 +36,42 @@ def _dyn_from_oracle(s):
 
 
 # ------------------------------------------------------------------------------------------
+# device math (csrc/usv_math.cuh) against numpy float64
+# ------------------------------------------------------------------------------------------
+def _ulps(got, want):
+    return np.abs(got - want) / np.spacing(np.maximum(np.abs(want), 1e-300))
+
+
+def test_device_math_probe(usv):
+    """sqrt_k / div_k / asin_k / rot_small replace np.sqrt, '/', np.math.asin, np.cos / np.sin of the reference
+    (usv_asmc.py:72,103,150,179-181): held to <= 1 / 1 / 2 ulp and 1.5e-16 absolute."""
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(11)
+    n = 1 << 18
+    # sqrt: sums of squares, |sigma|, discriminants -- including exact zero and tiny / huge magnitudes
+    x = np.concatenate([[0.0, 1e-300, 1e-30, 4.0, 1e30], rng.uniform(0, 4, n), 10.0 ** rng.uniform(-20, 8, n)])
+    got = usv.math_probe("sqrt", torch.tensor(x, device=dev)).cpu().numpy()
+    assert got[0] == 0.0
+    assert _ulps(got[1:], np.sqrt(x[1:])).max() <= 1.0
+    # division by 0.001 + speed and by the squared path length
+    num = rng.uniform(-3, 3, n)
+    den = np.concatenate([0.001 + rng.uniform(0, 3, n // 2), rng.uniform(1e4, 1.3e4, n - n // 2)])
+    got = usv.math_probe("div", torch.tensor(np.stack([num, den]), device=dev)).cpu().numpy()
+    assert _ulps(got, num / den).max() <= 1.0
+    # asin on [-1, 1] including the end points, the range switch and tiny arguments
+    x = np.concatenate([[0.0, 1.0, -1.0, 0.5, -0.5, np.nextafter(0.5, 1), 1e-12, -1e-300], rng.uniform(-1, 1, n),
+                        rng.uniform(-0.05, 0.05, n)])
+    got = usv.math_probe("asin", torch.tensor(x, device=dev)).cpu().numpy()
+    assert _ulps(got, np.arcsin(x)).max() <= 2.0
+    assert got[0] == 0.0 and np.all(np.sign(got[1:]) == np.sign(x[1:]))
+    # small rotation of a unit vector
+    d = rng.uniform(-0.03125, 0.03125, n)
+    th = rng.uniform(-np.pi, np.pi, n)
+    got = usv.math_probe("rot", torch.tensor(np.stack([d, np.cos(th), np.sin(th)]), device=dev)).cpu().numpy()
+    assert np.abs(got[0] - np.cos(th + d)).max() < 4e-16 and np.abs(got[1] - np.sin(th + d)).max() < 4e-16
+
+
+# ------------------------------------------------------------------------------------------
 # UsvAsmc.compute
 # ------------------------------------------------------------------------------------------
 def test_asmc_compute_golden_anchor_and_fixed_actions(usv):
