@@ -10,8 +10,8 @@
 //                    reward / flags, episode statistics and the SB3 auto-reset (usv_reset.cuh).
 // The split exists because the two halves want opposite shapes: the dynamics are one long serial
 // float64 chain per env (few fat threads), the sensor pass is 30 obstacles x 128 rays of short
-// independent tests (many thin threads).  The hand-over (heading cos/sin, header, partial reward,
-// flags: 61 B per env) is written and re-read through L2 within one launch pair.
+// independent tests (many thin threads).  The hand-over (pose, heading cos/sin, partial reward, flags: 48 B,
+// and the 64 B observation header row) is written and re-read through L2 within one launch pair.
 #pragma once
 #include "usv_reset.cuh"
 #include "usv_sensor.cuh"
@@ -22,6 +22,7 @@ constexpr int DYN_B = 32;        // threads (= envs) per CTA of the dynamics ker
                                  // 65 536-env shard spread evenly over the 148 SMs (13.8 per SM)
 constexpr int DYN_MIN_CTAS = 16; // all of them resident at once (<= 128 registers): no second, nearly empty wave
 constexpr int SENS_WARPS = 8;    // warps (= envs) per CTA of the sensor kernel
+constexpr int SENS_MIN_CTAS = 4; // 32 resident warps per SM (<= 64 registers): the pass is latency bound
 
 // ---------------------------------------------------------------------------------------------
 template <bool PERTURB>
@@ -116,17 +117,13 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     const double tdx = p.x - tgx, tdy = p.y - tgy;
     const double tdist = sqrt_k(fma(tdx, tdx, tdy * tdy));
     // the reference divides (x / 10, angle / pi, ...): multiplying by the rounded reciprocal differs by at
-    // most one float64 ulp before the float32 rounding
-    float* hdr = s.hdr + i;
-    hdr[(long long)H_U * n] = (float)(p.u * 0.1);
-    hdr[(long long)H_V * n] = (float)(p.v * 0.1);
-    hdr[(long long)H_R * n] = (float)(p.r * 0.1);
-    hdr[(long long)H_ANG * n] = (float)(ang * (1.0 / PI));
-    hdr[(long long)H_DIST * n] = (float)(tdist * (1.0 / DIST_NORM));
-    hdr[(long long)H_YE * n] = (float)(ye * 0.1);
-    hdr[(long long)H_VREF * n] = (float)(vref * 0.1);
-    hdr[(long long)H_MA0 * n] = (float)(ma0 * 0.1);
-    hdr[(long long)H_MA2 * n] = (float)(ma2 * 0.1);
+    // most one float64 ulp before the float32 rounding.  Columns 7, 8 (last_action), 10 (max_action[1]) and
+    // 13 (max_acceleration[1]) are 0 for the whole life of this env.
+    float4* hrow = reinterpret_cast<float4*>(s.hdr16 + i * HDR_PAD);
+    hrow[0] = make_float4((float)(p.u * 0.1), (float)(p.v * 0.1), (float)(p.r * 0.1), (float)(ang * (1.0 / PI)));
+    hrow[1] = make_float4((float)(tdist * (1.0 / DIST_NORM)), (float)(ye * 0.1), (float)(vref * 0.1), 0.0f);
+    hrow[2] = make_float4(0.0f, (float)(ma0 * 0.1), 0.0f, (float)(ma2 * 0.1));
+    hrow[3] = make_float4((float)(MAX_ACC_U / 10), 0.0f, (float)(MAX_ACC_R / 10), 0.0f);
 
     // ---- reward without the collision term, simple_env.py:150-201 ----------------------------
     const double t = ye * (1.0 / 0.075);
@@ -134,10 +131,15 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     const double ye_reward = exp(-fmin(at, t * t));  // max(exp(-|t|), exp(-t^2)): exp is monotone
     const double angle_reward = exp(-fabs(ang));
     const double vel_reward = exp(-fabs(sqrt_k(fma(p.u, p.u, p.v * p.v)) - vref)) * 0.05;
-    s.rew_part[i] = ye_reward + angle_reward + vel_reward;  // delta_action_reward = -0, arrived = 0
-    s.cs[i] = cs;
-    s.cs[n + i] = sn;
-    s.flags[i] = (uint8_t)((oob ? FLG_OOB : 0u) | (tlimit ? FLG_TLIMIT : 0u));
+    Hand hd;
+    hd.x = p.x;
+    hd.y = p.y;
+    hd.cs = cs;
+    hd.sn = sn;
+    hd.rew_part = ye_reward + angle_reward + vel_reward;  // delta_action_reward = -0, arrived = 0
+    hd.flags = (oob ? FLG_OOB : 0u) | (tlimit ? FLG_TLIMIT : 0u);
+    hd.pad = 0u;
+    s.hand[i] = hd;
     if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.psi))) atomicAdd(&s.stats->nonfinite, 1ull);
 
     // ---- store state ---------------------------------------------------------------------------
@@ -168,26 +170,12 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// observation column `lane` (< 15) from the hand-over block, simple_env.py:91-96
-__device__ __forceinline__ float header_column(const StatePtrs& s, long long i, int lane) {
-    // column -> hand-over row; -1: constant
-    int row = -1;
-    float v = 0.0f;                       // columns 7, 8 (last_action), 10 (max_action[1]), 13 (max_acc[1])
-    if (lane <= 6) row = lane;            // u v r | angle dist ye v_ref
-    else if (lane == 9) row = H_MA0;
-    else if (lane == 11) row = H_MA2;
-    else if (lane == 12) v = (float)(MAX_ACC_U / 10);
-    else if (lane == 14) v = (float)(MAX_ACC_R / 10);
-    if (row >= 0) v = s.hdr[(long long)row * s.n + i];
-    return v;
-}
-
 template <bool OBST, typename ObT>
-__global__ void __launch_bounds__(SENS_WARPS * 32)
+__global__ void __launch_bounds__(SENS_WARPS * 32, SENS_MIN_CTAS)
 sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restrict__ reward,
               uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated, float* __restrict__ terminal_obs) {
     __shared__ double2 raytab[N_SENS];
-    __shared__ SensorScratch scratch[SENS_WARPS];
+    __shared__ SensorScratch scratch[OBST ? SENS_WARPS : 1];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (OBST) {
         if (tid < N_SENS) raytab[tid] = s.raytab[tid];
@@ -197,12 +185,14 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
     const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
     if (i >= n) return;
 
+    // ---- hand-over from the dynamics kernel ------------------------------------------------------
+    const Hand hd = s.hand[i];
+    float head = (lane < HDR) ? s.hdr16[i * HDR_PAD + lane] : 0.0f;  // observation columns 0..14, simple_env.py:91-96
+
     // ---- sensors, simple_env.py:203-226 --------------------------------------------------------
     float sens[4] = {1.0f, 1.0f, 1.0f, 1.0f};  // max range / 100 (simple_env.py:83); ignore_obstacles: all rays (:222-224)
     bool term = false, collided = false;
     if (OBST) {
-        const double x = s.dyn[(long long)D_X * n + i], y = s.dyn[(long long)D_Y * n + i];
-        const double cps = s.cs[i], sps = s.cs[n + i];
         const int nob = s.n_obs[i];
         const ObT* row = obst_row<ObT>(s, i);
         double ox = 0.0, oy = 0.0, rr = 0.0;
@@ -212,22 +202,18 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
             rr = (double)row[2 * MAX_OBST + lane];
         }
         double out[4];
-        bool hit[4];
-        sensor_warp(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, out, hit, 0.05, term, 0.2, collided);
+        sensor_warp(scratch[warp], raytab, lane, nob, hd.x, hd.y, hd.cs, hd.sn, ox, oy, rr, out, 0.05, term, 0.2, collided);
 #pragma unroll
-        for (int p = 0; p < 4; ++p)
-            if (hit[p]) sens[p] = (float)(out[p] * 0.01);
+        for (int p = 0; p < 4; ++p) sens[p] = (float)(out[p] * 0.01);  // SENSOR_MAX_RANGE * 0.01 rounds to 1.0f
     }
 
     // ---- flags (simple_env.py:334-336 + TimeLimit), reward (:150-201) ---------------------------
-    const unsigned flg = s.flags[i];
-    const bool oob = flg & FLG_OOB, tlimit = flg & FLG_TLIMIT;
+    const bool oob = hd.flags & FLG_OOB, tlimit = hd.flags & FLG_TLIMIT;
     const bool trunc = oob || tlimit;
     const bool done = term || trunc;
-    const double rew = (collided ? -20.0 : 0.0) + s.rew_part[i];
-    const double ep_ret = s.ep_return[i] + rew;
-    float head = (lane < HDR) ? header_column(s, i, lane) : 0.0f;
+    const double rew = (collided ? -20.0 : 0.0) + hd.rew_part;
     if (lane == 0) {
+        const double ep_ret = s.ep_return[i] + rew;
         reward[i] = (float)rew;
         terminated[i] = term ? 1 : 0;
         truncated[i] = trunc ? 1 : 0;
@@ -240,6 +226,7 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
             if (oob) atomicAdd(&st->out_of_bounds, 1ull);
             if (tlimit && !term && !oob) atomicAdd(&st->time_limit, 1ull);
         }
+        if (!(done && fl.auto_reset)) s.ep_return[i] = ep_ret;  // the reset below zeroes it otherwise
     }
 
     // ---- observation row(s): 15 header columns + 128 sensor columns, contiguous in obs[N][143] ----
@@ -252,8 +239,6 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
             for (int p = 0; p < 4; ++p) trow[HDR + lane + 32 * p] = sens[p];
         }
         head = reset_env_warp<ObT>(s, i, lane);  // header <- reset obs; sensor columns stay (simple_env.py:302)
-    } else if (lane == 0) {
-        s.ep_return[i] = ep_ret;
     }
     if (lane < HDR) orow[lane] = head;
 #pragma unroll
@@ -335,8 +320,8 @@ sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const dou
         rr = obstacles[((long long)lane * 3 + 2) * n + i];
     }
     double o[4];
-    bool hit[4], a, b;
-    sensor_warp(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, o, hit, 0.05, a, 0.2, b);
+    bool a, b;
+    sensor_warp(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, o, 0.05, a, 0.2, b);
 #pragma unroll
     for (int p = 0; p < 4; ++p) out[(long long)(lane + 32 * p) * n + i] = o[p];
 }

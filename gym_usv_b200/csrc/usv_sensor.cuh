@@ -7,51 +7,82 @@
 // FIRST one each ray hits; the equivalent sort-free rule is "among the obstacles a ray hits, the
 // one with the smallest key wins" (SURVEY.md H2).  One warp owns one env:
 //   phase A  lane = obstacle: offset rotated into the body frame, key, and the wedge of rays the circle
-//            can touch (+-asin(r/d) around its bearing, found in float32 and widened by a margin),
-//            clipped to the 4 pi / 3 fan; a warp scan turns the wedge sizes into offsets of a compacted
-//            list of (obstacle, ray) candidate pairs (~100 per env instead of 29 x 128);
-//   phase B  lane = candidate pair, 32 per pass, all lanes busy: the reference's float64 hit test; a
-//            hit sets the obstacle's bit in the ray's hit mask and leaves its reading;
-//   phase C  lane = ray (4 passes of 32): no hit -> max range; one hit -> that reading; several hits
-//            (overlapping circles, rare) -> smallest key wins and its reading is recomputed.
-// All hit / miss / ordering decisions are taken in float64.  In the body frame the ray directions are
-// the constant table (cos phi_i, sin phi_i), so along = cos phi bx + sin phi by and
-// perp = sin phi bx - cos phi by equal the reference's expressions (usv_asmc_ca_env.py:516-518) with
-// cos / sin (psi + phi_i) expanded.
+//            can touch (+-asin(r/d) around its bearing; cheap float32 approximations widened by a margin
+//            -- a few extra candidates cost a test, a missing one would be an error), clipped to the
+//            4 pi / 3 fan; a warp scan turns the wedge sizes into offsets of a compacted list of
+//            (obstacle, ray) candidate pairs (~140 per env instead of 29 x 128);
+//   phase B  lane = candidate pair, 32 per pass, all lanes busy: the reference's float64 hit test; a hit
+//            stores its reading in the pair's slot and enters the ray's winner word with a shared-memory
+//            atomicMin on (order-preserving float32 key bits | obstacle slot);
+//   phase C  lane = ray (4 passes of 32): winner word -> obstacle -> pair slot -> reading.
+// All hit / miss decisions are float64.  The winner order is decided on float32-rounded keys, which is
+// exact unless two obstacles that hit the SAME ray have keys equal to within 2^-19 relative: phase B
+// detects exactly that (the atomicMin returns a word with the same key bits) and the env then re-does
+// its rays on the exact path (float64 keys, ascending slot order breaks ties like the reference's
+// stable argsort).  In the body frame the ray directions are the constant table (cos phi_i, sin phi_i),
+// so along = cos phi bx + sin phi by and perp = sin phi bx - cos phi by equal the reference's
+// expressions (usv_asmc_ca_env.py:516-518) with cos / sin (psi + phi_i) expanded.
 #pragma once
 #include "usv_math.cuh"
 #include "usv_state.cuh"
 
 namespace usv {
 
+constexpr int PAIR_SLOTS = 256;           // readings kept per env; pairs beyond that are recomputed in phase C
+constexpr uint32_t NO_HIT = 0xFFFFFFFFu;
+
 struct SensorScratch {  // per warp
     double bx[MAX_OBST], by[MAX_OBST], rr2[MAX_OBST], key[MAX_OBST];
-    double hval[N_SENS];        // reading left by a hitting pair (valid when the ray has exactly one hit)
-    uint32_t hitmask[N_SENS];   // bit j: obstacle j hits this ray
+    double hpair[PAIR_SLOTS];   // reading of candidate pair t (valid where the pair hit)
+    uint32_t best[N_SENS];      // min over hitting obstacles of (key bits & ~31 | slot)
     int off[MAX_OBST];          // exclusive prefix sum of the candidate counts
     uint32_t seg[MAX_OBST];     // first ray of piece 1 | rays in piece 1 << 8 | first ray of piece 2 << 16
+    uint32_t kbits[MAX_OBST];   // order-preserving bits of (float)key, low 5 bits = slot
+    int ne[MAX_OBST];           // slots of the obstacles that have candidates, in order
 };
 
-// reading of ray ri on obstacle j, whatever it is (phase C recomputation)
-__device__ __forceinline__ double ray_reading(const SensorScratch& sc, const double2* raytab, int ri, int j) {
+// atan2(y, x) to 2.1e-4 rad (7th-order odd polynomial on the folded octant)
+__device__ __forceinline__ float atan2_coarse(float y, float x) {
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    const float a = __fdividef(mn, fmaxf(mx, 1e-30f));
+    const float s = a * a;
+    float r = fmaf(fmaf(fmaf(-0.0464964749f, s, 0.15931422f), s, -0.327622764f), s * a, a);
+    r = (ay > ax) ? 1.57079637f - r : r;
+    r = (x < 0.0f) ? 3.14159274f - r : r;
+    return copysignf(r, y);
+}
+// asin(q) for 0 <= q <= 1, never more than 7.5e-5 rad below the true value
+__device__ __forceinline__ float asin_coarse(float q) {
+    if (q > 0.5f) return asinf(fminf(q, 1.0f));
+    const float s = q * q;
+    return q * fmaf(s, fmaf(s, fmaf(s, 15.0f / 336, 3.0f / 40), 1.0f / 6), 1.0f);
+}
+
+// the reference's test of ray ri against obstacle j: hit iff along >= 0, delta >= 0 and the reading is
+// inside the range (usv_asmc_ca_env.py:448-458)
+__device__ __forceinline__ bool ray_test(const SensorScratch& sc, const double2* raytab, int ri, int j, double& h) {
     const double2 t = raytab[ri];
     const double bx = sc.bx[j], by = sc.by[j];
-    const double along = fma(t.x, bx, t.y * by);
-    const double perp = fma(t.y, bx, -(t.x * by));
-    return along - sqrt_k(fma(-perp, perp, sc.rr2[j]));
+    const double along = fma(t.x, bx, t.y * by);         // :516
+    const double perp = fma(t.y, bx, -(t.x * by));       // :518
+    const double delta = fma(-perp, perp, sc.rr2[j]);    // :453
+    if (!(along >= 0.0 && delta >= 0.0)) return false;   // :448, :454
+    h = along - sqrt_k(delta);                           // :457
+    return h < SENSOR_MAX_RANGE;                         // :458
 }
 
 // ox, oy, rr: this lane's obstacle (ignored when lane >= nob).  cps/sps = cos/sin(psi).
-// out[p]: reading of ray (lane + 32 p), SENSOR_MAX_RANGE when nothing is hit; hit[p] says which.
+// out[p]: reading of ray (lane + 32 p), SENSOR_MAX_RANGE when nothing is hit.
 // min_key_lt / min_hit_lt: warp-uniform "min over obstacles of key < key_thr" and "min over rays of
 // reading < hit_thr" (simple_env.py:334 and :153-156).
 __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __restrict__ raytab, const int lane,
                                             const int nob, const double x, const double y, const double cps,
                                             const double sps, const double ox, const double oy, const double rr,
-                                            double out[4], bool hit[4], const double key_thr, bool& min_key_lt,
+                                            double out[4], const double key_thr, bool& min_key_lt,
                                             const double hit_thr, bool& min_hit_lt) {
     constexpr unsigned FULL = 0xFFFFFFFFu;
-    reinterpret_cast<uint4*>(sc.hitmask)[lane] = make_uint4(0u, 0u, 0u, 0u);
+    reinterpret_cast<uint4*>(sc.best)[lane] = make_uint4(NO_HIT, NO_HIT, NO_HIT, NO_HIT);
 
     // ---- phase A: lane = obstacle ---------------------------------------------------------------
     bool key_lt = false;
@@ -66,12 +97,13 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
         sc.by[lane] = by;
         sc.rr2[lane] = rr * rr;
         sc.key[lane] = key;
+        const uint32_t kb = __float_as_uint((float)key);  // float32 rounding is monotone: it can tie, never invert
+        sc.kbits[lane] = (((kb & 0x80000000u) ? ~kb : (kb | 0x80000000u)) & ~31u) | (uint32_t)lane;
         if (d <= rr) {  // boat inside the circle (only on a terminal step): every ray may hit
             n1 = N_SENS;
         } else {
-            const float rel = atan2f((float)by, (float)bx);       // bearing relative to the bow
-            const float cf = (rel + 2.0943951f) * INV_PITCH_F;    // its ray index, in [-32, 160]
-            const float w = asinf(fminf((float)rr / (float)d, 1.0f)) * INV_PITCH_F + 0.05f;
+            const float cf = (atan2_coarse((float)by, (float)bx) + 2.0943951f) * INV_PITCH_F;  // ray index of the bearing, [-32, 160]
+            const float w = asin_coarse(__fdividef((float)rr, (float)d)) * INV_PITCH_F + 0.05f;  // approximations: < 0.01 ray
             const int klo = (int)ceilf(cf - w), khi = (int)floorf(cf + w);
             // rays klo..khi (mod 192) that fall inside the fan 0..127: one piece, plus a second one when the
             // wedge wraps around the stern (khi >= 192 or klo <= -65); the wedge is < 98 rays wide, so the
@@ -94,64 +126,80 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
         const int v = __shfl_up_sync(FULL, incl, s);
         if (lane >= s) incl += v;
     }
-    sc.off[lane] = incl - cnt;
+    const int off = incl - cnt;
+    const bool has = cnt > 0;
+    const unsigned has_bal = __ballot_sync(FULL, has);
+    if (has) sc.ne[__popc(has_bal & ((1u << lane) - 1u))] = lane;
+    sc.off[lane] = off;
     sc.seg[lane] = (uint32_t)lo1 | ((uint32_t)n1 << 8) | ((uint32_t)lo2 << 16);
     const int total = __shfl_sync(FULL, incl, 31);
     __syncwarp();
 
     // ---- phase B: lane = candidate pair ------------------------------------------------------------
-    for (int t = lane; t < total; t += 32) {
-        int j = 0;  // largest j with off[j] <= t: the obstacle whose piece(s) contain pair t
-#pragma unroll
-        for (int s = 16; s; s >>= 1)
-            if (sc.off[j + s] <= t) j += s;
-        const int p = t - sc.off[j];
-        const uint32_t sg = sc.seg[j];
-        const int m1 = (int)((sg >> 8) & 0xFFu);
-        const int ri = (p < m1) ? (int)(sg & 0xFFu) + p : (int)(sg >> 16) + (p - m1);
-        const double2 tb = raytab[ri];
-        const double bx = sc.bx[j], by = sc.by[j];
-        const double along = fma(tb.x, bx, tb.y * by);             // usv_asmc_ca_env.py:516
-        const double perp = fma(tb.y, bx, -(tb.x * by));           // :518
-        const double delta = fma(-perp, perp, sc.rr2[j]);          // :453
-        if (along >= 0.0 && delta >= 0.0) {                        // :448, :454
-            const double h = along - sqrt_k(delta);                // :457
-            if (h < SENSOR_MAX_RANGE) {                            // :458
-                atomicOr(&sc.hitmask[ri], 1u << j);
-                sc.hval[ri] = h;  // several hits on one ray race here; phase C recomputes those rays
+    // Pair t belongs to the last obstacle (among those with candidates) whose offset is <= t.  Per pass of 32
+    // pairs: bit k of `starts` marks an obstacle whose list starts at pair base + k, `before` counts those that
+    // started earlier, so the owner of pair base + q is ne[before + popc(starts & bits 0..q) - 1].
+    bool ambiguous = false;
+    int before = 0;
+    for (int base = 0; base < total; base += 32) {
+        const unsigned rel = (unsigned)(off - base);
+        const unsigned starts = __reduce_or_sync(FULL, (has && rel < 32u) ? (1u << rel) : 0u);
+        const int t = base + lane;
+        if (t < total) {
+            const int j = sc.ne[before + __popc(starts & (0xFFFFFFFFu >> (31 - lane))) - 1];
+            const int p = t - sc.off[j];
+            const uint32_t sg = sc.seg[j];
+            const int m1 = (int)((sg >> 8) & 0xFFu);
+            const int ri = (p < m1) ? (int)(sg & 0xFFu) + p : (int)(sg >> 16) + (p - m1);
+            double h;
+            if (ray_test(sc, raytab, ri, j, h)) {
+                const uint32_t v = sc.kbits[j];
+                const uint32_t old = atomicMin(&sc.best[ri], v);
+                ambiguous = ambiguous || ((old >> 5) == (v >> 5));  // same ray, keys equal in float32: order undecided
+                if (t < PAIR_SLOTS) sc.hpair[t] = h;
             }
         }
+        before += __popc(starts);
     }
+    ambiguous = __any_sync(FULL, ambiguous);
     __syncwarp();
 
     // ---- phase C: lane = ray ---------------------------------------------------------------------
     bool hit_lt = false;
+    if (!ambiguous) {
 #pragma unroll
-    for (int p = 0; p < 4; ++p) {
-        const int ri = lane + 32 * p;
-        uint32_t m = sc.hitmask[ri];
-        out[p] = SENSOR_MAX_RANGE;
-        hit[p] = m != 0u;
-        if (m) {
-            double h;
-            if (m & (m - 1u)) {
-                int bj = 0;
-                double bkey = INFINITY;
-                do {  // ascending j + strict '<': the lower slot wins a tie, as the reference's stable argsort does
-                    const int j = __ffs(m) - 1;
-                    m &= m - 1u;
-                    const double kj = sc.key[j];
-                    if (kj < bkey) {
-                        bkey = kj;
-                        bj = j;
-                    }
-                } while (m);
-                h = ray_reading(sc, raytab, ri, bj);
-            } else {
-                h = sc.hval[ri];
+        for (int p = 0; p < 4; ++p) {
+            const int ri = lane + 32 * p;
+            const uint32_t w = sc.best[ri];
+            double h = SENSOR_MAX_RANGE;
+            if (w != NO_HIT) {
+                const int j = (int)(w & 31u);
+                const uint32_t sg = sc.seg[j];
+                const int m1 = (int)((sg >> 8) & 0xFFu);
+                int q = ri - (int)(sg & 0xFFu);
+                if ((unsigned)q >= (unsigned)m1) q = m1 + ri - (int)(sg >> 16);
+                const int t = sc.off[j] + q;
+                if (t < PAIR_SLOTS) h = sc.hpair[t];
+                else ray_test(sc, raytab, ri, j, h);
+                hit_lt = hit_lt || (h < hit_thr);
             }
             out[p] = h;
-            hit_lt = hit_lt || (h < hit_thr);
+        }
+    } else {
+        // exact path: every obstacle against this lane's rays, float64 keys, strict '<' in ascending slot order
+        // (the lower slot wins a tie, as the reference's stable argsort does)
+        for (int p = 0; p < 4; ++p) {
+            const int ri = lane + 32 * p;
+            double bkey = INFINITY, bh = SENSOR_MAX_RANGE;
+            for (int j = 0; j < nob; ++j) {
+                double h;
+                if (ray_test(sc, raytab, ri, j, h) && sc.key[j] < bkey) {
+                    bkey = sc.key[j];
+                    bh = h;
+                }
+            }
+            out[p] = bh;
+            hit_lt = hit_lt || (bkey < INFINITY && bh < hit_thr);
         }
     }
     min_hit_lt = __any_sync(FULL, hit_lt);

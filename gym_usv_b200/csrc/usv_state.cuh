@@ -34,9 +34,18 @@ static_assert(N_DYN == USV_DYN_ROWS, "header/kernel row count mismatch");
 enum EpiRow { E_PSX = 0, E_PSY, E_PEX, E_PEY, E_MA0, E_MA2, E_VREF, N_EPI };
 static_assert(N_EPI == USV_EPI_ROWS, "header/kernel row count mismatch");
 
-// rows of the float32 hand-over block the dynamics kernel leaves for the sensor kernel: the
-// env-dependent observation header columns (simple_env.py:91-96) already divided and rounded
-enum HdrRow { H_U = 0, H_V, H_R, H_ANG, H_DIST, H_YE, H_VREF, H_MA0, H_MA2, N_HDR };
+// Hand-over from the dynamics kernel to the sensor kernel (same launch pair, stays in L2): one 48-byte record per
+// env (three 16-byte loads, all lanes of the env's warp read the same addresses) plus the observation header
+// row, 15 float32 columns of simple_env.py:91-96 already divided and rounded, padded to 16 (one 64-byte line).
+struct alignas(16) Hand {
+    double x, y;        // pose the sensors see
+    double cs, sn;      // cos / sin of its heading
+    double rew_part;    // reward without the collision term
+    unsigned flags;     // FLG_OOB | FLG_TLIMIT
+    unsigned pad;
+};
+static_assert(sizeof(Hand) == 48, "hand-over record");
+constexpr int HDR_PAD = 16;
 constexpr unsigned FLG_OOB = 1u, FLG_TLIMIT = 2u;
 
 // simple_env.py:34-35,56,13
@@ -60,11 +69,8 @@ struct StatePtrs {
     int* steps;         // [n]
     int* episode;       // [n]
     double* ep_return;  // [n]
-    // hand-over from the dynamics kernel to the sensor kernel (same launch pair, lives in L2)
-    double* cs;         // [2][n]  cos / sin of the post-step heading
-    double* rew_part;   // [n]     reward without the collision term
-    float* hdr;         // [N_HDR][n]
-    uint8_t* flags;     // [n]     FLG_OOB | FLG_TLIMIT
+    Hand* hand;         // [n]      dynamics -> sensor hand-over
+    float* hdr16;       // [n][16]  observation header rows
     DeviceStats* stats;
     const double2* raytab;  // [128] cos/sin of the ray angles relative to the bow
     long long n;
@@ -79,19 +85,6 @@ struct StepFlags {
 template <typename ObT>
 __device__ __forceinline__ ObT* obst_row(const StatePtrs& s, long long i) {
     return static_cast<ObT*>(s.obst) + i * OBST_ROW;
-}
-
-// sqrt for arguments that are sums of squares / discriminants (a >= 0, far from overflow):
-// float32 reciprocal-sqrt seed + two Newton steps in float64 (<= 1 ulp), ~9 instructions instead of
-// the ~25 of the IEEE-rounded sqrt().  a == 0 gives 0.
-__device__ __forceinline__ double sqrt_pos(double a) {
-    const float af = fmaxf((float)a, 1e-30f);
-    const double r = (double)rsqrtf(af);
-    const double h = 0.5 * r;
-    double g = a * r;
-    g = fma(fma(-g, g, a), h, g);
-    g = fma(fma(-g, g, a), h, g);
-    return g;
 }
 
 }  // namespace usv

@@ -152,10 +152,8 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     alloc((void**)&h->sp.steps, n * sizeof(int));
     alloc((void**)&h->sp.episode, n * sizeof(int));
     alloc((void**)&h->sp.ep_return, n * sizeof(double));
-    alloc((void**)&h->sp.cs, n * 2 * sizeof(double));
-    alloc((void**)&h->sp.rew_part, n * sizeof(double));
-    alloc((void**)&h->sp.hdr, n * N_HDR * sizeof(float));
-    alloc((void**)&h->sp.flags, n);
+    alloc((void**)&h->sp.hand, n * sizeof(Hand));
+    alloc((void**)&h->sp.hdr16, n * HDR_PAD * sizeof(float));
     alloc((void**)&h->sp.stats, sizeof(DeviceStats));
     double2* rt = nullptr;
     alloc((void**)&rt, N_SENS * sizeof(double2));
@@ -185,10 +183,8 @@ int usvgpu_destroy(usvgpu_handle h) {
     cudaFree(h->sp.steps);
     cudaFree(h->sp.episode);
     cudaFree(h->sp.ep_return);
-    cudaFree(h->sp.cs);
-    cudaFree(h->sp.rew_part);
-    cudaFree(h->sp.hdr);
-    cudaFree(h->sp.flags);
+    cudaFree(h->sp.hand);
+    cudaFree(h->sp.hdr16);
     cudaFree(h->sp.stats);
     cudaFree((void*)h->sp.raytab);
     delete h;
