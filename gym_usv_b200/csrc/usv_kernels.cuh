@@ -343,18 +343,22 @@ __global__ void math_probe_kernel(int which, long long n, const double* __restri
     }
 }
 
+template <int CHAINS>
 __global__ void __launch_bounds__(256) fp64_peak_kernel(int iters, double seed, double* __restrict__ sink) {
-    double a[8];
+    double a[CHAINS];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) a[k] = seed + (double)(threadIdx.x + k);
+    for (int k = 0; k < CHAINS; ++k) a[k] = seed + (double)(threadIdx.x + k);
     const double m = 1.0 - 1e-9 * seed, b = 1e-9;
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) a[k] = fma(a[k], m, b);
+        for (int r = 0; r < 8 / CHAINS; ++r) {
+#pragma unroll
+            for (int k = 0; k < CHAINS; ++k) a[k] = fma(a[k], m, b);
+        }
     }
     double t = 0.0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t += a[k];
+    for (int k = 0; k < CHAINS; ++k) t += a[k];
     if (t == 123.456) sink[0] = t;  // never true: keeps the chains alive
 }
 

@@ -13,13 +13,13 @@
 //            (obstacle, ray) candidate pairs (~140 per env instead of 29 x 128);
 //   phase B  lane = candidate pair, 32 per pass, all lanes busy: the reference's float64 hit test; a hit
 //            stores its reading in the pair's slot and enters the ray's winner word with a shared-memory
-//            atomicMin on (order-preserving float32 key bits | obstacle slot);
-//   phase C  lane = ray (4 passes of 32): winner word -> obstacle -> pair slot -> reading.
-// All hit / miss decisions are float64.  The winner order is decided on float32-rounded keys, which is
-// exact unless two obstacles that hit the SAME ray have keys equal to within 2^-19 relative: phase B
-// detects exactly that (the atomicMin returns a word with the same key bits) and the env then re-does
-// its rays on the exact path (float64 keys, ascending slot order breaks ties like the reference's
-// stable argsort).  In the body frame the ray directions are the constant table (cos phi_i, sin phi_i),
+//            atomicMin on (order-preserving float32 key bits, top 24 | pair slot, low 8);
+//   phase C  lane = ray (4 passes of 32): winner word -> pair slot -> reading (slot 255 holds "max range").
+// All hit / miss decisions are float64.  The winner order is decided on the top 24 bits of the float32-
+// rounded keys, which is exact unless two obstacles that hit the SAME ray have keys equal to within 2^-16
+// relative: phase B detects exactly that (the atomicMin returns a word with the same key bits) and the
+// env then re-does its rays on the exact path (float64 keys, ascending slot order breaks ties like the
+// reference's stable argsort); so does an env with more than 255 candidate pairs (boat inside circles).  In the body frame the ray directions are the constant table (cos phi_i, sin phi_i),
 // so along = cos phi bx + sin phi by and perp = sin phi bx - cos phi by equal the reference's
 // expressions (usv_asmc_ca_env.py:516-518) with cos / sin (psi + phi_i) expanded.
 #pragma once
@@ -28,16 +28,14 @@
 
 namespace usv {
 
-constexpr int PAIR_SLOTS = 256;           // readings kept per env; pairs beyond that are recomputed in phase C
+constexpr int PAIR_SLOTS = 256;           // slot 255 is reserved: "no hit" -> SENSOR_MAX_RANGE
 constexpr uint32_t NO_HIT = 0xFFFFFFFFu;
 
 struct SensorScratch {  // per warp
-    double bx[MAX_OBST], by[MAX_OBST], rr2[MAX_OBST], key[MAX_OBST];
+    double4 geo[MAX_OBST];      // bx, by (offset in the body frame), radius^2, key
+    int4 rec[MAX_OBST];         // split, rbase, rbase2, key bits: pair t of this obstacle is ray t + (t < split ? rbase : rbase2)
     double hpair[PAIR_SLOTS];   // reading of candidate pair t (valid where the pair hit)
-    uint32_t best[N_SENS];      // min over hitting obstacles of (key bits & ~31 | slot)
-    int off[MAX_OBST];          // exclusive prefix sum of the candidate counts
-    uint32_t seg[MAX_OBST];     // first ray of piece 1 | rays in piece 1 << 8 | first ray of piece 2 << 16
-    uint32_t kbits[MAX_OBST];   // order-preserving bits of (float)key, low 5 bits = slot
+    uint32_t best[N_SENS];      // min over hitting obstacles of (key bits & ~255 | pair slot)
     int ne[MAX_OBST];           // slots of the obstacles that have candidates, in order
 };
 
@@ -59,17 +57,15 @@ __device__ __forceinline__ float asin_coarse(float q) {
     return q * fmaf(s, fmaf(s, fmaf(s, 15.0f / 336, 3.0f / 40), 1.0f / 6), 1.0f);
 }
 
-// the reference's test of ray ri against obstacle j: hit iff along >= 0, delta >= 0 and the reading is
-// inside the range (usv_asmc_ca_env.py:448-458)
-__device__ __forceinline__ bool ray_test(const SensorScratch& sc, const double2* raytab, int ri, int j, double& h) {
-    const double2 t = raytab[ri];
-    const double bx = sc.bx[j], by = sc.by[j];
-    const double along = fma(t.x, bx, t.y * by);         // :516
-    const double perp = fma(t.y, bx, -(t.x * by));       // :518
-    const double delta = fma(-perp, perp, sc.rr2[j]);    // :453
-    if (!(along >= 0.0 && delta >= 0.0)) return false;   // :448, :454
-    h = along - sqrt_k(delta);                           // :457
-    return h < SENSOR_MAX_RANGE;                         // :458
+// the reference's test of a ray (direction t in the body frame) against an obstacle g: hit iff along >= 0,
+// delta >= 0 and the reading is inside the range (usv_asmc_ca_env.py:448-458)
+__device__ __forceinline__ bool ray_test(const double2 t, const double4 g, double& h) {
+    const double along = fma(t.x, g.x, t.y * g.y);      // :516
+    const double perp = fma(t.y, g.x, -(t.x * g.y));    // :518
+    const double delta = fma(-perp, perp, g.z);         // :453
+    if (!(along >= 0.0 && delta >= 0.0)) return false;  // :448, :454
+    h = along - sqrt_k(delta);                          // :457
+    return h < SENSOR_MAX_RANGE;                        // :458
 }
 
 // ox, oy, rr: this lane's obstacle (ignored when lane >= nob).  cps/sps = cos/sin(psi).
@@ -87,18 +83,17 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
     // ---- phase A: lane = obstacle ---------------------------------------------------------------
     bool key_lt = false;
     int lo1 = 0, n1 = 0, lo2 = 0, n2 = 0;
+    uint32_t kbits = 0u;
+    if (lane == 0) sc.hpair[PAIR_SLOTS - 1] = SENSOR_MAX_RANGE;
     if (lane < nob) {
         const double dx = ox - x, dy = oy - y;  // usv_asmc_ca_env.py:508
         const double d = sqrt_k(fma(dx, dx, dy * dy));
         const double key = d - rr;              // simple_env.py:205-206
         key_lt = key < key_thr;
         const double bx = fma(cps, dx, sps * dy), by = fma(cps, dy, -(sps * dx));  // offset in the body frame
-        sc.bx[lane] = bx;
-        sc.by[lane] = by;
-        sc.rr2[lane] = rr * rr;
-        sc.key[lane] = key;
+        sc.geo[lane] = make_double4(bx, by, rr * rr, key);
         const uint32_t kb = __float_as_uint((float)key);  // float32 rounding is monotone: it can tie, never invert
-        sc.kbits[lane] = (((kb & 0x80000000u) ? ~kb : (kb | 0x80000000u)) & ~31u) | (uint32_t)lane;
+        kbits = ((kb & 0x80000000u) ? ~kb : (kb | 0x80000000u)) & ~255u;
         if (d <= rr) {  // boat inside the circle (only on a terminal step): every ray may hit
             n1 = N_SENS;
         } else {
@@ -130,8 +125,7 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
     const bool has = cnt > 0;
     const unsigned has_bal = __ballot_sync(FULL, has);
     if (has) sc.ne[__popc(has_bal & ((1u << lane) - 1u))] = lane;
-    sc.off[lane] = off;
-    sc.seg[lane] = (uint32_t)lo1 | ((uint32_t)n1 << 8) | ((uint32_t)lo2 << 16);
+    sc.rec[lane] = make_int4(off + n1, lo1 - off, lo2 - off - n1, (int)kbits);
     const int total = __shfl_sync(FULL, incl, 31);
     __syncwarp();
 
@@ -147,16 +141,18 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
         const int t = base + lane;
         if (t < total) {
             const int j = sc.ne[before + __popc(starts & (0xFFFFFFFFu >> (31 - lane))) - 1];
-            const int p = t - sc.off[j];
-            const uint32_t sg = sc.seg[j];
-            const int m1 = (int)((sg >> 8) & 0xFFu);
-            const int ri = (p < m1) ? (int)(sg & 0xFFu) + p : (int)(sg >> 16) + (p - m1);
+            const int4 rc = sc.rec[j];
+            const int ri = t + ((t < rc.x) ? rc.y : rc.z);
             double h;
-            if (ray_test(sc, raytab, ri, j, h)) {
-                const uint32_t v = sc.kbits[j];
-                const uint32_t old = atomicMin(&sc.best[ri], v);
-                ambiguous = ambiguous || ((old >> 5) == (v >> 5));  // same ray, keys equal in float32: order undecided
-                if (t < PAIR_SLOTS) sc.hpair[t] = h;
+            if (ray_test(raytab[ri], sc.geo[j], h)) {
+                if (t < PAIR_SLOTS - 1) {
+                    const uint32_t v = (uint32_t)rc.w | (uint32_t)t;
+                    const uint32_t old = atomicMin(&sc.best[ri], v);
+                    ambiguous = ambiguous || ((old >> 8) == (v >> 8));  // same ray, equal key bits: order undecided
+                    sc.hpair[t] = h;
+                } else {
+                    ambiguous = true;  // out of pair slots
+                }
             }
         }
         before += __popc(starts);
@@ -165,43 +161,32 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
     __syncwarp();
 
     // ---- phase C: lane = ray ---------------------------------------------------------------------
-    bool hit_lt = false;
+    double hmin = SENSOR_MAX_RANGE;
     if (!ambiguous) {
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int ri = lane + 32 * p;
-            const uint32_t w = sc.best[ri];
-            double h = SENSOR_MAX_RANGE;
-            if (w != NO_HIT) {
-                const int j = (int)(w & 31u);
-                const uint32_t sg = sc.seg[j];
-                const int m1 = (int)((sg >> 8) & 0xFFu);
-                int q = ri - (int)(sg & 0xFFu);
-                if ((unsigned)q >= (unsigned)m1) q = m1 + ri - (int)(sg >> 16);
-                const int t = sc.off[j] + q;
-                if (t < PAIR_SLOTS) h = sc.hpair[t];
-                else ray_test(sc, raytab, ri, j, h);
-                hit_lt = hit_lt || (h < hit_thr);
-            }
-            out[p] = h;
+            out[p] = sc.hpair[sc.best[lane + 32 * p] & 0xFFu];  // NO_HIT -> slot 255 -> SENSOR_MAX_RANGE
+            hmin = fmin(hmin, out[p]);
         }
     } else {
         // exact path: every obstacle against this lane's rays, float64 keys, strict '<' in ascending slot order
         // (the lower slot wins a tie, as the reference's stable argsort does)
         for (int p = 0; p < 4; ++p) {
-            const int ri = lane + 32 * p;
+            const double2 tb = raytab[lane + 32 * p];
             double bkey = INFINITY, bh = SENSOR_MAX_RANGE;
             for (int j = 0; j < nob; ++j) {
+                const double4 g = sc.geo[j];
                 double h;
-                if (ray_test(sc, raytab, ri, j, h) && sc.key[j] < bkey) {
-                    bkey = sc.key[j];
+                if (ray_test(tb, g, h) && g.w < bkey) {
+                    bkey = g.w;
                     bh = h;
                 }
             }
             out[p] = bh;
-            hit_lt = hit_lt || (bkey < INFINITY && bh < hit_thr);
+            hmin = fmin(hmin, bh);
         }
     }
+    const bool hit_lt = hmin < hit_thr;  // readings of rays without a hit are SENSOR_MAX_RANGE
     min_hit_lt = __any_sync(FULL, hit_lt);
     __syncwarp();
 }

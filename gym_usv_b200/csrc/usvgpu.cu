@@ -346,7 +346,7 @@ int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, do
 }
 
 int usvgpu_fp64_peak(int device, int32_t blocks, int32_t iters, double* dfma_per_sec, void* stream) {
-    if (!dfma_per_sec || blocks <= 0 || iters <= 0) return fail(nullptr, USV_ERR_INVALID, "bad fp64_peak arguments");
+    if (!dfma_per_sec || blocks == 0 || iters <= 0) return fail(nullptr, USV_ERR_INVALID, "bad fp64_peak arguments");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
     CU_TRY(nullptr, cudaSetDevice(device));
@@ -356,9 +356,15 @@ int usvgpu_fp64_peak(int device, int32_t blocks, int32_t iters, double* dfma_per
     cudaEvent_t ev[2];
     CU_TRY(nullptr, cudaEventCreate(&ev[0]));
     CU_TRY(nullptr, cudaEventCreate(&ev[1]));
-    fp64_peak_kernel<<<blocks, 256, 0, st>>>(iters / 8 + 1, 1.0, sink);  // warm-up
+    // blocks > 0: 256 threads x 8 independent chains (throughput).  blocks < 0: |blocks| CTAs of 128 threads (one
+    // warp per SM sub-partition when |blocks| <= SM count) x 1 dependent chain (latency: 8 FMAs per iteration).
+    const bool lat = blocks < 0;
+    if (lat) blocks = -blocks;
+    if (lat) fp64_peak_kernel<1><<<blocks, 128, 0, st>>>(iters / 8 + 1, 1.0, sink);
+    else fp64_peak_kernel<8><<<blocks, 256, 0, st>>>(iters / 8 + 1, 1.0, sink);  // warm-up
     CU_TRY(nullptr, cudaEventRecord(ev[0], st));
-    fp64_peak_kernel<<<blocks, 256, 0, st>>>(iters, 1.0, sink);
+    if (lat) fp64_peak_kernel<1><<<blocks, 128, 0, st>>>(iters, 1.0, sink);
+    else fp64_peak_kernel<8><<<blocks, 256, 0, st>>>(iters, 1.0, sink);
     CU_TRY(nullptr, cudaEventRecord(ev[1], st));
     CU_TRY(nullptr, cudaEventSynchronize(ev[1]));
     float ms = 0.f;
@@ -366,7 +372,7 @@ int usvgpu_fp64_peak(int device, int32_t blocks, int32_t iters, double* dfma_per
     cudaEventDestroy(ev[0]);
     cudaEventDestroy(ev[1]);
     cudaFree(sink);
-    *dfma_per_sec = (double)blocks * 256.0 * 8.0 * (double)iters / ((double)ms * 1e-3);
+    *dfma_per_sec = (double)blocks * (lat ? 128.0 : 256.0) * 8.0 * (double)iters / ((double)ms * 1e-3);
     return USV_OK;
 }
 

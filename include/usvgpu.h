@@ -171,7 +171,9 @@ int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, do
 
 /* Measured float64 FMA rate of this GPU (the pipe that bounds both step kernels): a grid of
  * `blocks` x 256 threads runs `iters` x 8 independent DFMA chains per thread; *dfma_per_sec receives
- * thread-level FMAs per second (CUDA events on `stream`; synchronises). */
+ * thread-level FMAs per second (CUDA events on `stream`; synchronises).  blocks < 0 measures the dependent-issue
+ * latency instead: |blocks| CTAs of 128 threads, ONE dependent chain per thread (seconds per FMA of a chain =
+ * |blocks| * 128 / *dfma_per_sec). */
 int usvgpu_fp64_peak(int device, int32_t blocks, int32_t iters, double* dfma_per_sec, void* stream);
 
 #ifdef __cplusplus

@@ -203,6 +203,50 @@ def test_sensors_random_vs_oracle(usv):
     assert (want < 100).mean() > 0.02
 
 
+def test_sensors_key_ties_take_the_exact_path(usv):
+    """Obstacles that hit the same ray with keys equal in float32 (exact duplicates, float64-equal keys with
+    different radii, and keys 1e-9 apart) must resolve like the reference's stable argsort: the CUDA pass detects
+    the float32 tie and re-does the env on its float64 path (usv_sensor.cuh)."""
+    rng = np.random.default_rng(5)
+    m = 4000
+    n = np.full(m, 12)
+    pos = np.stack([rng.uniform(5, 15, m), rng.uniform(5, 15, m), rng.uniform(-3, 3, m)], 1)
+    ox, oy = rng.uniform(0, 20, (m, 32)), rng.uniform(0, 20, (m, 32))
+    rad = rng.uniform(0.15, 0.5, (m, 32))
+    ahead = rng.uniform(2.0, 6.0, m)
+    bearing = pos[:, 2] + rng.uniform(-1.5, 1.5, m)
+    ox[:, 3] = pos[:, 0] + ahead * np.cos(bearing)
+    oy[:, 3] = pos[:, 1] + ahead * np.sin(bearing)
+    kind = rng.integers(0, 3, m)
+    # kind 0: slot 7 duplicates slot 3 exactly
+    # kind 2: slot 7 further along the same bearing, larger radius, key 1e-9 above / below slot 3's (equal in float32,
+    #         ordered in float64)
+    extra = rng.uniform(0.05, 0.3, m)
+    delta = rng.choice([-1e-9, 1e-9], m)
+    rad7 = np.where(kind == 0, rad[:, 3], rad[:, 3] + extra + delta)
+    d7 = np.where(kind == 0, ahead, ahead + extra)
+    ox[:, 7] = pos[:, 0] + d7 * np.cos(bearing)
+    oy[:, 7] = pos[:, 1] + d7 * np.sin(bearing)
+    rad[:, 7] = rad7
+    # kind 1: float64-EQUAL keys with different geometry, in exactly representable numbers: boat at (8, 8) heading 0,
+    # circles (11, 8) r 0.5 and (11.25, 8) r 0.75 -> both keys are 2.5; the lower slot must win (stable argsort),
+    # and the two readings differ on every ray but the bow ray
+    k1 = np.flatnonzero(kind == 1)
+    pos[k1] = [8.0, 8.0, 0.0]
+    swap = rng.random(len(k1)) < 0.5
+    near, far = np.where(swap, 7, 3), np.where(swap, 3, 7)
+    ox[k1, near], oy[k1, near], rad[k1, near] = 11.0, 8.0, 0.5
+    ox[k1, far], oy[k1, far], rad[k1, far] = 11.25, 8.0, 0.75
+    # keep the other circles of those scenes away from the bow so that the tie decides the reading
+    for j in range(12):
+        if j not in (3, 7):
+            ox[k1, j] = rng.uniform(0, 6, len(k1))
+    got = _sensor_batch(usv, pos, ox, oy, rad, n)
+    want = np.stack([uo.sensors(pos[i], rad[i, :n[i]], ox[i, :n[i]], oy[i, :n[i]]) for i in range(m)])
+    assert np.array_equal(got < 100, want < 100)
+    np.testing.assert_allclose(got, want, rtol=0, atol=1e-8)
+
+
 # ------------------------------------------------------------------------------------------
 # env step: golden replay (reference states injected) and oracle lock-step
 # ------------------------------------------------------------------------------------------
