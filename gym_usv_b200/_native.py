@@ -116,9 +116,10 @@ def lib():
     """Load libusvgpu.so (never builds implicitly on a box without the .so AND without nvcc)."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
+        path = os.environ.get("USVGPU_LIB", LIB_PATH)  # experiments: an alternative build of the same ABI
+        if path == LIB_PATH and not os.path.exists(LIB_PATH):
             build()
-        L = C.CDLL(LIB_PATH)
+        L = C.CDLL(path)
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(L, name)
             fn.restype, fn.argtypes = res, args

@@ -13,6 +13,8 @@
 // independent tests (many thin threads).  The hand-over (pose, heading cos/sin, partial reward, flags: 48 B,
 // and the 64 B observation header row) is written and re-read through L2 within one launch pair.
 #pragma once
+#include <cuda_pipeline.h>
+
 #include "usv_reset.cuh"
 #include "usv_sensor.cuh"
 
@@ -21,8 +23,14 @@ namespace usv {
 constexpr int DYN_B = 32;        // threads (= envs) per CTA of the dynamics kernel: one warp, so that the 2048 warps of a
                                  // 65 536-env shard spread evenly over the 148 SMs (13.8 per SM)
 constexpr int DYN_MIN_CTAS = 16; // all of them resident at once (<= 128 registers): no second, nearly empty wave
-constexpr int SENS_WARPS = 8;    // warps (= envs) per CTA of the sensor kernel
-constexpr int SENS_MIN_CTAS = 4; // 32 resident warps per SM (<= 64 registers): the pass is latency bound
+#ifndef USV_SENS_WARPS
+#define USV_SENS_WARPS 8
+#endif
+#ifndef USV_SENS_MIN_CTAS
+#define USV_SENS_MIN_CTAS 3
+#endif
+constexpr int SENS_WARPS = USV_SENS_WARPS;    // warps (= envs) per CTA of the sensor kernel
+constexpr int SENS_MIN_CTAS = USV_SENS_MIN_CTAS; // resident CTAs per SM the persistent grid is sized for (<= 80 registers)
 
 // ---------------------------------------------------------------------------------------------
 template <bool PERTURB>
@@ -170,79 +178,126 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// What one warp needs from HBM / L2 to do one env is fetched one env AHEAD of the one being computed, with
+// cp.async (LDGSTS) straight into a per-warp shared-memory stage: no registers are held across the sensor pass
+// and the load latency (the r01h profile's top stall: 34 % long-scoreboard) hides behind the previous env.
+template <typename ObT>
+struct alignas(16) SensorStage {
+    ObT obst[OBST_ROW];    // x[32] y[32] radius[32]: the table is padded to 32 slots, copied without waiting for n_obs
+    Hand hd;
+    float head[HDR_PAD];   // observation columns 0..14 (simple_env.py:91-96)
+    int nob;
+    int pad[3];
+};
+
+template <bool OBST, typename ObT>
+__device__ __forceinline__ void sensor_prefetch(SensorStage<ObT>& st, const StatePtrs& s, long long i, int lane) {
+    constexpr int ROW_CHUNKS = (int)(sizeof(ObT) * OBST_ROW / 16);  // 24 (float32 table) or 48 (float64)
+    if (OBST) {
+        const char* row = reinterpret_cast<const char*>(obst_row<ObT>(s, i));
+        char* dst = reinterpret_cast<char*>(st.obst);
+#pragma unroll
+        for (int c = lane; c < ROW_CHUNKS; c += 32) __pipeline_memcpy_async(dst + 16 * c, row + 16 * c, 16);
+        if (lane == 31) __pipeline_memcpy_async(&st.nob, s.n_obs + i, 4);
+    }
+    // lanes 24..26: the 48-byte hand-over record; lanes 27..30: the 64-byte header row
+    if (lane >= 24 && lane < 27)
+        __pipeline_memcpy_async(reinterpret_cast<char*>(&st.hd) + 16 * (lane - 24),
+                                reinterpret_cast<const char*>(s.hand + i) + 16 * (lane - 24), 16);
+    if (lane >= 27 && lane < 31)
+        __pipeline_memcpy_async(reinterpret_cast<char*>(st.head) + 16 * (lane - 27),
+                                reinterpret_cast<const char*>(s.hdr16 + i * HDR_PAD) + 16 * (lane - 27), 16);
+    __pipeline_commit();
+}
+
+// Persistent: the grid is sized to the machine (SENS_MIN_CTAS CTAs per SM) and every warp walks envs
+// warp_id, warp_id + n_warps, ...
 template <bool OBST, typename ObT>
 __global__ void __launch_bounds__(SENS_WARPS * 32, SENS_MIN_CTAS)
 sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restrict__ reward,
               uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated, float* __restrict__ terminal_obs) {
     __shared__ double2 raytab[N_SENS];
     __shared__ SensorScratch scratch[OBST ? SENS_WARPS : 1];
+    __shared__ SensorStage<ObT> stage[SENS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long n = s.n;
+    const long long stride = (long long)gridDim.x * SENS_WARPS;
+    long long i = (long long)blockIdx.x * SENS_WARPS + warp;
+    SensorStage<ObT>& st = stage[warp];
+    if (i < n) sensor_prefetch<OBST, ObT>(st, s, i, lane);
     if (OBST) {
         if (tid < N_SENS) raytab[tid] = s.raytab[tid];
+        if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = SENSOR_MAX_RANGE;  // the "no hit" slot
         __syncthreads();
     }
-    const long long n = s.n;
-    const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
     if (i >= n) return;
 
-    // ---- hand-over from the dynamics kernel ------------------------------------------------------
-    const Hand hd = s.hand[i];
-    float head = (lane < HDR) ? s.hdr16[i * HDR_PAD + lane] : 0.0f;  // observation columns 0..14, simple_env.py:91-96
+    for (;;) {
+        // ---- this env's inputs: stage -> registers, then the stage is free for the next env -------
+        __pipeline_wait_prior(0);
+        __syncwarp();
+        const Hand hd = st.hd;
+        float head = st.head[lane & (HDR_PAD - 1)];
+        const int nob = OBST ? st.nob : 0;
+        const double ox = (double)st.obst[lane], oy = (double)st.obst[MAX_OBST + lane];
+        const double rr = (double)st.obst[2 * MAX_OBST + lane];
+        __syncwarp();
+        const long long i_next = i + stride;
+        if (i_next < n) sensor_prefetch<OBST, ObT>(st, s, i_next, lane);  // in flight during this env's pass
 
-    // ---- sensors, simple_env.py:203-226 --------------------------------------------------------
-    float sens[4] = {1.0f, 1.0f, 1.0f, 1.0f};  // max range / 100 (simple_env.py:83); ignore_obstacles: all rays (:222-224)
-    bool term = false, collided = false;
-    if (OBST) {
-        const int nob = s.n_obs[i];
-        const ObT* row = obst_row<ObT>(s, i);
-        double ox = 0.0, oy = 0.0, rr = 0.0;
-        if (lane < nob) {
-            ox = (double)row[lane];
-            oy = (double)row[MAX_OBST + lane];
-            rr = (double)row[2 * MAX_OBST + lane];
-        }
-        double out[4];
-        sensor_warp(scratch[warp], raytab, lane, nob, hd.x, hd.y, hd.cs, hd.sn, ox, oy, rr, out, 0.05, term, 0.2, collided);
+        // ---- sensors, simple_env.py:203-226 ----------------------------------------------------
+        float sens[4] = {1.0f, 1.0f, 1.0f, 1.0f};  // max range / 100 (simple_env.py:83); ignore_obstacles: all rays (:222-224)
+        bool term = false, collided = false;
+        if (OBST) {
+            double out[4];
+            sensor_warp(scratch[warp], raytab, lane, nob, hd.x, hd.y, hd.cs, hd.sn, ox, oy, rr, out, 0.05, term, 0.2,
+                        collided);
 #pragma unroll
-        for (int p = 0; p < 4; ++p) sens[p] = (float)(out[p] * 0.01);  // SENSOR_MAX_RANGE * 0.01 rounds to 1.0f
-    }
+            for (int p = 0; p < 4; ++p) sens[p] = (float)(out[p] * 0.01);  // SENSOR_MAX_RANGE * 0.01 rounds to 1.0f
+        }
 
-    // ---- flags (simple_env.py:334-336 + TimeLimit), reward (:150-201) ---------------------------
-    const bool oob = hd.flags & FLG_OOB, tlimit = hd.flags & FLG_TLIMIT;
-    const bool trunc = oob || tlimit;
-    const bool done = term || trunc;
-    const double rew = (collided ? -20.0 : 0.0) + hd.rew_part;
-    if (lane == 0) {
-        const double ep_ret = s.ep_return[i] + rew;
-        reward[i] = (float)rew;
-        terminated[i] = term ? 1 : 0;
-        truncated[i] = trunc ? 1 : 0;
-        if (done) {
-            DeviceStats* st = s.stats;
-            atomicAdd(&st->return_sum, ep_ret);
-            atomicAdd(&st->length_sum, (double)s.steps[i]);
-            atomicAdd(&st->episodes, 1ull);
-            if (term) atomicAdd(&st->terminated, 1ull);
-            if (oob) atomicAdd(&st->out_of_bounds, 1ull);
-            if (tlimit && !term && !oob) atomicAdd(&st->time_limit, 1ull);
+        // ---- flags (simple_env.py:334-336 + TimeLimit), reward (:150-201) -----------------------
+        const bool oob = hd.flags & FLG_OOB, tlimit = hd.flags & FLG_TLIMIT;
+        const bool trunc = oob || tlimit;
+        const bool done = term || trunc;
+        const double rew = (collided ? -20.0 : 0.0) + hd.rew_part;
+        if (lane == 0) {
+            reward[i] = (float)rew;
+            terminated[i] = term ? 1 : 0;
+            truncated[i] = trunc ? 1 : 0;
+            if (done) {
+                const double ep_ret = s.ep_return[i] + rew;
+                DeviceStats* ds = s.stats;
+                atomicAdd(&ds->return_sum, ep_ret);
+                atomicAdd(&ds->length_sum, (double)s.steps[i]);
+                atomicAdd(&ds->episodes, 1ull);
+                if (term) atomicAdd(&ds->terminated, 1ull);
+                if (oob) atomicAdd(&ds->out_of_bounds, 1ull);
+                if (tlimit && !term && !oob) atomicAdd(&ds->time_limit, 1ull);
+                if (!fl.auto_reset) s.ep_return[i] = ep_ret;  // the reset below zeroes it otherwise
+            } else {
+                atomicAdd(&s.ep_return[i], rew);  // result unused: a fire-and-forget reduction, no load to wait for
+            }
         }
-        if (!(done && fl.auto_reset)) s.ep_return[i] = ep_ret;  // the reset below zeroes it otherwise
-    }
 
-    // ---- observation row(s): 15 header columns + 128 sensor columns, contiguous in obs[N][143] ----
-    float* orow = obs + i * OBS_DIM;
-    if (done && fl.auto_reset) {
-        if (terminal_obs) {
-            float* trow = terminal_obs + i * OBS_DIM;
-            if (lane < HDR) trow[lane] = head;
+        // ---- observation row(s): 15 header columns + 128 sensor columns, contiguous in obs[N][143] ----
+        float* orow = obs + i * OBS_DIM;
+        if (done && fl.auto_reset) {
+            if (terminal_obs) {
+                float* trow = terminal_obs + i * OBS_DIM;
+                if (lane < HDR) trow[lane] = head;
 #pragma unroll
-            for (int p = 0; p < 4; ++p) trow[HDR + lane + 32 * p] = sens[p];
+                for (int p = 0; p < 4; ++p) trow[HDR + lane + 32 * p] = sens[p];
+            }
+            head = reset_env_warp<ObT>(s, i, lane);  // header <- reset obs; sensor columns stay (simple_env.py:302)
         }
-        head = reset_env_warp<ObT>(s, i, lane);  // header <- reset obs; sensor columns stay (simple_env.py:302)
-    }
-    if (lane < HDR) orow[lane] = head;
+        if (lane < HDR) orow[lane] = head;
 #pragma unroll
-    for (int p = 0; p < 4; ++p) orow[HDR + lane + 32 * p] = sens[p];
+        for (int p = 0; p < 4; ++p) orow[HDR + lane + 32 * p] = sens[p];
+
+        if (i_next >= n) break;
+        i = i_next;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -306,6 +361,7 @@ sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const dou
     __shared__ SensorScratch scratch[SENS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid < N_SENS) raytab[tid] = g_raytab[tid];
+    if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = SENSOR_MAX_RANGE;
     __syncthreads();
     const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
     if (i >= n) return;

@@ -69,6 +69,7 @@ __device__ __forceinline__ bool ray_test(const double2 t, const double4 g, doubl
 }
 
 // ox, oy, rr: this lane's obstacle (ignored when lane >= nob).  cps/sps = cos/sin(psi).
+// The caller sets sc.hpair[PAIR_SLOTS - 1] = SENSOR_MAX_RANGE once (the "no hit" slot).
 // out[p]: reading of ray (lane + 32 p), SENSOR_MAX_RANGE when nothing is hit.
 // min_key_lt / min_hit_lt: warp-uniform "min over obstacles of key < key_thr" and "min over rays of
 // reading < hit_thr" (simple_env.py:334 and :153-156).
@@ -84,7 +85,6 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
     bool key_lt = false;
     int lo1 = 0, n1 = 0, lo2 = 0, n2 = 0;
     uint32_t kbits = 0u;
-    if (lane == 0) sc.hpair[PAIR_SLOTS - 1] = SENSOR_MAX_RANGE;
     if (lane < nob) {
         const double dx = ox - x, dy = oy - y;  // usv_asmc_ca_env.py:508
         const double d = sqrt_k(fma(dx, dx, dy * dy));
@@ -166,7 +166,7 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
             out[p] = sc.hpair[sc.best[lane + 32 * p] & 0xFFu];  // NO_HIT -> slot 255 -> SENSOR_MAX_RANGE
-            hmin = fmin(hmin, out[p]);
+            hmin = (out[p] < hmin) ? out[p] : hmin;
         }
     } else {
         // exact path: every obstacle against this lane's rays, float64 keys, strict '<' in ascending slot order
@@ -183,7 +183,7 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
                 }
             }
             out[p] = bh;
-            hmin = fmin(hmin, bh);
+            hmin = (bh < hmin) ? bh : hmin;
         }
     }
     const bool hit_lt = hmin < hit_thr;  // readings of rays without a hit are SENSOR_MAX_RANGE

@@ -32,6 +32,7 @@ struct UsvGpu {
     std::string err;
     unsigned long long host_env_steps;
     unsigned long long launches;  // kernels launched by step / rollout so far
+    int sm_count;
 };
 
 static thread_local std::string g_create_err;
@@ -70,7 +71,9 @@ static int check_device(UsvGpu* h, int device) {
 template <bool OBST, typename ObT>
 static void launch_sensor(UsvGpu* h, const StepFlags& fl, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
                           float* tobs, cudaStream_t st) {
-    const unsigned blocks = (unsigned)((h->sp.n + SENS_WARPS - 1) / SENS_WARPS);
+    const long long need = (h->sp.n + SENS_WARPS - 1) / SENS_WARPS;
+    const long long resident = (long long)h->sm_count * SENS_MIN_CTAS;  // persistent: one wave, warps loop over envs
+    const unsigned blocks = (unsigned)(need < resident ? need : resident);
     sensor_kernel<OBST, ObT><<<blocks, SENS_WARPS * 32, 0, st>>>(h->sp, fl, obs, reward, term, trunc, tobs);
 }
 
@@ -135,6 +138,8 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->host_env_steps = 0;
     h->launches = 0;
     h->obst_elem = cfg->obstacles_f32 ? sizeof(float) : sizeof(double);
+    h->sm_count = 148;
+    cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
     memset(&h->sp, 0, sizeof(h->sp));
     h->sp.n = n_envs;
     h->sp.global_offset = global_env_offset;
