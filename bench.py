@@ -296,23 +296,33 @@ def run_ours(args, rank, local_rank, world):
     value = n * world * args.steps / (ms_max * 1e-3)
 
     # ---- e2e: host numpy in / host numpy out through VecEnv.step() -----------------------------------
+    # usvgpu_step_host: pinned H2D of the actions, the two kernels, D2H of observations / rewards / flags into
+    # page-locked host buffers, stream sync, terminal observations of the finished envs -- all inside the timed region.
     e2e_steps = max(3, min(args.steps, args.e2e_steps))
     h_acts = np.ascontiguousarray(acts.cpu().numpy())
-    env0 = envs[0]
-    for k in range(2):
-        env0.step(h_acts[k % A])
-    sync_all()
-    t0 = time.perf_counter()
-    sink = 0.0
-    for k in range(e2e_steps):
-        obs, rew, dones, infos = envs[k % len(envs)].step(h_acts[k % A])
-        sink += float(rew[0])
-    torch.cuda.synchronize(dev)
-    te = time.perf_counter() - t0
-    tt = torch.tensor([te], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    e2e_value = n * world * e2e_steps / float(tt.item())
+
+    def e2e_run(mapped):
+        for e in envs:
+            e.mapped_obs = bool(mapped)
+        for k in range(3):
+            envs[k % len(envs)].step(h_acts[k % A])
+        sync_all()
+        t0 = time.perf_counter()
+        sink = 0.0
+        for k in range(e2e_steps):
+            obs, rew, dones, infos = envs[k % len(envs)].step(h_acts[k % A])
+            sink += float(rew[0]) + float(obs[-1, -1])
+        torch.cuda.synchronize(dev)
+        te = time.perf_counter() - t0
+        tt = torch.tensor([te], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return n * world * e2e_steps / float(tt.item())
+
+    e2e_variants = {"staged_d2h": e2e_run(False), "mapped_obs_stores": e2e_run(True)}
+    for e in envs:
+        e.mapped_obs = bool(args.mapped_obs)
+    e2e_value = e2e_variants["mapped_obs_stores" if args.mapped_obs else "staged_d2h"]
     h2d = n * 2 * 4
     d2h = n * (143 * 4 + 4 + 1 + 1)
 
@@ -346,7 +356,9 @@ def run_ours(args, rank, local_rank, world):
             "data": "synthetic", "config": workload_config(args, world),
             "sub_steps_per_sec": value * 20,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "api": "UsvGpuVecEnv.step(np.ndarray) -> np.ndarray obs/rew/dones + lazy infos"},
+                    "steps": e2e_steps, "variants": e2e_variants,
+                    "api": "UsvGpuVecEnv.step(np.ndarray) -> np.ndarray obs/rew/dones + infos of done envs "
+                           "(usvgpu_step_host: page-locked host buffers, H2D + kernels + D2H + sync per step)"},
             "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "kernel": knames[dom],
@@ -389,7 +401,8 @@ def main():
     ap.add_argument("--obstacles-f32", type=int, default=1)
     ap.add_argument("--precision", default="f64", choices=["f64", "mixed"])
     ap.add_argument("--seed", type=int, default=0)
-    ap.add_argument("--e2e-steps", type=int, default=30)
+    ap.add_argument("--e2e-steps", type=int, default=60)
+    ap.add_argument("--mapped-obs", type=int, default=0, help="e2e: sensor kernel stores obs rows straight to mapped host memory")
     ap.add_argument("--ref-envs", type=int, default=4096, help="bounded CPU sample: lock-step envs per oracle step")
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -97,6 +97,13 @@ _SIGNATURES = {
     "usvgpu_step_timed": (C.c_int, [C.c_void_p] * 9),
     "usvgpu_rollout": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p]),
+    "usvgpu_use_staging": (C.c_int, [C.c_void_p] * 6),
+    "usvgpu_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_int64]),
+    "usvgpu_host_free": (C.c_int, [C.c_void_p]),
+    "usvgpu_reset_host": (C.c_int, [C.c_void_p] * 4),
+    "usvgpu_step_host": (C.c_int, [C.c_void_p] * 6 + [C.c_int32, C.c_void_p]),
+    "usvgpu_stream_sync": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "usvgpu_terminal_obs_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "usvgpu_field_bytes": (C.c_int64, [C.c_void_p, C.c_int32]),
     "usvgpu_get_state": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
     "usvgpu_set_state": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),

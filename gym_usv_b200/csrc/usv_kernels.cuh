@@ -317,6 +317,21 @@ __global__ void reset_kernel(StatePtrs s, const uint8_t* __restrict__ mask, floa
 }
 
 // ---------------------------------------------------------------------------------------------
+// rows[k][:] = src[index[k]][:] for the host-buffer face (terminal observations of the envs that finished this step):
+// one warp per row, 8 rows per CTA
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const float* __restrict__ src, const int* __restrict__ index, long long n_index, long long n,
+                   float* __restrict__ rows) {
+    const long long k = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (k >= n_index) return;
+    const int lane = threadIdx.x & 31;
+    const long long i = index[k];
+    if (i < 0 || i >= n) return;
+    for (int c = lane; c < OBS_DIM; c += 32) rows[k * OBS_DIM + c] = src[i * OBS_DIM + c];
+}
+
+// ---------------------------------------------------------------------------------------------
 // Unit-parity kernels
 // ---------------------------------------------------------------------------------------------
 template <bool PERTURB>

@@ -33,6 +33,16 @@ struct UsvGpu {
     unsigned long long host_env_steps;
     unsigned long long launches;  // kernels launched by step / rollout so far
     int sm_count;
+    // device staging for the host-buffer face (usvgpu_step_host), allocated on first use
+    float* d_actions;
+    float* d_obs;
+    float* d_tobs;
+    float* d_reward;
+    uint8_t* d_flags;   // terminated[N] then truncated[N]
+    int32_t* d_idx;     // gather list for usvgpu_terminal_obs_host
+    float* d_rows;      // gathered rows
+    int64_t gather_cap;
+    bool own_staging;   // false after usvgpu_use_staging(): the caller's device buffers are used instead
 };
 
 static thread_local std::string g_create_err;
@@ -139,6 +149,11 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->launches = 0;
     h->obst_elem = cfg->obstacles_f32 ? sizeof(float) : sizeof(double);
     h->sm_count = 148;
+    h->d_actions = h->d_obs = h->d_tobs = h->d_reward = h->d_rows = nullptr;
+    h->d_flags = nullptr;
+    h->d_idx = nullptr;
+    h->gather_cap = 0;
+    h->own_staging = true;
     cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
     memset(&h->sp, 0, sizeof(h->sp));
     h->sp.n = n_envs;
@@ -192,6 +207,15 @@ int usvgpu_destroy(usvgpu_handle h) {
     cudaFree(h->sp.hdr16);
     cudaFree(h->sp.stats);
     cudaFree((void*)h->sp.raytab);
+    if (h->own_staging) {
+        cudaFree(h->d_actions);
+        cudaFree(h->d_obs);
+        cudaFree(h->d_tobs);
+        cudaFree(h->d_reward);
+        cudaFree(h->d_flags);
+    }
+    cudaFree(h->d_idx);
+    cudaFree(h->d_rows);
     delete h;
     return USV_OK;
 }
@@ -251,6 +275,135 @@ int usvgpu_rollout(usvgpu_handle h, const float* actions, int32_t n_steps, int32
                            (cudaStream_t)stream);
         if (rc) return rc;
     }
+    return USV_OK;
+}
+
+// ---- host-buffer face: what stock SB3 does with a VecEnv (numpy actions in, numpy observations out) ----------
+static int ensure_staging(UsvGpu* h) {
+    if (h->d_obs) return USV_OK;
+    const size_t n = (size_t)h->sp.n;
+    CU_TRY(h, cudaMalloc((void**)&h->d_actions, n * 2 * sizeof(float)));
+    CU_TRY(h, cudaMalloc((void**)&h->d_reward, n * sizeof(float)));
+    CU_TRY(h, cudaMalloc((void**)&h->d_flags, 2 * n));
+    CU_TRY(h, cudaMalloc((void**)&h->d_tobs, n * OBS_DIM * sizeof(float)));
+    CU_TRY(h, cudaMemset(h->d_tobs, 0, n * OBS_DIM * sizeof(float)));
+    CU_TRY(h, cudaMalloc((void**)&h->d_obs, n * OBS_DIM * sizeof(float)));
+    CU_TRY(h, cudaMemset(h->d_obs, 0, n * OBS_DIM * sizeof(float)));
+    return USV_OK;
+}
+
+int usvgpu_use_staging(usvgpu_handle h, float* actions, float* obs, float* reward, uint8_t* flags, float* terminal_obs) {
+    if (!h) return USV_ERR_INVALID;
+    if (!actions || !obs || !reward || !flags || !terminal_obs) return fail(h, USV_ERR_INVALID, "NULL staging buffer");
+    if (h->d_obs && h->own_staging) {
+        cudaSetDevice(h->device);
+        cudaDeviceSynchronize();
+        cudaFree(h->d_actions);
+        cudaFree(h->d_obs);
+        cudaFree(h->d_tobs);
+        cudaFree(h->d_reward);
+        cudaFree(h->d_flags);
+    }
+    h->own_staging = false;
+    h->d_actions = actions;
+    h->d_obs = obs;
+    h->d_reward = reward;
+    h->d_flags = flags;
+    h->d_tobs = terminal_obs;
+    return USV_OK;
+}
+
+int usvgpu_host_alloc(void** out, int64_t bytes) {
+    if (!out || bytes <= 0) return fail(nullptr, USV_ERR_INVALID, "bad host_alloc arguments");
+    CU_TRY(nullptr, cudaHostAlloc(out, (size_t)bytes, cudaHostAllocPortable | cudaHostAllocMapped));
+    return USV_OK;
+}
+
+int usvgpu_host_free(void* p) {
+    if (p) CU_TRY(nullptr, cudaFreeHost(p));
+    return USV_OK;
+}
+
+int usvgpu_reset_host(usvgpu_handle h, const uint8_t* mask_host, float* obs_host, void* stream) {
+    if (!h || !obs_host) return USV_ERR_INVALID;
+    CU_TRY(h, cudaSetDevice(h->device));
+    int rc = ensure_staging(h);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t n = (size_t)h->sp.n;
+    const uint8_t* mask = nullptr;
+    if (mask_host) {
+        CU_TRY(h, cudaMemcpyAsync(h->d_flags, mask_host, n, cudaMemcpyHostToDevice, st));
+        mask = h->d_flags;
+    }
+    rc = usvgpu_reset(h, mask, h->d_obs, stream);
+    if (rc) return rc;
+    CU_TRY(h, cudaMemcpyAsync(obs_host, h->d_obs, n * OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU_TRY(h, cudaStreamSynchronize(st));
+    return USV_OK;
+}
+
+int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host, float* reward_host,
+                     uint8_t* terminated_host, uint8_t* truncated_host, int32_t mapped_obs, void* stream) {
+    if (!h) return USV_ERR_INVALID;
+    if (!actions_host || !obs_host || !reward_host || !terminated_host || !truncated_host)
+        return fail(h, USV_ERR_INVALID, "NULL buffer");
+    CU_TRY(h, cudaSetDevice(h->device));
+    int rc = ensure_staging(h);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t n = (size_t)h->sp.n;
+    CU_TRY(h, cudaMemcpyAsync(h->d_actions, actions_host, n * 2 * sizeof(float), cudaMemcpyHostToDevice, st));
+    float* obs_dst = h->d_obs;
+    if (mapped_obs) {  // the sensor kernel stores the rows straight into the caller's page-locked, mapped buffer
+        void* dp = nullptr;
+        CU_TRY(h, cudaHostGetDevicePointer(&dp, obs_host, 0));
+        obs_dst = (float*)dp;
+    }
+    rc = step_impl(h, h->d_actions, obs_dst, h->d_reward, h->d_flags, h->d_flags + n, h->d_tobs, st);
+    if (rc) return rc;
+    CU_TRY(h, cudaMemcpyAsync(reward_host, h->d_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU_TRY(h, cudaMemcpyAsync(terminated_host, h->d_flags, n, cudaMemcpyDeviceToHost, st));
+    CU_TRY(h, cudaMemcpyAsync(truncated_host, h->d_flags + n, n, cudaMemcpyDeviceToHost, st));
+    if (!mapped_obs)
+        CU_TRY(h, cudaMemcpyAsync(obs_host, h->d_obs, n * OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st));
+    return USV_OK;
+}
+
+int usvgpu_stream_sync(usvgpu_handle h, void* stream) {
+    if (!h) return USV_ERR_INVALID;
+    CU_TRY(h, cudaSetDevice(h->device));
+    CU_TRY(h, cudaStreamSynchronize((cudaStream_t)stream));
+    return USV_OK;
+}
+
+int usvgpu_terminal_obs_host(usvgpu_handle h, const int32_t* index_host, int64_t n_index, float* rows_host,
+                             void* stream) {
+    if (!h || !index_host || !rows_host || n_index < 0) return USV_ERR_INVALID;
+    if (n_index == 0) return USV_OK;
+    if (!h->d_tobs) return fail(h, USV_ERR_INVALID, "no usvgpu_step_host() has run on this handle");
+    if (n_index > h->sp.n) return fail(h, USV_ERR_INVALID, "more indices than envs");
+    CU_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_index > h->gather_cap) {
+        int64_t cap = h->gather_cap ? h->gather_cap : 1024;
+        while (cap < n_index) cap *= 2;
+        if (cap > h->sp.n) cap = h->sp.n;
+        CU_TRY(h, cudaStreamSynchronize(st));
+        cudaFree(h->d_idx);
+        cudaFree(h->d_rows);
+        h->d_idx = nullptr;
+        h->d_rows = nullptr;
+        h->gather_cap = 0;
+        CU_TRY(h, cudaMalloc((void**)&h->d_idx, (size_t)cap * sizeof(int32_t)));
+        CU_TRY(h, cudaMalloc((void**)&h->d_rows, (size_t)cap * OBS_DIM * sizeof(float)));
+        h->gather_cap = cap;
+    }
+    CU_TRY(h, cudaMemcpyAsync(h->d_idx, index_host, (size_t)n_index * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    gather_rows_kernel<<<(unsigned)((n_index + 7) / 8), 256, 0, st>>>(h->d_tobs, h->d_idx, n_index, h->sp.n, h->d_rows);
+    CU_TRY(h, cudaGetLastError());
+    CU_TRY(h, cudaMemcpyAsync(rows_host, h->d_rows, (size_t)n_index * OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU_TRY(h, cudaStreamSynchronize(st));
     return USV_OK;
 }
 

@@ -54,7 +54,7 @@ class UsvGpuVecEnv:
                  ignore_obstacles: bool = False, do_perturb: bool = False, skip_kinematic: bool = False,
                  max_episode_steps: Optional[int] = None, auto_reset: bool = True, precision: str = "f64",
                  obstacles_f32: bool = False, global_env_offset: int = 0, info_mode: str = "list",
-                 render_mode: Optional[str] = None):
+                 render_mode: Optional[str] = None, copy_host_outputs: bool = False, mapped_obs: bool = False):
         if not torch.cuda.is_available():
             raise nat.UsvError("UsvGpuVecEnv needs a CUDA device: there is no CPU fallback")
         self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
@@ -83,21 +83,28 @@ class UsvGpuVecEnv:
             self.obs = torch.zeros((n, nat.OBS_DIM), dtype=torch.float32, device=self.device)
             self.terminal_obs = torch.zeros((n, nat.OBS_DIM), dtype=torch.float32, device=self.device)
             self.reward = torch.zeros(n, dtype=torch.float32, device=self.device)
-            self.terminated = torch.zeros(n, dtype=torch.uint8, device=self.device)
-            self.truncated = torch.zeros(n, dtype=torch.uint8, device=self.device)
+            self._flags = torch.zeros((2, n), dtype=torch.uint8, device=self.device)
+            self.terminated, self.truncated = self._flags[0], self._flags[1]
             self._actions_dev = torch.zeros((n, nat.ACT_DIM), dtype=torch.float32, device=self.device)
-        # pinned host mirrors for the numpy face
-        self._h_actions = torch.zeros((n, nat.ACT_DIM), dtype=torch.float32).pin_memory()
-        self._h_obs = torch.zeros((n, nat.OBS_DIM), dtype=torch.float32).pin_memory()
-        self._h_reward = torch.zeros(n, dtype=torch.float32).pin_memory()
-        self._h_term = torch.zeros(n, dtype=torch.uint8).pin_memory()
-        self._h_trunc = torch.zeros(n, dtype=torch.uint8).pin_memory()
+        self._bind_staging()
+        # page-locked host buffers of the numpy face, allocated on first use: two sets, used alternately, so the
+        # arrays step() returned stay valid while the next step is computed (copy_host_outputs=True hands out
+        # private copies instead)
+        self._host = None
+        self._slot = 0
+        self.copy_host_outputs = bool(copy_host_outputs)
+        self.mapped_obs = bool(mapped_obs)
         self._pending = None
         self._ep_ret = np.zeros(n, dtype=np.float64)   # host-side episode bookkeeping for infos['episode']
         self._ep_len = np.zeros(n, dtype=np.int64)
         self._closed = False
 
     # ------------------------------------------------------------------ plumbing
+    def _bind_staging(self):
+        # the host-buffer face stages through the same device tensors as the tensor face
+        nat.check(self._lib.usvgpu_use_staging(self._h, *[C.c_void_p(t.data_ptr()) for t in (
+            self._actions_dev, self.obs, self.reward, self._flags, self.terminal_obs)]), self._h)
+
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
@@ -112,8 +119,34 @@ class UsvGpuVecEnv:
 
     def close(self):
         if not self._closed and self._h:
+            if self._host is not None:
+                torch.cuda.synchronize(self.device)
+                for ptr in self._host_ptrs:
+                    self._lib.usvgpu_host_free(ptr)
+                self._host = None
             self._lib.usvgpu_destroy(self._h)
             self._closed = True
+
+    def _host_array(self, shape, dtype):
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        ptr = C.c_void_p()
+        nat.check(self._lib.usvgpu_host_alloc(C.byref(ptr), nbytes))
+        self._host_ptrs.append(ptr)
+        buf = (C.c_char * nbytes).from_address(ptr.value)
+        arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+        arr[...] = 0
+        return arr
+
+    def _host_buffers(self):
+        if self._host is None:
+            n = self.num_envs
+            self._host_ptrs = []
+            self._host = [{"actions": self._host_array((n, nat.ACT_DIM), np.float32),
+                           "obs": self._host_array((n, nat.OBS_DIM), np.float32),
+                           "reward": self._host_array((n,), np.float32),
+                           "term": self._host_array((n,), np.uint8),
+                           "trunc": self._host_array((n,), np.uint8)} for _ in range(2)]
+        return self._host
 
     # ------------------------------------------------------------------ device-resident face
     def reset_tensor(self, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -161,30 +194,31 @@ class UsvGpuVecEnv:
 
     # ------------------------------------------------------------------ SB3 VecEnv face (host numpy)
     def reset(self) -> np.ndarray:
-        self.reset_tensor()
+        hb = self._host_buffers()[self._slot]
+        self._check(self._lib.usvgpu_reset_host(self._h, None, hb["obs"].ctypes.data_as(C.c_void_p), self._stream()))
         self._ep_ret[:] = 0
         self._ep_len[:] = 0
-        return self.obs.cpu().numpy()
+        return hb["obs"].copy() if self.copy_host_outputs else hb["obs"]
 
     def step_async(self, actions) -> None:
-        a = np.asarray(actions, dtype=np.float32).reshape(self.num_envs, nat.ACT_DIM)
-        self._h_actions.numpy()[...] = a
-        self._actions_dev.copy_(self._h_actions, non_blocking=True)
-        self.step_tensor(self._actions_dev)
-        self._h_obs.copy_(self.obs, non_blocking=True)
-        self._h_reward.copy_(self.reward, non_blocking=True)
-        self._h_term.copy_(self.terminated, non_blocking=True)
-        self._h_trunc.copy_(self.truncated, non_blocking=True)
+        self._slot ^= 1
+        hb = self._host_buffers()[self._slot]
+        hb["actions"][...] = np.asarray(actions, dtype=np.float32).reshape(self.num_envs, nat.ACT_DIM)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        self._check(self._lib.usvgpu_step_host(self._h, p(hb["actions"]), p(hb["obs"]), p(hb["reward"]),
+                                               p(hb["term"]), p(hb["trunc"]), int(self.mapped_obs), self._stream()))
         self._pending = True
 
     def step_wait(self):
         assert self._pending, "step_wait() without step_async()"
-        torch.cuda.current_stream(self.device).synchronize()
+        self._check(self._lib.usvgpu_stream_sync(self._h, self._stream()))
         self._pending = None
-        obs = self._h_obs.numpy().copy()
-        rew = self._h_reward.numpy().copy()
-        term = self._h_term.numpy().astype(bool)
-        trunc = self._h_trunc.numpy().astype(bool)
+        hb = self._host[self._slot]
+        obs, rew = hb["obs"], hb["reward"]
+        if self.copy_host_outputs:
+            obs, rew = obs.copy(), rew.copy()
+        term = hb["term"].view(np.bool_)
+        trunc = hb["trunc"].view(np.bool_)
         dones = term | trunc
         self._ep_ret += rew
         self._ep_len += 1
@@ -192,7 +226,10 @@ class UsvGpuVecEnv:
         payload = []
         if done_idx.size:
             if self.cfg.auto_reset:
-                tob = self.terminal_obs[torch.as_tensor(done_idx, device=self.device)].cpu().numpy()
+                idx32 = done_idx.astype(np.int32)
+                tob = np.empty((done_idx.size, nat.OBS_DIM), dtype=np.float32)
+                self._check(self._lib.usvgpu_terminal_obs_host(self._h, idx32.ctypes.data_as(C.c_void_p), idx32.size,
+                                                               tob.ctypes.data_as(C.c_void_p), self._stream()))
             for k, i in enumerate(done_idx):
                 info = {"TimeLimit.truncated": bool(trunc[i] and not term[i]),
                         "episode": {"r": float(self._ep_ret[i]), "l": int(self._ep_len[i])}}
@@ -223,6 +260,7 @@ class UsvGpuVecEnv:
             self._h = C.c_void_p()
             nat.check(self._lib.usvgpu_create(C.byref(self.cfg), self._dev_index, self.num_envs,
                                               self.global_env_offset, self._seed, C.byref(self._h)))
+            self._bind_staging()
         return [None if seed is None else seed + i for i in range(self.num_envs)]
 
     def _indices(self, indices) -> Iterable[int]:

@@ -138,6 +138,28 @@ int usvgpu_step_timed(usvgpu_handle h, const float* actions, float* obs, float* 
 int usvgpu_rollout(usvgpu_handle h, const float* actions, int32_t n_steps, int32_t action_wrap, float* obs,
                    float* reward, uint8_t* terminated, uint8_t* truncated, void* stream);
 
+/* ---- host-buffer face: what stock SB3 does with a VecEnv (numpy actions in, numpy observations out;
+ * DummyVecEnv.step_wait, train_test/sb3_train_vec.py:67).  All pointers below are HOST memory.  The handle owns the
+ * device staging buffers.  Buffers should be page-locked (usvgpu_host_alloc, cudaHostRegister or torch
+ * pin_memory) so that the copies run asynchronously on `stream`; pageable memory works but is staged by the
+ * driver.  usvgpu_step_host only ENQUEUES (H2D actions, the two kernels, D2H reward / flags / observations):
+ * read the outputs after usvgpu_stream_sync().  mapped_obs != 0: obs_host must come from usvgpu_host_alloc; the
+ * sensor kernel then stores the observation rows straight into it over PCIe (no staging copy of the 572 B rows). */
+/* Optional: make the host-buffer face stage through the CALLER's device buffers (actions [N][2], obs [N][143],
+ * reward [N] float32, flags uint8 [2][N] = terminated then truncated, terminal_obs [N][143]) instead of
+ * handle-owned ones, so that a caller mixing usvgpu_step and usvgpu_step_host sees one set of buffers. */
+int usvgpu_use_staging(usvgpu_handle h, float* actions, float* obs, float* reward, uint8_t* flags, float* terminal_obs);
+int usvgpu_host_alloc(void** out, int64_t bytes);
+int usvgpu_host_free(void* p);
+int usvgpu_reset_host(usvgpu_handle h, const uint8_t* mask_host, float* obs_host, void* stream); /* synchronises */
+int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host, float* reward_host,
+                     uint8_t* terminated_host, uint8_t* truncated_host, int32_t mapped_obs, void* stream);
+int usvgpu_stream_sync(usvgpu_handle h, void* stream);
+/* SB3 infos[i]["terminal_observation"] for the n_index envs listed in index_host (those whose flags came back set
+ * from the last usvgpu_step_host): rows_host float32 [n_index][143].  Synchronises `stream`. */
+int usvgpu_terminal_obs_host(usvgpu_handle h, const int32_t* index_host, int64_t n_index, float* rows_host,
+                             void* stream);
+
 /* Copy a whole field group out of / into the handle.  buf may be host or device memory
  * (cudaMemcpyDefault); size is checked against usvgpu_field_bytes(). */
 int64_t usvgpu_field_bytes(usvgpu_handle h, int32_t field);

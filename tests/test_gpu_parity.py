@@ -451,6 +451,37 @@ def test_vecenv_host_face_sb3_semantics(usv):
     env.close()
 
 
+@pytest.mark.parametrize("mapped_obs", [False, True])
+def test_host_face_equals_tensor_face(usv, mapped_obs):
+    """usvgpu_step_host (numpy in / numpy out, page-locked double buffers, optional mapped observation stores) gives
+    bit-identical results to usvgpu_step on device tensors, including the terminal observations of finished envs."""
+    N, T = 3000, 40
+    et = usv.UsvGpuVecEnv(N, device=0, seed=9, max_episode_steps=11)
+    eh = usv.UsvGpuVecEnv(N, device=0, seed=9, max_episode_steps=11, mapped_obs=mapped_obs, info_mode="lazy")
+    ot = et.reset_tensor().cpu().numpy()
+    oh = eh.reset()
+    assert np.array_equal(ot, oh)
+    prev = None
+    n_done = 0
+    for t in range(T):
+        a = action_stream(N, seed=100 + t)
+        obs_t, rew_t, term_t, trunc_t = [x.cpu().numpy() for x in et.step_tensor(torch.tensor(a, device=et.device))]
+        tob_t = et.terminal_obs.cpu().numpy()
+        obs, rew, dones, infos = eh.step(a)
+        assert np.array_equal(obs, obs_t) and np.array_equal(rew, rew_t)
+        assert np.array_equal(dones, (term_t | trunc_t).astype(bool))
+        for i in np.flatnonzero(dones):
+            n_done += 1
+            assert np.array_equal(infos[i]["terminal_observation"], tob_t[i])
+            assert infos[i]["TimeLimit.truncated"] == bool(trunc_t[i] and not term_t[i])
+        if prev is not None:  # the arrays of the previous step are still intact (double buffering)
+            assert np.array_equal(prev[0], prev[1])
+        prev = (obs, obs_t.copy())
+    assert n_done >= 3 * N
+    et.close()
+    eh.close()
+
+
 def test_rollout_entry_matches_step_loop(usv):
     N, K = 4096, 12
     dev = torch.device("cuda", 0)
