@@ -37,8 +37,8 @@ template <bool PERTURB>
 __global__ void __launch_bounds__(DYN_B, DYN_MIN_CTAS)
 dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     const long long n = s.n;
-    const long long i = (long long)blockIdx.x * DYN_B + threadIdx.x;
-    if (i >= n) return;
+    const long long i = fl.lo + (long long)blockIdx.x * DYN_B + threadIdx.x;
+    if (i >= fl.hi) return;
 
     // ---- load state (coalesced SoA columns) -------------------------------------------------
     double* dyn = s.dyn + i;
@@ -220,9 +220,9 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
     __shared__ SensorScratch scratch[OBST ? SENS_WARPS : 1];
     __shared__ SensorStage<ObT> stage[SENS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long n = s.n;
+    const long long n = fl.hi;
     const long long stride = (long long)gridDim.x * SENS_WARPS;
-    long long i = (long long)blockIdx.x * SENS_WARPS + warp;
+    long long i = fl.lo + (long long)blockIdx.x * SENS_WARPS + warp;
     SensorStage<ObT>& st = stage[warp];
     if (i < n) sensor_prefetch<OBST, ObT>(st, s, i, lane);
     if (OBST) {
@@ -268,8 +268,10 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
             if (done) {
                 const double ep_ret = s.ep_return[i] + rew;
                 DeviceStats* ds = s.stats;
+                const double ep_len = (double)s.steps[i];
+                s.ep_done[i] = make_double2(ep_ret, ep_len);
                 atomicAdd(&ds->return_sum, ep_ret);
-                atomicAdd(&ds->length_sum, (double)s.steps[i]);
+                atomicAdd(&ds->length_sum, ep_len);
                 atomicAdd(&ds->episodes, 1ull);
                 if (term) atomicAdd(&ds->terminated, 1ull);
                 if (oob) atomicAdd(&ds->out_of_bounds, 1ull);
@@ -321,14 +323,15 @@ __global__ void reset_kernel(StatePtrs s, const uint8_t* __restrict__ mask, floa
 // one warp per row, 8 rows per CTA
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-gather_rows_kernel(const float* __restrict__ src, const int* __restrict__ index, long long n_index, long long n,
-                   float* __restrict__ rows) {
+gather_rows_kernel(const float* __restrict__ src, const double2* __restrict__ ep_done, const int* __restrict__ index,
+                   long long n_index, long long n, float* __restrict__ rows, double2* __restrict__ ep_out) {
     const long long k = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (k >= n_index) return;
     const int lane = threadIdx.x & 31;
     const long long i = index[k];
     if (i < 0 || i >= n) return;
     for (int c = lane; c < OBS_DIM; c += 32) rows[k * OBS_DIM + c] = src[i * OBS_DIM + c];
+    if (lane == 0) ep_out[k] = ep_done[i];
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -69,6 +69,7 @@ struct StatePtrs {
     int* steps;         // [n]
     int* episode;       // [n]
     double* ep_return;  // [n]
+    double2* ep_done;   // [n]  (return, length) of the env's last finished episode (SB3 infos[i]["episode"])
     Hand* hand;         // [n]      dynamics -> sensor hand-over
     float* hdr16;       // [n][16]  observation header rows
     DeviceStats* stats;
@@ -80,6 +81,8 @@ struct StatePtrs {
 
 struct StepFlags {
     int do_perturb, skip_kinematic, max_episode_steps, auto_reset;
+    long long lo, hi;  // env range [lo, hi) of this launch: the host-buffer face steps a shard in chunks so that the
+                       // copy-out of one chunk overlaps the kernels of the next
 };
 
 template <typename ObT>

@@ -24,6 +24,8 @@
 // =================================================================================================
 using namespace usv;
 
+constexpr int HOST_CHUNKS_MAX = 16;
+
 struct UsvGpu {
     UsvConfig cfg;
     int device;
@@ -39,9 +41,16 @@ struct UsvGpu {
     float* d_tobs;
     float* d_reward;
     uint8_t* d_flags;   // terminated[N] then truncated[N]
-    int32_t* d_idx;     // gather list for usvgpu_terminal_obs_host
-    float* d_rows;      // gathered rows
+    int32_t* h_idx;     // page-locked, mapped: gather list of usvgpu_terminal_obs_host
+    float* h_rows;      // page-locked, mapped: gathered rows (the gather kernel stores them over PCIe)
+    double2* h_ep;      // page-locked, mapped: (return, length) of the finished episodes
     int64_t gather_cap;
+    cudaStream_t side;      // the gather runs here, beside the observation copies
+    cudaStream_t copy;      // observation chunks go home on this stream while the caller's stream computes the next chunk
+    cudaEvent_t ev_chunk[HOST_CHUNKS_MAX];
+    cudaEvent_t ev_copied;
+    int host_chunks;
+    cudaEvent_t ev_flags;   // reward / flags of the last usvgpu_step_host have reached the host
     bool own_staging;   // false after usvgpu_use_staging(): the caller's device buffers are used instead
 };
 
@@ -81,7 +90,7 @@ static int check_device(UsvGpu* h, int device) {
 template <bool OBST, typename ObT>
 static void launch_sensor(UsvGpu* h, const StepFlags& fl, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
                           float* tobs, cudaStream_t st) {
-    const long long need = (h->sp.n + SENS_WARPS - 1) / SENS_WARPS;
+    const long long need = (fl.hi - fl.lo + SENS_WARPS - 1) / SENS_WARPS;
     const long long resident = (long long)h->sm_count * SENS_MIN_CTAS;  // persistent: one wave, warps loop over envs
     const unsigned blocks = (unsigned)(need < resident ? need : resident);
     sensor_kernel<OBST, ObT><<<blocks, SENS_WARPS * 32, 0, st>>>(h->sp, fl, obs, reward, term, trunc, tobs);
@@ -89,9 +98,10 @@ static void launch_sensor(UsvGpu* h, const StepFlags& fl, float* obs, float* rew
 
 // One VecEnv.step(): dynamics_kernel (thread per env) then sensor_kernel (warp per env), stream-ordered.
 static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
-                     float* tobs, cudaStream_t st, cudaEvent_t mid = nullptr) {
-    const StepFlags fl = {h->cfg.do_perturb, h->cfg.skip_kinematic, h->cfg.max_episode_steps, h->cfg.auto_reset};
-    const unsigned dblocks = (unsigned)((h->sp.n + DYN_B - 1) / DYN_B);
+                     float* tobs, cudaStream_t st, cudaEvent_t mid = nullptr, long long lo = 0, long long hi = -1) {
+    if (hi < 0) hi = h->sp.n;
+    const StepFlags fl = {h->cfg.do_perturb, h->cfg.skip_kinematic, h->cfg.max_episode_steps, h->cfg.auto_reset, lo, hi};
+    const unsigned dblocks = (unsigned)((hi - lo + DYN_B - 1) / DYN_B);
     if (h->cfg.do_perturb) dynamics_kernel<true><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
     else dynamics_kernel<false><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
     cudaError_t e = cudaGetLastError();
@@ -107,7 +117,7 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
     }
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("sensor launch: ") + cudaGetErrorString(e));
-    h->host_env_steps += (unsigned long long)h->sp.n;
+    h->host_env_steps += (unsigned long long)(hi - lo);
     h->launches += 2;
     return USV_OK;
 }
@@ -149,10 +159,17 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->launches = 0;
     h->obst_elem = cfg->obstacles_f32 ? sizeof(float) : sizeof(double);
     h->sm_count = 148;
-    h->d_actions = h->d_obs = h->d_tobs = h->d_reward = h->d_rows = nullptr;
+    h->d_actions = h->d_obs = h->d_tobs = h->d_reward = h->h_rows = nullptr;
     h->d_flags = nullptr;
-    h->d_idx = nullptr;
+    h->h_idx = nullptr;
+    h->h_ep = nullptr;
     h->gather_cap = 0;
+    h->side = nullptr;
+    h->copy = nullptr;
+    h->ev_flags = nullptr;
+    h->ev_copied = nullptr;
+    for (int c = 0; c < HOST_CHUNKS_MAX; ++c) h->ev_chunk[c] = nullptr;
+    h->host_chunks = 2;
     h->own_staging = true;
     cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
     memset(&h->sp, 0, sizeof(h->sp));
@@ -172,6 +189,7 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     alloc((void**)&h->sp.steps, n * sizeof(int));
     alloc((void**)&h->sp.episode, n * sizeof(int));
     alloc((void**)&h->sp.ep_return, n * sizeof(double));
+    alloc((void**)&h->sp.ep_done, n * sizeof(double2));
     alloc((void**)&h->sp.hand, n * sizeof(Hand));
     alloc((void**)&h->sp.hdr16, n * HDR_PAD * sizeof(float));
     alloc((void**)&h->sp.stats, sizeof(DeviceStats));
@@ -203,6 +221,7 @@ int usvgpu_destroy(usvgpu_handle h) {
     cudaFree(h->sp.steps);
     cudaFree(h->sp.episode);
     cudaFree(h->sp.ep_return);
+    cudaFree(h->sp.ep_done);
     cudaFree(h->sp.hand);
     cudaFree(h->sp.hdr16);
     cudaFree(h->sp.stats);
@@ -214,8 +233,15 @@ int usvgpu_destroy(usvgpu_handle h) {
         cudaFree(h->d_reward);
         cudaFree(h->d_flags);
     }
-    cudaFree(h->d_idx);
-    cudaFree(h->d_rows);
+    if (h->h_idx) cudaFreeHost(h->h_idx);
+    if (h->h_rows) cudaFreeHost(h->h_rows);
+    if (h->h_ep) cudaFreeHost(h->h_ep);
+    if (h->side) cudaStreamDestroy(h->side);
+    if (h->copy) cudaStreamDestroy(h->copy);
+    if (h->ev_flags) cudaEventDestroy(h->ev_flags);
+    if (h->ev_copied) cudaEventDestroy(h->ev_copied);
+    for (int c = 0; c < HOST_CHUNKS_MAX; ++c)
+        if (h->ev_chunk[c]) cudaEventDestroy(h->ev_chunk[c]);
     delete h;
     return USV_OK;
 }
@@ -280,6 +306,12 @@ int usvgpu_rollout(usvgpu_handle h, const float* actions, int32_t n_steps, int32
 
 // ---- host-buffer face: what stock SB3 does with a VecEnv (numpy actions in, numpy observations out) ----------
 static int ensure_staging(UsvGpu* h) {
+    if (!h->side) CU_TRY(h, cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
+    if (!h->ev_flags) CU_TRY(h, cudaEventCreateWithFlags(&h->ev_flags, cudaEventDisableTiming));
+    if (!h->copy) CU_TRY(h, cudaStreamCreateWithFlags(&h->copy, cudaStreamNonBlocking));
+    if (!h->ev_copied) CU_TRY(h, cudaEventCreateWithFlags(&h->ev_copied, cudaEventDisableTiming));
+    for (int c = 0; c < HOST_CHUNKS_MAX; ++c)
+        if (!h->ev_chunk[c]) CU_TRY(h, cudaEventCreateWithFlags(&h->ev_chunk[c], cudaEventDisableTiming));
     if (h->d_obs) return USV_OK;
     const size_t n = (size_t)h->sp.n;
     CU_TRY(h, cudaMalloc((void**)&h->d_actions, n * 2 * sizeof(float)));
@@ -354,19 +386,56 @@ int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n = (size_t)h->sp.n;
     CU_TRY(h, cudaMemcpyAsync(h->d_actions, actions_host, n * 2 * sizeof(float), cudaMemcpyHostToDevice, st));
-    float* obs_dst = h->d_obs;
     if (mapped_obs) {  // the sensor kernel stores the rows straight into the caller's page-locked, mapped buffer
         void* dp = nullptr;
         CU_TRY(h, cudaHostGetDevicePointer(&dp, obs_host, 0));
-        obs_dst = (float*)dp;
+        rc = step_impl(h, h->d_actions, (float*)dp, h->d_reward, h->d_flags, h->d_flags + n, h->d_tobs, st);
+        if (rc) return rc;
+    } else {
+        // Chunks of envs: while the copy engine takes chunk c's observation rows home (37.5 MB per 65 536 envs: the
+        // PCIe link is what bounds this face), the SMs compute chunk c + 1.
+        // The first chunk is small (1/8 of the shard) so that the copy engine starts early; the rest is split evenly.
+        int chunks = h->host_chunks;
+        if ((long long)n < 8192LL * chunks) chunks = 1;
+        const long long first = chunks > 1 ? ((long long)n / 8 + 255) / 256 * 256 : (long long)n;
+        const long long per = chunks > 1 ? (((long long)n - first + chunks - 2) / (chunks - 1) + 255) / 256 * 256 : 0;
+        long long lo = 0;
+        for (int c = 0; c < chunks && lo < (long long)n; ++c) {
+            long long hi = lo + (c == 0 ? first : per);
+            if (hi > (long long)n || c == chunks - 1) hi = (long long)n;
+            rc = step_impl(h, h->d_actions, h->d_obs, h->d_reward, h->d_flags, h->d_flags + n, h->d_tobs, st, nullptr, lo, hi);
+            if (rc) return rc;
+            CU_TRY(h, cudaEventRecord(h->ev_chunk[c], st));
+            CU_TRY(h, cudaStreamWaitEvent(h->copy, h->ev_chunk[c], 0));
+            // the one device-to-host copy engine serves its queue in order: reward and flags of the whole shard go
+            // just before the LAST chunk's rows, so the host has them (ev_flags) while those rows are in flight
+            const size_t m = (size_t)(hi - lo);
+            if (hi == (long long)n) {
+                CU_TRY(h, cudaMemcpyAsync(reward_host, h->d_reward, n * sizeof(float), cudaMemcpyDeviceToHost, h->copy));
+                CU_TRY(h, cudaMemcpyAsync(terminated_host, h->d_flags, n, cudaMemcpyDeviceToHost, h->copy));
+                CU_TRY(h, cudaMemcpyAsync(truncated_host, h->d_flags + n, n, cudaMemcpyDeviceToHost, h->copy));
+                CU_TRY(h, cudaEventRecord(h->ev_flags, h->copy));
+            }
+            CU_TRY(h, cudaMemcpyAsync(obs_host + lo * OBS_DIM, h->d_obs + lo * OBS_DIM, m * OBS_DIM * sizeof(float),
+                                      cudaMemcpyDeviceToHost, h->copy));
+            lo = hi;
+        }
+        CU_TRY(h, cudaEventRecord(h->ev_copied, h->copy));
     }
-    rc = step_impl(h, h->d_actions, obs_dst, h->d_reward, h->d_flags, h->d_flags + n, h->d_tobs, st);
-    if (rc) return rc;
-    CU_TRY(h, cudaMemcpyAsync(reward_host, h->d_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st));
-    CU_TRY(h, cudaMemcpyAsync(terminated_host, h->d_flags, n, cudaMemcpyDeviceToHost, st));
-    CU_TRY(h, cudaMemcpyAsync(truncated_host, h->d_flags + n, n, cudaMemcpyDeviceToHost, st));
-    if (!mapped_obs)
-        CU_TRY(h, cudaMemcpyAsync(obs_host, h->d_obs, n * OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (mapped_obs) {
+        CU_TRY(h, cudaMemcpyAsync(reward_host, h->d_reward, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CU_TRY(h, cudaMemcpyAsync(terminated_host, h->d_flags, n, cudaMemcpyDeviceToHost, st));
+        CU_TRY(h, cudaMemcpyAsync(truncated_host, h->d_flags + n, n, cudaMemcpyDeviceToHost, st));
+        CU_TRY(h, cudaEventRecord(h->ev_flags, st));
+    }
+    if (!mapped_obs) CU_TRY(h, cudaStreamWaitEvent(st, h->ev_copied, 0));  // `stream` is done when the rows are home
+    return USV_OK;
+}
+
+int usvgpu_set_host_chunks(usvgpu_handle h, int32_t chunks) {
+    if (!h) return USV_ERR_INVALID;
+    if (chunks < 1 || chunks > HOST_CHUNKS_MAX) return fail(h, USV_ERR_INVALID, "host chunks must be in 1..16");
+    h->host_chunks = chunks;
     return USV_OK;
 }
 
@@ -377,33 +446,53 @@ int usvgpu_stream_sync(usvgpu_handle h, void* stream) {
     return USV_OK;
 }
 
+int usvgpu_flags_sync(usvgpu_handle h) {
+    if (!h) return USV_ERR_INVALID;
+    if (!h->ev_flags) return fail(h, USV_ERR_INVALID, "no usvgpu_step_host() has run on this handle");
+    CU_TRY(h, cudaSetDevice(h->device));
+    CU_TRY(h, cudaEventSynchronize(h->ev_flags));
+    return USV_OK;
+}
+
 int usvgpu_terminal_obs_host(usvgpu_handle h, const int32_t* index_host, int64_t n_index, float* rows_host,
-                             void* stream) {
+                             double* episode_host) {
     if (!h || !index_host || !rows_host || n_index < 0) return USV_ERR_INVALID;
     if (n_index == 0) return USV_OK;
-    if (!h->d_tobs) return fail(h, USV_ERR_INVALID, "no usvgpu_step_host() has run on this handle");
+    if (!h->d_tobs || !h->ev_flags) return fail(h, USV_ERR_INVALID, "no usvgpu_step_host() has run on this handle");
     if (n_index > h->sp.n) return fail(h, USV_ERR_INVALID, "more indices than envs");
     CU_TRY(h, cudaSetDevice(h->device));
-    cudaStream_t st = (cudaStream_t)stream;
     if (n_index > h->gather_cap) {
         int64_t cap = h->gather_cap ? h->gather_cap : 1024;
         while (cap < n_index) cap *= 2;
         if (cap > h->sp.n) cap = h->sp.n;
-        CU_TRY(h, cudaStreamSynchronize(st));
-        cudaFree(h->d_idx);
-        cudaFree(h->d_rows);
-        h->d_idx = nullptr;
-        h->d_rows = nullptr;
+        CU_TRY(h, cudaStreamSynchronize(h->side));
+        if (h->h_idx) cudaFreeHost(h->h_idx);
+        if (h->h_rows) cudaFreeHost(h->h_rows);
+        if (h->h_ep) cudaFreeHost(h->h_ep);
+        h->h_idx = nullptr;
+        h->h_rows = nullptr;
+        h->h_ep = nullptr;
         h->gather_cap = 0;
-        CU_TRY(h, cudaMalloc((void**)&h->d_idx, (size_t)cap * sizeof(int32_t)));
-        CU_TRY(h, cudaMalloc((void**)&h->d_rows, (size_t)cap * OBS_DIM * sizeof(float)));
+        CU_TRY(h, cudaHostAlloc((void**)&h->h_idx, (size_t)cap * sizeof(int32_t), cudaHostAllocMapped));
+        CU_TRY(h, cudaHostAlloc((void**)&h->h_rows, (size_t)cap * OBS_DIM * sizeof(float), cudaHostAllocMapped));
+        CU_TRY(h, cudaHostAlloc((void**)&h->h_ep, (size_t)cap * sizeof(double2), cudaHostAllocMapped));
         h->gather_cap = cap;
     }
-    CU_TRY(h, cudaMemcpyAsync(h->d_idx, index_host, (size_t)n_index * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-    gather_rows_kernel<<<(unsigned)((n_index + 7) / 8), 256, 0, st>>>(h->d_tobs, h->d_idx, n_index, h->sp.n, h->d_rows);
+    // The kernels of the step are complete once the flags are on the host (the caller saw them); the gather runs on
+    // the side stream, reading the list from and storing the rows to mapped host memory, while the copy engine is
+    // still busy with the observations on the caller's stream.
+    CU_TRY(h, cudaStreamWaitEvent(h->side, h->ev_flags, 0));
+    memcpy(h->h_idx, index_host, (size_t)n_index * sizeof(int32_t));
+    void *d_idx = nullptr, *d_rows = nullptr, *d_ep = nullptr;
+    CU_TRY(h, cudaHostGetDevicePointer(&d_idx, h->h_idx, 0));
+    CU_TRY(h, cudaHostGetDevicePointer(&d_rows, h->h_rows, 0));
+    CU_TRY(h, cudaHostGetDevicePointer(&d_ep, h->h_ep, 0));
+    gather_rows_kernel<<<(unsigned)((n_index + 7) / 8), 256, 0, h->side>>>(h->d_tobs, h->sp.ep_done, (const int*)d_idx, n_index,
+                                                                         h->sp.n, (float*)d_rows, (double2*)d_ep);
     CU_TRY(h, cudaGetLastError());
-    CU_TRY(h, cudaMemcpyAsync(rows_host, h->d_rows, (size_t)n_index * OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st));
-    CU_TRY(h, cudaStreamSynchronize(st));
+    CU_TRY(h, cudaStreamSynchronize(h->side));
+    memcpy(rows_host, h->h_rows, (size_t)n_index * OBS_DIM * sizeof(float));
+    if (episode_host) memcpy(episode_host, h->h_ep, (size_t)n_index * sizeof(double2));
     return USV_OK;
 }
 

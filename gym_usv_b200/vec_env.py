@@ -54,7 +54,8 @@ class UsvGpuVecEnv:
                  ignore_obstacles: bool = False, do_perturb: bool = False, skip_kinematic: bool = False,
                  max_episode_steps: Optional[int] = None, auto_reset: bool = True, precision: str = "f64",
                  obstacles_f32: bool = False, global_env_offset: int = 0, info_mode: str = "list",
-                 render_mode: Optional[str] = None, copy_host_outputs: bool = False, mapped_obs: bool = False):
+                 render_mode: Optional[str] = None, copy_host_outputs: bool = False, mapped_obs: bool = False,
+                 host_chunks: int = 2):
         if not torch.cuda.is_available():
             raise nat.UsvError("UsvGpuVecEnv needs a CUDA device: there is no CPU fallback")
         self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
@@ -86,7 +87,6 @@ class UsvGpuVecEnv:
             self._flags = torch.zeros((2, n), dtype=torch.uint8, device=self.device)
             self.terminated, self.truncated = self._flags[0], self._flags[1]
             self._actions_dev = torch.zeros((n, nat.ACT_DIM), dtype=torch.float32, device=self.device)
-        self._bind_staging()
         # page-locked host buffers of the numpy face, allocated on first use: two sets, used alternately, so the
         # arrays step() returned stay valid while the next step is computed (copy_host_outputs=True hands out
         # private copies instead)
@@ -94,13 +94,14 @@ class UsvGpuVecEnv:
         self._slot = 0
         self.copy_host_outputs = bool(copy_host_outputs)
         self.mapped_obs = bool(mapped_obs)
+        self.host_chunks = int(host_chunks)
+        self._bind_staging()
         self._pending = None
-        self._ep_ret = np.zeros(n, dtype=np.float64)   # host-side episode bookkeeping for infos['episode']
-        self._ep_len = np.zeros(n, dtype=np.int64)
         self._closed = False
 
     # ------------------------------------------------------------------ plumbing
     def _bind_staging(self):
+        self._check(self._lib.usvgpu_set_host_chunks(self._h, self.host_chunks))
         # the host-buffer face stages through the same device tensors as the tensor face
         nat.check(self._lib.usvgpu_use_staging(self._h, *[C.c_void_p(t.data_ptr()) for t in (
             self._actions_dev, self.obs, self.reward, self._flags, self.terminal_obs)]), self._h)
@@ -196,8 +197,6 @@ class UsvGpuVecEnv:
     def reset(self) -> np.ndarray:
         hb = self._host_buffers()[self._slot]
         self._check(self._lib.usvgpu_reset_host(self._h, None, hb["obs"].ctypes.data_as(C.c_void_p), self._stream()))
-        self._ep_ret[:] = 0
-        self._ep_len[:] = 0
         return hb["obs"].copy() if self.copy_host_outputs else hb["obs"]
 
     def step_async(self, actions) -> None:
@@ -211,33 +210,34 @@ class UsvGpuVecEnv:
 
     def step_wait(self):
         assert self._pending, "step_wait() without step_async()"
-        self._check(self._lib.usvgpu_stream_sync(self._h, self._stream()))
+        # reward / flags arrive first: the episode bookkeeping below overlaps the observation copy
+        self._check(self._lib.usvgpu_flags_sync(self._h))
         self._pending = None
         hb = self._host[self._slot]
-        obs, rew = hb["obs"], hb["reward"]
-        if self.copy_host_outputs:
-            obs, rew = obs.copy(), rew.copy()
+        rew = hb["reward"].copy() if self.copy_host_outputs else hb["reward"]
         term = hb["term"].view(np.bool_)
         trunc = hb["trunc"].view(np.bool_)
         dones = term | trunc
-        self._ep_ret += rew
-        self._ep_len += 1
         done_idx = np.flatnonzero(dones)
         payload = []
         if done_idx.size:
+            # terminal observations and the (return, length) of the finished episodes, both kept on the device
+            idx32 = done_idx.astype(np.int32)
+            tob = np.empty((done_idx.size, nat.OBS_DIM), dtype=np.float32)
+            epi = np.empty((done_idx.size, 2), dtype=np.float64)
+            self._check(self._lib.usvgpu_terminal_obs_host(self._h, idx32.ctypes.data_as(C.c_void_p), idx32.size,
+                                                           tob.ctypes.data_as(C.c_void_p),
+                                                           epi.ctypes.data_as(C.c_void_p)))
+            tl = (trunc[done_idx] & ~term[done_idx]).tolist()
+            er, el = epi[:, 0].tolist(), epi[:, 1].astype(np.int64).tolist()
             if self.cfg.auto_reset:
-                idx32 = done_idx.astype(np.int32)
-                tob = np.empty((done_idx.size, nat.OBS_DIM), dtype=np.float32)
-                self._check(self._lib.usvgpu_terminal_obs_host(self._h, idx32.ctypes.data_as(C.c_void_p), idx32.size,
-                                                               tob.ctypes.data_as(C.c_void_p), self._stream()))
-            for k, i in enumerate(done_idx):
-                info = {"TimeLimit.truncated": bool(trunc[i] and not term[i]),
-                        "episode": {"r": float(self._ep_ret[i]), "l": int(self._ep_len[i])}}
-                if self.cfg.auto_reset:
-                    info["terminal_observation"] = tob[k]
-                payload.append(info)
-            self._ep_ret[done_idx] = 0
-            self._ep_len[done_idx] = 0
+                payload = [{"TimeLimit.truncated": tl[k], "episode": {"r": er[k], "l": el[k]},
+                            "terminal_observation": tob[k]} for k in range(done_idx.size)]
+            else:
+                payload = [{"TimeLimit.truncated": tl[k], "episode": {"r": er[k], "l": el[k]}}
+                           for k in range(done_idx.size)]
+        self._check(self._lib.usvgpu_stream_sync(self._h, self._stream()))  # the observations are on the host
+        obs = hb["obs"].copy() if self.copy_host_outputs else hb["obs"]
         if self.info_mode == "lazy":
             infos: Any = LazyInfos(self.num_envs, done_idx, payload)
         else:

@@ -155,10 +155,19 @@ int usvgpu_reset_host(usvgpu_handle h, const uint8_t* mask_host, float* obs_host
 int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host, float* reward_host,
                      uint8_t* terminated_host, uint8_t* truncated_host, int32_t mapped_obs, void* stream);
 int usvgpu_stream_sync(usvgpu_handle h, void* stream);
+/* usvgpu_step_host steps the shard in `chunks` (1..16, default 2) env ranges -- a first small one (1/8 of the
+ * shard) and chunks - 1 even ones -- so that the copy-out of one range overlaps the kernels of the next; results do
+ * not depend on it. */
+int usvgpu_set_host_chunks(usvgpu_handle h, int32_t chunks);
+/* Blocks until reward / terminated / truncated of the last usvgpu_step_host are on the host (the observation copy
+ * may still be in flight: the caller can do its episode bookkeeping meanwhile, then usvgpu_stream_sync). */
+int usvgpu_flags_sync(usvgpu_handle h);
 /* SB3 infos[i]["terminal_observation"] for the n_index envs listed in index_host (those whose flags came back set
- * from the last usvgpu_step_host): rows_host float32 [n_index][143].  Synchronises `stream`. */
+ * from the last usvgpu_step_host): rows_host float32 [n_index][143] (any host memory); episode_host (may be NULL)
+ * float64 [n_index][2] = return and length of the episode that just ended (SB3 Monitor's infos[i]["episode"]
+ * r, l).  Runs on a handle-owned side stream beside the observation copy; returns when the rows are in rows_host. */
 int usvgpu_terminal_obs_host(usvgpu_handle h, const int32_t* index_host, int64_t n_index, float* rows_host,
-                             void* stream);
+                             double* episode_host);
 
 /* Copy a whole field group out of / into the handle.  buf may be host or device memory
  * (cudaMemcpyDefault); size is checked against usvgpu_field_bytes(). */

@@ -451,18 +451,20 @@ def test_vecenv_host_face_sb3_semantics(usv):
     env.close()
 
 
-@pytest.mark.parametrize("mapped_obs", [False, True])
-def test_host_face_equals_tensor_face(usv, mapped_obs):
+@pytest.mark.parametrize("mapped_obs,host_chunks,N", [(False, 1, 3000), (True, 1, 3000), (False, 2, 20000), (False, 3, 30000)])
+def test_host_face_equals_tensor_face(usv, mapped_obs, host_chunks, N):
     """usvgpu_step_host (numpy in / numpy out, page-locked double buffers, optional mapped observation stores) gives
     bit-identical results to usvgpu_step on device tensors, including the terminal observations of finished envs."""
-    N, T = 3000, 40
+    T = 40
     et = usv.UsvGpuVecEnv(N, device=0, seed=9, max_episode_steps=11)
-    eh = usv.UsvGpuVecEnv(N, device=0, seed=9, max_episode_steps=11, mapped_obs=mapped_obs, info_mode="lazy")
+    eh = usv.UsvGpuVecEnv(N, device=0, seed=9, max_episode_steps=11, mapped_obs=mapped_obs, info_mode="lazy",
+                          host_chunks=host_chunks)
     ot = et.reset_tensor().cpu().numpy()
     oh = eh.reset()
     assert np.array_equal(ot, oh)
     prev = None
     n_done = 0
+    ep_ret, ep_len = np.zeros(N), np.zeros(N, dtype=np.int64)
     for t in range(T):
         a = action_stream(N, seed=100 + t)
         obs_t, rew_t, term_t, trunc_t = [x.cpu().numpy() for x in et.step_tensor(torch.tensor(a, device=et.device))]
@@ -470,10 +472,16 @@ def test_host_face_equals_tensor_face(usv, mapped_obs):
         obs, rew, dones, infos = eh.step(a)
         assert np.array_equal(obs, obs_t) and np.array_equal(rew, rew_t)
         assert np.array_equal(dones, (term_t | trunc_t).astype(bool))
+        ep_ret += rew
+        ep_len += 1
         for i in np.flatnonzero(dones):
             n_done += 1
             assert np.array_equal(infos[i]["terminal_observation"], tob_t[i])
             assert infos[i]["TimeLimit.truncated"] == bool(trunc_t[i] and not term_t[i])
+            # SB3 Monitor's episode record, accumulated on the device in float64
+            assert infos[i]["episode"]["l"] == ep_len[i] and abs(infos[i]["episode"]["r"] - ep_ret[i]) < 1e-4
+        ep_ret[dones] = 0
+        ep_len[dones] = 0
         if prev is not None:  # the arrays of the previous step are still intact (double buffering)
             assert np.array_equal(prev[0], prev[1])
         prev = (obs, obs_t.copy())

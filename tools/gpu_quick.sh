@@ -1,9 +1,4 @@
-set -x
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
+python -m pytest tests -m gpu -x -q -k "host_face or sb3" > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
 tail -15 gpurun_out/pytest_gpu.log
-python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; tail -c 600 gpurun_out/bench.err; python - <<'PY'
-import json
-d=json.loads(open('gpurun_out/bench.json').read().strip().splitlines()[-1])
-print(d['value'], d['e2e'], d['roofline']['kernels_us'], d['cpu_baseline'])
-PY
+python tools/e2e_breakdown.py 2>&1 | tee gpurun_out/e2e_breakdown.txt
