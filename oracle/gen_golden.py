@@ -172,10 +172,12 @@ def gen_reset_samples(R, n=1500):
 
 
 # -----------------------------------------------------------------------------------------
-def gen_legacy(R, steps=1000):
-    """config 1d: UsvAsmcEnv (usv-asmc-v0), np.random.seed(0), scalar f32 actions U(+-pi/2)."""
-    np.random.seed(0)
-    acts = np.random.default_rng(2).uniform(-np.pi / 2, np.pi / 2, steps).astype(np.float32)
+def _legacy_rollout(R, np_seed, act_seed, steps, full, hold=1):
+    """UsvAsmcEnv (usv-asmc-v0): np.random.seed(np_seed), scalar f32 actions U(+-pi/2) each held for `hold` steps,
+    auto-reset on done."""
+    np.random.seed(np_seed)
+    acts = np.random.default_rng(act_seed).uniform(-np.pi / 2, np.pi / 2, (steps + hold - 1) // hold)
+    acts = np.repeat(acts, hold)[:steps].astype(np.float32)
     env = R.UsvAsmcEnv()
     resets = []
 
@@ -195,12 +197,29 @@ def gen_legacy(R, steps=1000):
         if d:
             o = env.reset()
             resets.append((t + 1, rec(), o))
-    out = dict(actions=acts, obs=obs, reward=rew, done=done, pos=pos, vel=vel, aux=aux, last=last,
+    out = dict(actions=acts, obs=obs, reward=rew, done=done, pos=pos, vel=vel,
                reset_step=np.array([r[0] for r in resets]), reset_obs=np.array([r[2] for r in resets]))
+    if full:
+        out.update(aux=aux, last=last)
+    else:  # after a step the arrays hold float32 values (usv_asmc_env.py:247-251): store them as such
+        out["pos"], out["vel"] = pos.astype(np.float32), vel.astype(np.float32)
+        assert np.array_equal(out["pos"].astype(np.float64), pos) and np.array_equal(out["vel"].astype(np.float64), vel)
     for k in resets[0][1]:
         out["reset_" + k] = np.array([r[1][k] for r in resets])
+    return out, len(resets), int(done.sum())
+
+
+def gen_legacy(R):
+    """config 1d: 1000 steps from np.random.seed(0) with every array recorded, plus two longer rollouts (keys 'L0_*':
+    2000 steps, a new action every step; 'L1_*': 6000 steps, actions held for 250 steps so that the vessel runs into
+    the |x| > 30 / |ye| > 10 terminations and the float64 first step after each reset)."""
+    out, nres, nd = _legacy_rollout(R, 0, 2, 1000, full=True)
+    print("legacy: resets", nres, "done", nd)
+    for k, (np_seed, act_seed, steps, hold) in enumerate([(1, 3, 2000, 1), (2, 4, 6000, 250)]):
+        o, nres, nd = _legacy_rollout(R, np_seed, act_seed, steps, full=False, hold=hold)
+        print(f"legacy L{k}: resets", nres, "done", nd)
+        out.update({f"L{k}_{name}": v for name, v in o.items()})
     np.savez_compressed(os.path.join(OUT, "legacy_asmc_env.npz"), **out)
-    print("legacy: resets", len(resets), "done", int(done.sum()))
 
 
 if __name__ == "__main__":

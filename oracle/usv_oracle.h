@@ -105,6 +105,37 @@ void usv_oracle_vec_step(UsvOracleEnv* envs, int64_t n, const UsvOracleConfig* c
                          float* obs, double* reward, uint8_t* terminated, uint8_t* truncated,
                          float* terminal_obs, uint64_t seed, int64_t global_offset);
 
+/* ---- legacy path-following env 'usv-asmc-v0' (gym_usv/envs/usv_asmc_env.py), usv_oracle_legacy.c ---- */
+/* usv_asmc_env.py:53-58: the six arrays of UsvAsmcEnv.  Values are held in double; after the first step() they are
+ * float32 values (usv_asmc_env.py:247-251) and f32_state selects the float32 arithmetic flow. */
+typedef struct UsvOracleLegacy {
+    double state[6];     /* u, v_ak, r, ye, psi_ak, action_last                      */
+    double velocity[3];  /* u, v, r                                                  */
+    double position[3];  /* x, y, psi                                                */
+    double aux[3];       /* e_u_int, Ka_u, Ka_psi                                    */
+    double last[9];      /* eta_dot_last[3], upsilon_dot_last[3], e_u_last, Ka_dot_u_last, Ka_dot_psi_last */
+    double target[6];    /* x_0, y_0, desired_speed, ak, x_d, y_d                    */
+    double ep_return;
+    int32_t f32_state;   /* 0 after reset() (float64 arrays), 1 after a step()       */
+    int32_t steps;
+    int32_t episode;
+    int32_t pad_;
+} UsvOracleLegacy;
+
+int  usv_oracle_sizeof_legacy(void);
+void usv_oracle_legacy_init(UsvOracleLegacy* e);
+/* usv_asmc_env.py:258-300 from the seven uniform draws x, y, psi, x_0, y_0, x_d, desired_speed */
+void usv_oracle_legacy_reset_from_draws(UsvOracleLegacy* e, const double draws[7], float obs[6]);
+/* the same with Philox4x32-10 draws keyed by (seed, global env id, episode) instead of the global np.random */
+void usv_oracle_legacy_reset(UsvOracleLegacy* e, uint64_t seed, uint64_t global_id, float obs[6]);
+/* usv_asmc_env.py:99-255 (action: the float32 scalar the caller passes; done => reward = -1) */
+void usv_oracle_legacy_step(UsvOracleLegacy* e, float action, float obs[6], double* reward, uint8_t* done);
+void usv_oracle_legacy_vec_reset(UsvOracleLegacy* envs, int64_t n, uint64_t seed, int64_t global_offset, float* obs,
+                                 int n_threads);
+void usv_oracle_legacy_vec_step(UsvOracleLegacy* envs, int64_t n, const float* actions, float* obs, double* reward,
+                                uint8_t* done, float* terminal_obs, int auto_reset, uint64_t seed,
+                                int64_t global_offset, int n_threads);
+
 /* RNG primitives exposed for tests (Philox4x32-10) */
 void usv_oracle_philox(uint64_t seed, uint64_t global_id, uint32_t episode, uint32_t block, uint32_t out[4]);
 

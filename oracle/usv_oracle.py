@@ -55,6 +55,24 @@ ENV_DTYPE = np.dtype(
 )
 
 
+LEGACY_DTYPE = np.dtype(
+    [
+        ("state", "<f8", (6,)),
+        ("velocity", "<f8", (3,)),
+        ("position", "<f8", (3,)),
+        ("aux", "<f8", (3,)),
+        ("last", "<f8", (9,)),
+        ("target", "<f8", (6,)),
+        ("ep_return", "<f8"),
+        ("f32_state", "<i4"),
+        ("steps", "<i4"),
+        ("episode", "<i4"),
+        ("pad_", "<i4"),
+    ],
+    align=True,
+)
+
+
 class Config(C.Structure):
     _fields_ = [
         ("ignore_obstacles", C.c_int32),
@@ -70,7 +88,8 @@ class Config(C.Structure):
 
 def build(force: bool = False) -> str:
     """Compile the oracle with gcc (make -C oracle).  Returns the .so path."""
-    srcs = [os.path.join(_HERE, f) for f in ("usv_oracle.c", "usv_oracle_legacy.c", "usv_oracle.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("usv_oracle.c", "usv_oracle_legacy.c", "usv_oracle_legacy_step.inc",
+                                             "usv_oracle.h")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs if os.path.exists(s)
     )
@@ -107,6 +126,17 @@ def lib():
                      "usv_oracle_simple_step", "usv_oracle_vec_reset", "usv_oracle_vec_step",
                      "usv_oracle_philox"):
             getattr(L, name).restype = None
+        L.usv_oracle_sizeof_legacy.restype = C.c_int
+        L.usv_oracle_legacy_init.argtypes = [vp]
+        L.usv_oracle_legacy_reset_from_draws.argtypes = [vp, vp, vp]
+        L.usv_oracle_legacy_reset.argtypes = [vp, u64, u64, vp]
+        L.usv_oracle_legacy_step.argtypes = [vp, C.c_float, vp, vp, vp]
+        L.usv_oracle_legacy_vec_reset.argtypes = [vp, i64, u64, i64, vp, i32]
+        L.usv_oracle_legacy_vec_step.argtypes = [vp, i64, vp, vp, vp, vp, vp, i32, u64, i64, i32]
+        for name in ("usv_oracle_legacy_init", "usv_oracle_legacy_reset_from_draws", "usv_oracle_legacy_reset",
+                     "usv_oracle_legacy_step", "usv_oracle_legacy_vec_reset", "usv_oracle_legacy_vec_step"):
+            getattr(L, name).restype = None
+        assert L.usv_oracle_sizeof_legacy() == LEGACY_DTYPE.itemsize
         assert L.usv_oracle_sizeof_env() == ENV_DTYPE.itemsize, (L.usv_oracle_sizeof_env(), ENV_DTYPE.itemsize)
         assert L.usv_oracle_sizeof_asmc() == ASMC_DTYPE.itemsize
         _lib = L
@@ -187,6 +217,44 @@ class OracleVecEnv:
                                   _p(self.terminated), _p(self.truncated), _p(self.terminal_obs), self.seed,
                                   self.global_offset)
         return self.obs, self.reward, self.terminated, self.truncated
+
+
+# ---------------------------------------------------------------------------------------
+# usv-asmc-v0 legacy vector env (gym_usv/envs/usv_asmc_env.py)
+# ---------------------------------------------------------------------------------------
+class OracleLegacyVecEnv:
+    """N UsvAsmcEnv instances in lock-step (usv_asmc_env.py:99-300), SB3 auto-reset semantics."""
+
+    def __init__(self, n, seed=0, global_offset=0, auto_reset=True, n_threads=1):
+        self.n, self.seed, self.global_offset = int(n), int(seed), int(global_offset)
+        self.auto_reset, self.n_threads = bool(auto_reset), int(n_threads)
+        self.envs = np.zeros(self.n, dtype=LEGACY_DTYPE)
+        lib()
+        self.envs["episode"] = -1
+        self.obs = np.zeros((self.n, 6), dtype=np.float32)
+        self.terminal_obs = np.zeros((self.n, 6), dtype=np.float32)
+        self.reward = np.zeros(self.n)
+        self.done = np.zeros(self.n, dtype=np.uint8)
+
+    def reset(self):
+        lib().usv_oracle_legacy_vec_reset(_p(self.envs), self.n, self.seed, self.global_offset, _p(self.obs),
+                                          self.n_threads)
+        return self.obs
+
+    def reset_from_draws(self, draws):
+        """usv_asmc_env.py:258-300 from the reference's own seven uniform draws per env."""
+        d = np.ascontiguousarray(draws, dtype=np.float64).reshape(self.n, 7)
+        for i in range(self.n):
+            lib().usv_oracle_legacy_reset_from_draws(self.envs[i:i + 1].ctypes.data_as(C.c_void_p), _p(d[i]),
+                                                     _p(self.obs[i]))
+        return self.obs
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions, dtype=np.float32).reshape(self.n)
+        lib().usv_oracle_legacy_vec_step(_p(self.envs), self.n, _p(a), _p(self.obs), _p(self.reward), _p(self.done),
+                                         _p(self.terminal_obs), int(self.auto_reset), self.seed, self.global_offset,
+                                         self.n_threads)
+        return self.obs, self.reward, self.done
 
 
 def philox(seed, gid, episode, block):
