@@ -15,7 +15,7 @@ _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
-HEADERS = [os.path.join(CSRC, f) for f in ("usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
+HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
                                              "usv_sensor.cuh", "usv_kernels.cuh", "usv_math.cuh")] + \
           [os.path.join(_ROOT, "include", "usvgpu.h")]
 
@@ -35,6 +35,11 @@ PREC_F64 = 0
 PREC_MIXED = 1
 
 FIELD_DYN, FIELD_EPI, FIELD_OBSTACLES, FIELD_N_OBS, FIELD_STEPS, FIELD_EPISODE, FIELD_EP_RETURN = range(7)
+FIELD_LEGACY, FIELD_LEGACY_TARGET, FIELD_LEGACY_POS0 = 7, 8, 9
+LEGACY_ROWS = 19
+LEGACY_OBS_DIM = 6
+LEGACY_NAMES = ("action_last", "u", "v", "r", "x", "y", "psi", "e_u_int", "ka_u", "ka_psi", "x_dot_last", "y_dot_last",
+                "psi_dot_last", "u_dot_last", "v_dot_last", "r_dot_last", "e_u_last", "ka_dot_u_last", "ka_dot_psi_last")
 
 # row names of FIELD_DYN / FIELD_EPI (include/usvgpu.h)
 DYN_NAMES = ("x", "y", "psi", "u", "v", "r", "x_dot_last", "y_dot_last", "psi_dot_last", "u_dot_last", "v_dot_last",
@@ -92,6 +97,8 @@ _SIGNATURES = {
     "usvgpu_last_error": (C.c_char_p, [C.c_void_p]),
     "usvgpu_create": (C.c_int, [C.POINTER(UsvConfig), C.c_int, C.c_int64, C.c_int64, C.c_uint64, C.POINTER(C.c_void_p)]),
     "usvgpu_destroy": (C.c_int, [C.c_void_p]),
+    "usvgpu_obs_dim": (C.c_int, [C.c_void_p]),
+    "usvgpu_act_dim": (C.c_int, [C.c_void_p]),
     "usvgpu_reset": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_step": (C.c_int, [C.c_void_p] * 8),
     "usvgpu_step_timed": (C.c_int, [C.c_void_p] * 9),

@@ -324,13 +324,13 @@ __global__ void reset_kernel(StatePtrs s, const uint8_t* __restrict__ mask, floa
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 gather_rows_kernel(const float* __restrict__ src, const double2* __restrict__ ep_done, const int* __restrict__ index,
-                   long long n_index, long long n, float* __restrict__ rows, double2* __restrict__ ep_out) {
+                   long long n_index, long long n, int row_len, float* __restrict__ rows, double2* __restrict__ ep_out) {
     const long long k = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (k >= n_index) return;
     const int lane = threadIdx.x & 31;
     const long long i = index[k];
     if (i < 0 || i >= n) return;
-    for (int c = lane; c < OBS_DIM; c += 32) rows[k * OBS_DIM + c] = src[i * OBS_DIM + c];
+    for (int c = lane; c < row_len; c += 32) rows[k * row_len + c] = src[i * row_len + c];
     if (lane == 0) ep_out[k] = ep_done[i];
 }
 

@@ -18,6 +18,7 @@
 
 #include "../../include/usvgpu.h"
 #include "usv_kernels.cuh"
+#include "usv_legacy.cuh"
 
 // =================================================================================================
 // Host side: handle + C ABI
@@ -29,7 +30,10 @@ constexpr int HOST_CHUNKS_MAX = 16;
 struct UsvGpu {
     UsvConfig cfg;
     int device;
+    int obs_dim, act_dim;  // 143 / 2 ('usv-asmc-simple') or 6 / 1 ('usv-asmc-v0')
+    bool legacy;
     StatePtrs sp;
+    LegacyPtrs lp;         // env_kind == USV_ENV_ASMC_V0: sp holds only n, stats, ep_return, steps, episode, ep_done
     size_t obst_elem;
     std::string err;
     unsigned long long host_env_steps;
@@ -101,6 +105,16 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
                      float* tobs, cudaStream_t st, cudaEvent_t mid = nullptr, long long lo = 0, long long hi = -1) {
     if (hi < 0) hi = h->sp.n;
     const StepFlags fl = {h->cfg.do_perturb, h->cfg.skip_kinematic, h->cfg.max_episode_steps, h->cfg.auto_reset, lo, hi};
+    if (h->legacy) {  // 'usv-asmc-v0': one kernel, thread per env
+        legacy_step_kernel<<<(unsigned)((hi - lo + LEG_B - 1) / LEG_B), LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term,
+                                                                                    trunc, tobs);
+        cudaError_t le = cudaGetLastError();
+        if (le != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("legacy step launch: ") + cudaGetErrorString(le));
+        if (mid) cudaEventRecord(mid, st);
+        h->host_env_steps += (unsigned long long)(hi - lo);
+        h->launches += 1;
+        return USV_OK;
+    }
     const unsigned dblocks = (unsigned)((hi - lo + DYN_B - 1) / DYN_B);
     if (h->cfg.do_perturb) dynamics_kernel<true><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
     else dynamics_kernel<false><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
@@ -122,13 +136,20 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
     return USV_OK;
 }
 
+static bool bad_alignment(const UsvGpu* h, const void* obs, const void* actions) {
+    return h->legacy ? (((uintptr_t)obs & 7) || ((uintptr_t)actions & 3)) : (((uintptr_t)obs & 3) || ((uintptr_t)actions & 7));
+}
+
 static int field_ptr(UsvGpu* h, int32_t field, void** p, int64_t* bytes) {
     const int64_t n = h->sp.n;
     switch (field) {
-        case USV_FIELD_DYN: *p = h->sp.dyn; *bytes = n * N_DYN * 8; return 0;
-        case USV_FIELD_EPI: *p = h->sp.epi; *bytes = n * N_EPI * 8; return 0;
-        case USV_FIELD_OBSTACLES: *p = h->sp.obst; *bytes = n * MAX_OBST * 3 * (int64_t)h->obst_elem; return 0;
-        case USV_FIELD_N_OBS: *p = h->sp.n_obs; *bytes = n * 4; return 0;
+        case USV_FIELD_LEGACY: if (!h->legacy) return -1; *p = h->lp.st; *bytes = n * LEG_ROWS * 4; return 0;
+        case USV_FIELD_LEGACY_TARGET: if (!h->legacy) return -1; *p = h->lp.target; *bytes = n * 6 * 8; return 0;
+        case USV_FIELD_LEGACY_POS0: if (!h->legacy) return -1; *p = h->lp.pos0; *bytes = n * 3 * 8; return 0;
+        case USV_FIELD_DYN: if (h->legacy) return -1; *p = h->sp.dyn; *bytes = n * N_DYN * 8; return 0;
+        case USV_FIELD_EPI: if (h->legacy) return -1; *p = h->sp.epi; *bytes = n * N_EPI * 8; return 0;
+        case USV_FIELD_OBSTACLES: if (h->legacy) return -1; *p = h->sp.obst; *bytes = n * MAX_OBST * 3 * (int64_t)h->obst_elem; return 0;
+        case USV_FIELD_N_OBS: if (h->legacy) return -1; *p = h->sp.n_obs; *bytes = n * 4; return 0;
         case USV_FIELD_STEPS: *p = h->sp.steps; *bytes = n * 4; return 0;
         case USV_FIELD_EPISODE: *p = h->sp.episode; *bytes = n * 4; return 0;
         case USV_FIELD_EP_RETURN: *p = h->sp.ep_return; *bytes = n * 8; return 0;
@@ -147,7 +168,8 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     if (!cfg || !out) return fail(nullptr, USV_ERR_INVALID, "cfg/out is NULL");
     *out = nullptr;
     if (n_envs <= 0) return fail(nullptr, USV_ERR_INVALID, "n_envs must be positive");
-    if (cfg->env_kind != USV_ENV_ASMC_SIMPLE) return fail(nullptr, USV_ERR_INVALID, "env_kind not supported by this build");
+    if (cfg->env_kind != USV_ENV_ASMC_SIMPLE && cfg->env_kind != USV_ENV_ASMC_V0)
+        return fail(nullptr, USV_ERR_INVALID, "unknown env_kind");
     if (cfg->precision != USV_PREC_F64) return fail(nullptr, USV_ERR_INVALID, "precision not supported by this build");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
@@ -155,6 +177,10 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     if (!h) return fail(nullptr, USV_ERR_ALLOC, "host allocation failed");
     h->cfg = *cfg;
     h->device = device;
+    h->legacy = cfg->env_kind == USV_ENV_ASMC_V0;
+    h->obs_dim = h->legacy ? LEG_OBS : OBS_DIM;
+    h->act_dim = h->legacy ? 1 : 2;
+    memset(&h->lp, 0, sizeof(h->lp));
     h->host_env_steps = 0;
     h->launches = 0;
     h->obst_elem = cfg->obstacles_f32 ? sizeof(float) : sizeof(double);
@@ -182,16 +208,22 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
         if (e == cudaSuccess) e = cudaMalloc(p, bytes);
         if (e == cudaSuccess) e = cudaMemset(*p, 0, bytes);
     };
-    alloc((void**)&h->sp.dyn, n * N_DYN * sizeof(double));
-    alloc((void**)&h->sp.epi, n * N_EPI * sizeof(double));
-    alloc((void**)&h->sp.obst, n * MAX_OBST * 3 * h->obst_elem);
-    alloc((void**)&h->sp.n_obs, n * sizeof(int));
+    if (h->legacy) {
+        alloc((void**)&h->lp.st, n * LEG_ROWS * sizeof(float));
+        alloc((void**)&h->lp.pos0, n * 3 * sizeof(double));
+        alloc((void**)&h->lp.target, n * 6 * sizeof(double));
+    } else {
+        alloc((void**)&h->sp.dyn, n * N_DYN * sizeof(double));
+        alloc((void**)&h->sp.epi, n * N_EPI * sizeof(double));
+        alloc((void**)&h->sp.obst, n * MAX_OBST * 3 * h->obst_elem);
+        alloc((void**)&h->sp.n_obs, n * sizeof(int));
+        alloc((void**)&h->sp.hand, n * sizeof(Hand));
+        alloc((void**)&h->sp.hdr16, n * HDR_PAD * sizeof(float));
+    }
     alloc((void**)&h->sp.steps, n * sizeof(int));
     alloc((void**)&h->sp.episode, n * sizeof(int));
     alloc((void**)&h->sp.ep_return, n * sizeof(double));
     alloc((void**)&h->sp.ep_done, n * sizeof(double2));
-    alloc((void**)&h->sp.hand, n * sizeof(Hand));
-    alloc((void**)&h->sp.hdr16, n * HDR_PAD * sizeof(float));
     alloc((void**)&h->sp.stats, sizeof(DeviceStats));
     double2* rt = nullptr;
     alloc((void**)&rt, N_SENS * sizeof(double2));
@@ -207,13 +239,27 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
         usvgpu_destroy(h);
         return fail(nullptr, USV_ERR_CUDA, msg);
     }
+    h->lp.steps = h->sp.steps;
+    h->lp.episode = h->sp.episode;
+    h->lp.ep_return = h->sp.ep_return;
+    h->lp.ep_done = h->sp.ep_done;
+    h->lp.stats = h->sp.stats;
+    h->lp.n = n_envs;
+    h->lp.global_offset = global_env_offset;
+    h->lp.seed = seed;
     *out = h;
     return USV_OK;
 }
 
+int usvgpu_obs_dim(usvgpu_handle h) { return h ? h->obs_dim : USV_ERR_INVALID; }
+int usvgpu_act_dim(usvgpu_handle h) { return h ? h->act_dim : USV_ERR_INVALID; }
+
 int usvgpu_destroy(usvgpu_handle h) {
     if (!h) return USV_OK;
     cudaSetDevice(h->device);
+    cudaFree(h->lp.st);
+    cudaFree(h->lp.pos0);
+    cudaFree(h->lp.target);
     cudaFree(h->sp.dyn);
     cudaFree(h->sp.epi);
     cudaFree(h->sp.obst);
@@ -252,7 +298,8 @@ int usvgpu_reset(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream)
     const int threads = 128;
     const unsigned blocks = (unsigned)((h->sp.n + threads - 1) / threads);
     cudaStream_t st = (cudaStream_t)stream;
-    if (h->cfg.obstacles_f32) reset_kernel<float><<<blocks, threads, 0, st>>>(h->sp, mask, obs);
+    if (h->legacy) legacy_reset_kernel<<<blocks, threads, 0, st>>>(h->lp, mask, obs);
+    else if (h->cfg.obstacles_f32) reset_kernel<float><<<blocks, threads, 0, st>>>(h->sp, mask, obs);
     else reset_kernel<double><<<blocks, threads, 0, st>>>(h->sp, mask, obs);
     CU_TRY(h, cudaGetLastError());
     return USV_OK;
@@ -262,7 +309,7 @@ int usvgpu_step(usvgpu_handle h, const float* actions, float* obs, float* reward
                 uint8_t* truncated, float* terminal_obs, void* stream) {
     if (!h) return USV_ERR_INVALID;
     if (!actions || !obs || !reward || !terminated || !truncated) return fail(h, USV_ERR_INVALID, "NULL buffer");
-    if (((uintptr_t)obs & 3) || ((uintptr_t)actions & 7)) return fail(h, USV_ERR_INVALID, "obs must be 4-byte and actions 8-byte aligned");
+    if (bad_alignment(h, obs, actions)) return fail(h, USV_ERR_INVALID, "obs / actions misaligned (simple: 4 / 8 bytes, legacy: 8 / 4 bytes)");
     CU_TRY(h, cudaSetDevice(h->device));
     return step_impl(h, actions, obs, reward, terminated, truncated, terminal_obs, (cudaStream_t)stream);
 }
@@ -271,7 +318,7 @@ int usvgpu_step_timed(usvgpu_handle h, const float* actions, float* obs, float* 
                       uint8_t* truncated, float* terminal_obs, void* stream, float* kernel_ms) {
     if (!h) return USV_ERR_INVALID;
     if (!actions || !obs || !reward || !terminated || !truncated || !kernel_ms) return fail(h, USV_ERR_INVALID, "NULL buffer");
-    if (((uintptr_t)obs & 3) || ((uintptr_t)actions & 7)) return fail(h, USV_ERR_INVALID, "obs must be 4-byte and actions 8-byte aligned");
+    if (bad_alignment(h, obs, actions)) return fail(h, USV_ERR_INVALID, "obs / actions misaligned (simple: 4 / 8 bytes, legacy: 8 / 4 bytes)");
     CU_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = (cudaStream_t)stream;
     cudaEvent_t ev[3];
@@ -293,11 +340,11 @@ int usvgpu_rollout(usvgpu_handle h, const float* actions, int32_t n_steps, int32
     if (!h) return USV_ERR_INVALID;
     if (!actions || !obs || !reward || !terminated || !truncated || n_steps < 0)
         return fail(h, USV_ERR_INVALID, "bad rollout arguments");
-    if (((uintptr_t)obs & 3) || ((uintptr_t)actions & 7)) return fail(h, USV_ERR_INVALID, "obs must be 4-byte and actions 8-byte aligned");
+    if (bad_alignment(h, obs, actions)) return fail(h, USV_ERR_INVALID, "obs / actions misaligned (simple: 4 / 8 bytes, legacy: 8 / 4 bytes)");
     CU_TRY(h, cudaSetDevice(h->device));
     for (int k = 0; k < n_steps; ++k) {
         const int slab = action_wrap > 0 ? (k % action_wrap) : k;
-        int rc = step_impl(h, actions + (size_t)slab * h->sp.n * 2, obs, reward, terminated, truncated, nullptr,
+        int rc = step_impl(h, actions + (size_t)slab * h->sp.n * h->act_dim, obs, reward, terminated, truncated, nullptr,
                            (cudaStream_t)stream);
         if (rc) return rc;
     }
@@ -314,13 +361,13 @@ static int ensure_staging(UsvGpu* h) {
         if (!h->ev_chunk[c]) CU_TRY(h, cudaEventCreateWithFlags(&h->ev_chunk[c], cudaEventDisableTiming));
     if (h->d_obs) return USV_OK;
     const size_t n = (size_t)h->sp.n;
-    CU_TRY(h, cudaMalloc((void**)&h->d_actions, n * 2 * sizeof(float)));
+    CU_TRY(h, cudaMalloc((void**)&h->d_actions, n * h->act_dim * sizeof(float)));
     CU_TRY(h, cudaMalloc((void**)&h->d_reward, n * sizeof(float)));
     CU_TRY(h, cudaMalloc((void**)&h->d_flags, 2 * n));
-    CU_TRY(h, cudaMalloc((void**)&h->d_tobs, n * OBS_DIM * sizeof(float)));
-    CU_TRY(h, cudaMemset(h->d_tobs, 0, n * OBS_DIM * sizeof(float)));
-    CU_TRY(h, cudaMalloc((void**)&h->d_obs, n * OBS_DIM * sizeof(float)));
-    CU_TRY(h, cudaMemset(h->d_obs, 0, n * OBS_DIM * sizeof(float)));
+    CU_TRY(h, cudaMalloc((void**)&h->d_tobs, n * h->obs_dim * sizeof(float)));
+    CU_TRY(h, cudaMemset(h->d_tobs, 0, n * h->obs_dim * sizeof(float)));
+    CU_TRY(h, cudaMalloc((void**)&h->d_obs, n * h->obs_dim * sizeof(float)));
+    CU_TRY(h, cudaMemset(h->d_obs, 0, n * h->obs_dim * sizeof(float)));
     return USV_OK;
 }
 
@@ -370,7 +417,7 @@ int usvgpu_reset_host(usvgpu_handle h, const uint8_t* mask_host, float* obs_host
     }
     rc = usvgpu_reset(h, mask, h->d_obs, stream);
     if (rc) return rc;
-    CU_TRY(h, cudaMemcpyAsync(obs_host, h->d_obs, n * OBS_DIM * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CU_TRY(h, cudaMemcpyAsync(obs_host, h->d_obs, n * h->obs_dim * sizeof(float), cudaMemcpyDeviceToHost, st));
     CU_TRY(h, cudaStreamSynchronize(st));
     return USV_OK;
 }
@@ -385,7 +432,7 @@ int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t n = (size_t)h->sp.n;
-    CU_TRY(h, cudaMemcpyAsync(h->d_actions, actions_host, n * 2 * sizeof(float), cudaMemcpyHostToDevice, st));
+    CU_TRY(h, cudaMemcpyAsync(h->d_actions, actions_host, n * h->act_dim * sizeof(float), cudaMemcpyHostToDevice, st));
     if (mapped_obs) {  // the sensor kernel stores the rows straight into the caller's page-locked, mapped buffer
         void* dp = nullptr;
         CU_TRY(h, cudaHostGetDevicePointer(&dp, obs_host, 0));
@@ -416,7 +463,7 @@ int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host
                 CU_TRY(h, cudaMemcpyAsync(truncated_host, h->d_flags + n, n, cudaMemcpyDeviceToHost, h->copy));
                 CU_TRY(h, cudaEventRecord(h->ev_flags, h->copy));
             }
-            CU_TRY(h, cudaMemcpyAsync(obs_host + lo * OBS_DIM, h->d_obs + lo * OBS_DIM, m * OBS_DIM * sizeof(float),
+            CU_TRY(h, cudaMemcpyAsync(obs_host + lo * h->obs_dim, h->d_obs + lo * h->obs_dim, m * h->obs_dim * sizeof(float),
                                       cudaMemcpyDeviceToHost, h->copy));
             lo = hi;
         }
@@ -474,7 +521,7 @@ int usvgpu_terminal_obs_host(usvgpu_handle h, const int32_t* index_host, int64_t
         h->h_ep = nullptr;
         h->gather_cap = 0;
         CU_TRY(h, cudaHostAlloc((void**)&h->h_idx, (size_t)cap * sizeof(int32_t), cudaHostAllocMapped));
-        CU_TRY(h, cudaHostAlloc((void**)&h->h_rows, (size_t)cap * OBS_DIM * sizeof(float), cudaHostAllocMapped));
+        CU_TRY(h, cudaHostAlloc((void**)&h->h_rows, (size_t)cap * h->obs_dim * sizeof(float), cudaHostAllocMapped));
         CU_TRY(h, cudaHostAlloc((void**)&h->h_ep, (size_t)cap * sizeof(double2), cudaHostAllocMapped));
         h->gather_cap = cap;
     }
@@ -488,10 +535,10 @@ int usvgpu_terminal_obs_host(usvgpu_handle h, const int32_t* index_host, int64_t
     CU_TRY(h, cudaHostGetDevicePointer(&d_rows, h->h_rows, 0));
     CU_TRY(h, cudaHostGetDevicePointer(&d_ep, h->h_ep, 0));
     gather_rows_kernel<<<(unsigned)((n_index + 7) / 8), 256, 0, h->side>>>(h->d_tobs, h->sp.ep_done, (const int*)d_idx, n_index,
-                                                                         h->sp.n, (float*)d_rows, (double2*)d_ep);
+                                                                         h->sp.n, h->obs_dim, (float*)d_rows, (double2*)d_ep);
     CU_TRY(h, cudaGetLastError());
     CU_TRY(h, cudaStreamSynchronize(h->side));
-    memcpy(rows_host, h->h_rows, (size_t)n_index * OBS_DIM * sizeof(float));
+    memcpy(rows_host, h->h_rows, (size_t)n_index * h->obs_dim * sizeof(float));
     if (episode_host) memcpy(episode_host, h->h_ep, (size_t)n_index * sizeof(double2));
     return USV_OK;
 }

@@ -25,7 +25,9 @@ from . import _native as nat
 from . import spaces
 
 ENV_ID = "usv-asmc-simple"
-MAX_EPISODE_STEPS = {"usv-asmc-simple": 1000}  # gym_usv/__init__.py:30-34
+# gym_usv/__init__.py:30-34 registers a 1000-step TimeLimit for 'usv-asmc-simple' and none for 'usv-asmc-v0' (:3-6)
+MAX_EPISODE_STEPS = {"usv-asmc-simple": 1000, "usv-asmc-v0": 0}
+ENV_KINDS = {"usv-asmc-simple": nat.ENV_ASMC_SIMPLE, "usv-asmc-v0": nat.ENV_ASMC_V0}
 
 
 class LazyInfos(Sequence):
@@ -55,20 +57,26 @@ class UsvGpuVecEnv:
                  max_episode_steps: Optional[int] = None, auto_reset: bool = True, precision: str = "f64",
                  obstacles_f32: bool = False, global_env_offset: int = 0, info_mode: str = "list",
                  render_mode: Optional[str] = None, copy_host_outputs: bool = False, mapped_obs: bool = False,
-                 host_chunks: int = 2):
+                 host_chunks: int = 2, env_id: str = ENV_ID):
         if not torch.cuda.is_available():
             raise nat.UsvError("UsvGpuVecEnv needs a CUDA device: there is no CPU fallback")
         self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
         if self.device.type != "cuda":
             raise nat.UsvError("UsvGpuVecEnv needs a CUDA device: there is no CPU fallback")
         self.num_envs = int(num_envs)
-        self.observation_space = spaces.simple_observation_space()
-        self.action_space = spaces.simple_action_space()
+        if env_id not in ENV_KINDS:
+            raise nat.UsvError(f"unknown env id '{env_id}' (have: {sorted(ENV_KINDS)})")
+        self.env_id = env_id
+        self.legacy = env_id == "usv-asmc-v0"  # UsvAsmcEnv, gym_usv/envs/usv_asmc_env.py
+        self.obs_dim = nat.LEGACY_OBS_DIM if self.legacy else nat.OBS_DIM
+        self.act_dim = 1 if self.legacy else nat.ACT_DIM
+        self.observation_space = spaces.legacy_observation_space() if self.legacy else spaces.simple_observation_space()
+        self.action_space = spaces.legacy_action_space() if self.legacy else spaces.simple_action_space()
         self.render_mode = render_mode
         self.info_mode = info_mode
         if max_episode_steps is None:
-            max_episode_steps = MAX_EPISODE_STEPS[ENV_ID]
-        self.cfg = nat.UsvConfig(nat.ENV_ASMC_SIMPLE, int(ignore_obstacles), int(do_perturb), int(skip_kinematic),
+            max_episode_steps = MAX_EPISODE_STEPS[env_id]
+        self.cfg = nat.UsvConfig(ENV_KINDS[env_id], int(ignore_obstacles), int(do_perturb), int(skip_kinematic),
                                  int(max_episode_steps), int(auto_reset), {"f64": 0, "mixed": 1}[precision],
                                  int(obstacles_f32))
         self._seed = int(seed)
@@ -81,12 +89,12 @@ class UsvGpuVecEnv:
                                           self._seed, C.byref(self._h)))
         n = self.num_envs
         with torch.cuda.device(self.device):
-            self.obs = torch.zeros((n, nat.OBS_DIM), dtype=torch.float32, device=self.device)
-            self.terminal_obs = torch.zeros((n, nat.OBS_DIM), dtype=torch.float32, device=self.device)
+            self.obs = torch.zeros((n, self.obs_dim), dtype=torch.float32, device=self.device)
+            self.terminal_obs = torch.zeros((n, self.obs_dim), dtype=torch.float32, device=self.device)
             self.reward = torch.zeros(n, dtype=torch.float32, device=self.device)
             self._flags = torch.zeros((2, n), dtype=torch.uint8, device=self.device)
             self.terminated, self.truncated = self._flags[0], self._flags[1]
-            self._actions_dev = torch.zeros((n, nat.ACT_DIM), dtype=torch.float32, device=self.device)
+            self._actions_dev = torch.zeros((n, self.act_dim), dtype=torch.float32, device=self.device)
         # page-locked host buffers of the numpy face, allocated on first use: two sets, used alternately, so the
         # arrays step() returned stay valid while the next step is computed (copy_host_outputs=True hands out
         # private copies instead)
@@ -142,8 +150,8 @@ class UsvGpuVecEnv:
         if self._host is None:
             n = self.num_envs
             self._host_ptrs = []
-            self._host = [{"actions": self._host_array((n, nat.ACT_DIM), np.float32),
-                           "obs": self._host_array((n, nat.OBS_DIM), np.float32),
+            self._host = [{"actions": self._host_array((n, self.act_dim), np.float32),
+                           "obs": self._host_array((n, self.obs_dim), np.float32),
                            "reward": self._host_array((n,), np.float32),
                            "term": self._host_array((n,), np.uint8),
                            "trunc": self._host_array((n,), np.uint8)} for _ in range(2)]
@@ -165,8 +173,10 @@ class UsvGpuVecEnv:
         tensors owned by the env (overwritten by the next step).  No host copy, no sync."""
         if actions.device != self.device or actions.dtype != torch.float32 or not actions.is_contiguous():
             actions = actions.to(device=self.device, dtype=torch.float32).contiguous()
-        if actions.shape != (self.num_envs, nat.ACT_DIM):
-            raise ValueError(f"actions must have shape {(self.num_envs, nat.ACT_DIM)}, got {tuple(actions.shape)}")
+        if self.legacy and actions.dim() == 1:
+            actions = actions.unsqueeze(1)
+        if actions.shape != (self.num_envs, self.act_dim):
+            raise ValueError(f"actions must have shape {(self.num_envs, self.act_dim)}, got {tuple(actions.shape)}")
         self._check(self._lib.usvgpu_step(
             self._h, C.c_void_p(actions.data_ptr()), C.c_void_p(self.obs.data_ptr()),
             C.c_void_p(self.reward.data_ptr()), C.c_void_p(self.terminated.data_ptr()),
@@ -202,7 +212,7 @@ class UsvGpuVecEnv:
     def step_async(self, actions) -> None:
         self._slot ^= 1
         hb = self._host_buffers()[self._slot]
-        hb["actions"][...] = np.asarray(actions, dtype=np.float32).reshape(self.num_envs, nat.ACT_DIM)
+        hb["actions"][...] = np.asarray(actions, dtype=np.float32).reshape(self.num_envs, self.act_dim)
         p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
         self._check(self._lib.usvgpu_step_host(self._h, p(hb["actions"]), p(hb["obs"]), p(hb["reward"]),
                                                p(hb["term"]), p(hb["trunc"]), int(self.mapped_obs), self._stream()))
@@ -223,7 +233,7 @@ class UsvGpuVecEnv:
         if done_idx.size:
             # terminal observations and the (return, length) of the finished episodes, both kept on the device
             idx32 = done_idx.astype(np.int32)
-            tob = np.empty((done_idx.size, nat.OBS_DIM), dtype=np.float32)
+            tob = np.empty((done_idx.size, self.obs_dim), dtype=np.float32)
             epi = np.empty((done_idx.size, 2), dtype=np.float64)
             self._check(self._lib.usvgpu_terminal_obs_host(self._h, idx32.ctypes.data_as(C.c_void_p), idx32.size,
                                                            tob.ctypes.data_as(C.c_void_p),
@@ -276,7 +286,10 @@ class UsvGpuVecEnv:
             return [getattr(self, attr_name)] * len(idx)
         fields = self.get_state()
         if attr_name in ("position", "velocity"):
-            rows = fields["dyn"][0:3] if attr_name == "position" else fields["dyn"][3:6]
+            if self.legacy:  # rows of USV_FIELD_LEGACY: action_last | u v r | x y psi | ...
+                rows = fields["legacy"][4:7] if attr_name == "position" else fields["legacy"][1:4]
+            else:
+                rows = fields["dyn"][0:3] if attr_name == "position" else fields["dyn"][3:6]
             return [rows[:, i].copy() for i in idx]
         raise AttributeError(attr_name)
 
@@ -301,9 +314,14 @@ class UsvGpuVecEnv:
                "obstacles": (nat.FIELD_OBSTACLES, None, (), (3, nat.MAX_OBSTACLES)),
                "n_obs": (nat.FIELD_N_OBS, np.int32, (), ()), "steps": (nat.FIELD_STEPS, np.int32, (), ()),
                "episode": (nat.FIELD_EPISODE, np.int32, (), ()), "ep_return": (nat.FIELD_EP_RETURN, np.float64, (), ())}
+    _LEGACY_FIELDS = {"legacy": (nat.FIELD_LEGACY, np.float32, (nat.LEGACY_ROWS,), ()),
+                      "target": (nat.FIELD_LEGACY_TARGET, np.float64, (6,), ()),
+                      "pos0": (nat.FIELD_LEGACY_POS0, np.float64, (3,), ()),
+                      "steps": (nat.FIELD_STEPS, np.int32, (), ()), "episode": (nat.FIELD_EPISODE, np.int32, (), ()),
+                      "ep_return": (nat.FIELD_EP_RETURN, np.float64, (), ())}
 
     def _field_array(self, name):
-        fid, dt, lead, trail = self._FIELDS[name]
+        fid, dt, lead, trail = (self._LEGACY_FIELDS if self.legacy else self._FIELDS)[name]
         if dt is None:
             dt = np.float32 if self.cfg.obstacles_f32 else np.float64
         return fid, np.zeros(lead + (self.num_envs,) + trail, dtype=dt)
@@ -311,7 +329,7 @@ class UsvGpuVecEnv:
     def get_state(self, names: Optional[Sequence[str]] = None) -> dict:
         """Host copies of the state field groups ([rows][N]; obstacles [N][3][32]); see include/usvgpu.h UsvField."""
         out = {}
-        for name in (names or self._FIELDS):
+        for name in (names or (self._LEGACY_FIELDS if self.legacy else self._FIELDS)):
             fid, arr = self._field_array(name)
             self._check(self._lib.usvgpu_get_state(self._h, fid, arr.ctypes.data_as(C.c_void_p), arr.nbytes,
                                                    self._stream()))

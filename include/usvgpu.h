@@ -91,11 +91,17 @@ typedef enum UsvField {
     USV_FIELD_STEPS = 4,     /* int32 [N]   TimeLimit elapsed steps              */
     USV_FIELD_EPISODE = 5,   /* int32 [N]   resets so far (Philox counter word)  */
     USV_FIELD_EP_RETURN = 6, /* float64 [N] running episode return               */
-    /* legacy env (USV_ENV_ASMC_V0) float32 [25][N]: state[6] velocity[3] position[3] aux[3] last[9] action_last? see DESIGN.md */
+    /* legacy env (USV_ENV_ASMC_V0), float32 [19][N]: action_last (state[5]) | velocity u v r | position x y psi |
+     * aux_vars e_u_int Ka_u Ka_psi | last[9] (usv_asmc_env.py:108-113).  After a step every one of them IS a float32
+     * (usv_asmc_env.py:247-251). */
     USV_FIELD_LEGACY = 7,
-    USV_FIELD_LEGACY_TARGET = 8 /* float64 [6][N]: x_0 y_0 desired_speed ak x_d y_d (usv_asmc_env.py:296) */
+    USV_FIELD_LEGACY_TARGET = 8, /* float64 [6][N]: x_0 y_0 desired_speed ak x_d y_d (usv_asmc_env.py:296) */
+    /* float64 [3][N]: pose x y psi of an env that was reset and has not stepped yet (STEPS == 0): reset() stores
+     * float64 arrays (usv_asmc_env.py:293) and the first step computes in float64 from them */
+    USV_FIELD_LEGACY_POS0 = 9
 } UsvField;
 
+#define USV_LEGACY_ROWS 19
 #define USV_DYN_ROWS 23
 #define USV_EPI_ROWS 7
 
@@ -110,6 +116,13 @@ const char* usvgpu_last_error(usvgpu_handle h);
 int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t global_env_offset, uint64_t seed,
                   usvgpu_handle* out);
 int usvgpu_destroy(usvgpu_handle h);
+/* observation / action width of the handle's env kind: 143 / 2 ('usv-asmc-simple', simple_env.py:27,30) or
+ * 6 / 1 ('usv-asmc-v0', usv_asmc_env.py:89-96).  Every obs / action buffer below is [N][obs_dim] / [N][act_dim].
+ * For 'usv-asmc-v0' usvgpu_reset / usvgpu_step replace UsvAsmcEnv.reset / .step (usv_asmc_env.py:258-300, 99-255):
+ * terminated = the reference's `done`, truncated only with max_episode_steps > 0 (none is registered:
+ * gym_usv/__init__.py:3-6). */
+int usvgpu_obs_dim(usvgpu_handle h);
+int usvgpu_act_dim(usvgpu_handle h);
 
 /* Replaces Env.reset() (simple_env_asmc.py:14-16 -> simple_env.py:228-308) for the envs whose
  * mask byte is non-zero (all envs when mask == NULL).  Writes observation columns 0..14 of the
