@@ -61,6 +61,12 @@ def kernel_bytes(obstacles: bool, obstacles_f32: bool) -> dict:
     return {"usv::dynamics_kernel": dyn, "usv::sensor_kernel": sens}
 
 
+# 'usv-asmc-v0' (UsvAsmcEnv, one sub-step per env-step): float32 SoA state [19], float64 target (4 of 6 rows read)
+#   read : 19 f32 state + 4 f64 target + f32 action + i32 steps + f64 episode return            = 124 B
+#   write: 19 f32 state + 6 f32 observation + f32 reward + 2 flag bytes + i32 steps + f64 return = 118 B
+LEGACY_BYTES = (19 * 4 + 4 * 8 + 4 + 4 + 8) + (19 * 4 + 6 * 4 + 4 + 2 + 4 + 8)
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -149,14 +155,19 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-def cpu_oracle_rate(n_envs: int, budget_s: float, threads: int, ignore_obstacles: bool, seed: int = 0):
+def cpu_oracle_rate(n_envs: int, budget_s: float, threads: int, ignore_obstacles: bool, seed: int = 0,
+                    legacy: bool = False):
     """env-steps/s of the CPU oracle (all `threads` host threads) on n_envs lock-step envs, for ~budget_s."""
     import numpy as np
     import usv_oracle as uo
-    ov = uo.OracleVecEnv(n_envs, seed=seed, ignore_obstacles=ignore_obstacles, n_threads=threads)
-    ov.reset()
     rng = np.random.default_rng(0)
-    acts = rng.uniform([0.2, -1], [1, 1], (8, n_envs, 2)).astype(np.float32)
+    if legacy:
+        ov = uo.OracleLegacyVecEnv(n_envs, seed=seed, n_threads=threads)
+        acts = rng.uniform(-np.pi / 2, np.pi / 2, (8, n_envs)).astype(np.float32)
+    else:
+        ov = uo.OracleVecEnv(n_envs, seed=seed, ignore_obstacles=ignore_obstacles, n_threads=threads)
+        acts = rng.uniform([0.2, -1], [1, 1], (8, n_envs, 2)).astype(np.float32)
+    ov.reset()
     for k in range(2):
         ov.step(acts[k])
     t0 = time.perf_counter()
@@ -187,10 +198,14 @@ def run_reference(args, rank, world):
     import usv_oracle as uo
     threads = host_threads()
     n = args.ref_envs
-    ov = uo.OracleVecEnv(n, seed=args.seed, ignore_obstacles=bool(args.no_obstacles), n_threads=threads)
-    ov.reset()
     rng = np.random.default_rng(0)
-    acts = rng.uniform([0.2, -1], [1, 1], (8, n, 2)).astype(np.float32)
+    if args.env == "usv-asmc-v0":
+        ov = uo.OracleLegacyVecEnv(n, seed=args.seed, n_threads=threads)
+        acts = rng.uniform(-np.pi / 2, np.pi / 2, (8, n)).astype(np.float32)
+    else:
+        ov = uo.OracleVecEnv(n, seed=args.seed, ignore_obstacles=bool(args.no_obstacles), n_threads=threads)
+        acts = rng.uniform([0.2, -1], [1, 1], (8, n, 2)).astype(np.float32)
+    ov.reset()
     for k in range(args.warmup):
         ov.step(acts[k % 8])
     t0 = time.perf_counter()
@@ -201,7 +216,7 @@ def run_reference(args, rank, world):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * el / max(args.steps, 1), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "scaling": "weak", "vs_baseline": None, "dtype": dtype_of(args), "data": "synthetic",
         "config": workload_config(args, world, reference_sample=n),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": f"{n} lock-step envs x {args.steps} steps, OpenMP over {threads} host threads"},
@@ -211,7 +226,24 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def dtype_of(args):
+    if args.env == "usv-asmc-v0":
+        return "f32 state / f64 control terms (the reference's own mix)"
+    return "f64" if args.precision == "f64" else "f64 state / f32 force terms"
+
+
 def workload_config(args, world, reference_sample=None):
+    if args.env == "usv-asmc-v0":
+        cfg = {"workload": f"usv-asmc-v0 (legacy UsvAsmcEnv: ASMC path following without obstacles, one 0.01 s sub-step "
+                           f"per env-step), {args.envs_per_gpu} envs per GPU, BASELINE.json configs[1] secondary reading",
+               "envs_per_gpu": args.envs_per_gpu, "envs_total": args.envs_per_gpu * world, "sub_steps_per_env_step": 1,
+               "max_episode_steps": 0, "auto_reset": True,
+               "sharding": f"contiguous env-index ranges over {world} GPU(s), no data-path collective",
+               "actions": "uniform in the action box, pre-staged on device",
+               "l2": f"{args.batches} rotating env batches per GPU"}
+        if reference_sample is not None:
+            cfg["reference_sample_envs"] = reference_sample
+        return cfg
     cfg = {
         "workload": ("usv-asmc-simple (ASMC path following" + (", obstacles ignored" if args.no_obstacles else
                      " with randomised obstacles + 128-ray range sensors") + f"), {args.envs_per_gpu} envs per GPU, "
@@ -250,13 +282,17 @@ def run_ours(args, rank, local_rank, world):
     for b in range(args.batches):
         e = usv.UsvGpuVecEnv(hi - lo, device=local_rank, seed=args.seed + b, global_env_offset=lo,
                              ignore_obstacles=bool(args.no_obstacles), obstacles_f32=bool(args.obstacles_f32),
-                             precision=args.precision, info_mode="lazy")
+                             precision=args.precision, info_mode="lazy", env_id=args.env)
         e.reset_tensor()
         envs.append(e)
     A = 8
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    acts = torch.rand((A, n, 2), generator=gen, device=dev)
-    acts = (acts * torch.tensor([0.8, 2.0], device=dev) + torch.tensor([0.2, -1.0], device=dev)).contiguous()
+    legacy = args.env == "usv-asmc-v0"
+    if legacy:
+        acts = ((torch.rand((A, n, 1), generator=gen, device=dev) - 0.5) * float(np.pi)).contiguous()
+    else:
+        acts = torch.rand((A, n, 2), generator=gen, device=dev)
+        acts = (acts * torch.tensor([0.8, 2.0], device=dev) + torch.tensor([0.2, -1.0], device=dev)).contiguous()
 
     def sync_all():
         torch.cuda.synchronize(dev)
@@ -323,8 +359,8 @@ def run_ours(args, rank, local_rank, world):
     for e in envs:
         e.mapped_obs = bool(args.mapped_obs)
     e2e_value = e2e_variants["mapped_obs_stores" if args.mapped_obs else "staged_d2h"]
-    h2d = n * 2 * 4
-    d2h = n * (143 * 4 + 4 + 1 + 1)
+    h2d = n * envs[0].act_dim * 4
+    d2h = n * (envs[0].obs_dim * 4 + 4 + 1 + 1)
 
     # ---- per-kernel device time (CUDA events inside the library, on the launching stream) --------------
     kms = [0.0, 0.0]
@@ -345,6 +381,9 @@ def run_ours(args, rank, local_rank, world):
         abytes = algorithmic_bytes(not args.no_obstacles, bool(args.obstacles_f32))
         step_s = (ms * 1e-3) / args.steps  # rank-0 device time per step (two kernels)
         kb = kernel_bytes(not args.no_obstacles, bool(args.obstacles_f32))
+        if legacy:
+            abytes = LEGACY_BYTES
+            kb = {"usv::legacy_step_kernel": LEGACY_BYTES, "-": 0}
         knames = list(kb)
         dom = 0 if kms[0] >= kms[1] else 1
         dom_s = kms[dom] * 1e-3
@@ -352,14 +391,14 @@ def run_ours(args, rank, local_rank, world):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64" if args.precision == "f64" else "f64 state / f32 force terms",
+            "vs_baseline": None, "dtype": dtype_of(args),
             "data": "synthetic", "config": workload_config(args, world),
-            "sub_steps_per_sec": value * 20,
+            "sub_steps_per_sec": value * (1 if legacy else 20),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "variants": e2e_variants,
                     "api": "UsvGpuVecEnv.step(np.ndarray) -> np.ndarray obs/rew/dones + infos of done envs "
                            "(usvgpu_step_host: page-locked host buffers, H2D + kernels + D2H + sync per step)"},
-            "gpu_launches": 2 * args.steps,
+            "gpu_launches": (1 if legacy else 2) * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "kernel": knames[dom],
                          "algorithmic_bytes_per_env_step": kb[knames[dom]], "launch_us": dom_s * 1e6,
@@ -367,16 +406,18 @@ def run_ours(args, rank, local_rank, world):
                          "kernels_bytes_per_env_step": kb,
                          "whole_step": {"algorithmic_bytes_per_env_step": abytes, "us": step_s * 1e6,
                                         "achieved": abytes * n / step_s / 1e9, "frac": abytes * n / step_s / 1e9 / peak},
-                         "note": "both kernels are float64-issue bound, not HBM bound: see DESIGN.md and profiles/"},
+                         "note": ("one kernel per step; float32 SoA state" if legacy else
+                                  "both kernels are float64-issue bound, not HBM bound: see DESIGN.md and profiles/")},
             "clocks": clocks,
             "host_wall_s": t_wall,
             "episode_stats": stats,
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = host_threads()
-            v, st, el = cpu_oracle_rate(args.ref_envs, args.cpu_budget_s, threads, bool(args.no_obstacles), args.seed)
+            v, st, el = cpu_oracle_rate(args.ref_envs, args.cpu_budget_s, threads, bool(args.no_obstacles), args.seed,
+                                        legacy)
             v1, st1, el1 = cpu_oracle_rate(min(args.ref_envs, 1024), max(2.0, args.cpu_budget_s / 4), 1,
-                                           bool(args.no_obstacles), args.seed)
+                                           bool(args.no_obstacles), args.seed, legacy)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"{args.ref_envs} lock-step envs x {st} steps ({el:.1f} s), C oracle, OpenMP",
                                     "single_core_value": v1}
@@ -394,6 +435,7 @@ def main():
     ap.add_argument("--steps", type=int, default=600)
     ap.add_argument("--warmup", type=int, default=30)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--env", default="usv-asmc-simple", choices=["usv-asmc-simple", "usv-asmc-v0"])
     ap.add_argument("--envs-per-gpu", type=int, default=65536)
     ap.add_argument("--batches", type=int, default=3)
     ap.add_argument("--preroll", type=int, default=40, help="untimed steps per batch before warm-up (episode mixing)")
