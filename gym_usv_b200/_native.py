@@ -31,6 +31,7 @@ EPI_ROWS = 7
 
 ENV_ASMC_SIMPLE = 0
 ENV_ASMC_V0 = 1
+ENV_SIMPLE = 2
 PREC_F64 = 0
 PREC_MIXED = 1
 

@@ -33,6 +33,102 @@ constexpr int SENS_WARPS = USV_SENS_WARPS;    // warps (= envs) per CTA of the s
 constexpr int SENS_MIN_CTAS = USV_SENS_MIN_CTAS; // resident CTAs per SM the persistent grid is sized for (<= 80 registers)
 
 // ---------------------------------------------------------------------------------------------
+// UsvSimpleEnv.step (simple_env.py:310-346) without the sensor pass: kinematic update, closest point, truncation,
+// observation header, the reward terms that do not need the sensors, hand-over record.  Shared by 'usv-asmc-simple'
+// (KIN = false: called with a zero action after the 20 ASMC sub-steps) and 'usv-simple' (KIN = true).
+// ---------------------------------------------------------------------------------------------
+template <bool KIN>
+__device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags& fl, const long long i, const long long n,
+                                             Pose& p, double& cs, double& sn, double& progress, int& steps,
+                                             const double a0, const double a1) {
+    // episode constants are only needed from here on: loaded late to keep them out of the sub-step loop's registers
+    double* dyn = s.dyn + i;
+    progress = dyn[(long long)D_PROGRESS * n];
+    const double* epi = s.epi + i;
+    const double psx = epi[(long long)E_PSX * n], psy = epi[(long long)E_PSY * n];
+    const double pex = epi[(long long)E_PEX * n], pey = epi[(long long)E_PEY * n];
+    const double ma0 = epi[(long long)E_MA0 * n], ma2 = epi[(long long)E_MA2 * n];
+    const double vref = epi[(long long)E_VREF * n];
+
+    // ---- UsvSimpleEnv.step: kinematic update, simple_env.py:311-324 -----------------------------
+    // 'usv-asmc-simple' calls it with zeros(2) and its last_action is 0 for the whole life of the env, so the
+    // commanded velocity is 0 (KIN = false: c0 = c2 = 0 fold away).  'usv-simple' (KIN): action = 0.8 * last_action
+    // + 0.2 * max_action * [a0, 0, a1]; last_action survives resets (it is only set in __init__ and :343).
+    double c0 = 0.0, c2 = 0.0, la0 = 0.0, la2 = 0.0;
+    if (KIN) {
+        la0 = dyn[(long long)D_LA0 * n];
+        la2 = dyn[(long long)D_LA2 * n];
+        c0 = 0.8 * la0 + 0.2 * (ma0 * a0);
+        c2 = 0.8 * la2 + 0.2 * (ma2 * a1);
+        dyn[(long long)D_LA0 * n] = c0;  // :343 last_action = action
+        dyn[(long long)D_LA2 * n] = c2;
+    }
+    if (KIN || !fl.skip_kinematic) {
+        const double du = np_clip(c0 - p.u, -MAX_ACC_U, MAX_ACC_U);
+        p.u = np_clip(p.u + du, -ma0, ma0);
+        p.v = 0.0;  // clip(v + clip(-v, -0, 0), -0, 0): max_acceleration[1] = max_action[1] = 0
+        const double dr = np_clip(c2 - p.r, -MAX_ACC_R, MAX_ACC_R);
+        p.r = np_clip(p.r + dr, -ma2, ma2);
+        if (p.u != 0.0) {  // only when |u| > 1.75: the carried cos/sin are good to ~1e-15
+            p.x = p.x + (p.u * cs) * DT;
+            p.y = p.y + (p.u * sn) * DT;
+        }
+        p.psi = p.psi + p.r * DT;
+    }
+    sincos(p.psi, &sn, &cs);  // heading of the pose the sensors see (usv_asmc_ca_env.py:420-424)
+
+    // ---- closest point on the path, simple_env.py:139-148 ------------------------------------
+    const double pdx = pex - psx, pdy = pey - psy;
+    const double det = pdx * pdx + pdy * pdy;
+    double a = div_k(pdy * (p.y - psy) + pdx * (p.x - psx), det);
+    a += (0.005 / 10) * ENV_HI;
+    a = np_clip(a, progress, 1.0);
+    const double tgx = psx + a * pdx, tgy = psy + a * pdy;
+    progress = a;
+
+    // ---- truncation, simple_env.py:336 + TimeLimit (gym_usv/__init__.py:33) ------------------
+    const bool oob = (p.x > ENV_HI) || (p.y > ENV_HI) || (p.x < 0.0) || (p.y < 0.0);
+    steps += 1;
+    const bool tlimit = (fl.max_episode_steps > 0) && (steps >= fl.max_episode_steps);
+
+    // ---- observation header, simple_env.py:72-96 ---------------------------------------------
+    double half_inv_len;
+    sqrt_k(det, half_inv_len);
+    const double inv_len = 2.0 * half_inv_len;
+    const double ye = -(p.x - psx) * (pdy * inv_len) + (p.y - psy) * (pdx * inv_len);  // :133-137
+    const double ang = wrap_pi(atan2(tgy - p.y, tgx - p.x) - p.psi);                  // :67-69
+    const double tdx = p.x - tgx, tdy = p.y - tgy;
+    const double tdist = sqrt_k(fma(tdx, tdx, tdy * tdy));
+    // the reference divides (x / 10, angle / pi, ...): multiplying by the rounded reciprocal differs by at
+    // most one float64 ulp before the float32 rounding.  Columns 7, 8 (last_action), 10 (max_action[1]) and
+    // 13 (max_acceleration[1]) are 0 for the whole life of this env.
+    float4* hrow = reinterpret_cast<float4*>(s.hdr16 + i * HDR_PAD);
+    hrow[0] = make_float4((float)(p.u * 0.1), (float)(p.v * 0.1), (float)(p.r * 0.1), (float)(ang * (1.0 / PI)));
+    // columns 7, 8: the PREVIOUS last_action[[0, 2]] / max_action[[0, 2]] (:338 runs before :343)
+    hrow[1] = make_float4((float)(tdist * (1.0 / DIST_NORM)), (float)(ye * 0.1), (float)(vref * 0.1),
+                          KIN ? (float)(la0 / ma0) : 0.0f);
+    hrow[2] = make_float4(KIN ? (float)(la2 / ma2) : 0.0f, (float)(ma0 * 0.1), 0.0f, (float)(ma2 * 0.1));
+    hrow[3] = make_float4((float)(MAX_ACC_U / 10), 0.0f, (float)(MAX_ACC_R / 10), 0.0f);
+
+    // ---- reward without the collision term, simple_env.py:150-201 ----------------------------
+    const double t = ye * (1.0 / 0.075);
+    const double at = fabs(t);
+    const double ye_reward = exp(-fmin(at, t * t));  // max(exp(-|t|), exp(-t^2)): exp is monotone
+    const double angle_reward = exp(-fabs(ang));
+    const double vel_reward = exp(-fabs(sqrt_k(fma(p.u, p.u, p.v * p.v)) - vref)) * 0.05;
+    Hand hd;
+    hd.x = p.x;
+    hd.y = p.y;
+    hd.cs = cs;
+    hd.sn = sn;
+    hd.rew_part = ye_reward + angle_reward + vel_reward;  // arrived = 0
+    if (KIN) hd.rew_part += -((fabs(la0 - c0) + fabs(la2 - c2)) / 2) * 0.15;  // delta_action_reward, :176
+    hd.flags = (oob ? FLG_OOB : 0u) | (tlimit ? FLG_TLIMIT : 0u);
+    hd.pad = 0u;
+    s.hand[i] = hd;
+}
+
+// ---------------------------------------------------------------------------------------------
 template <bool PERTURB>
 __global__ void __launch_bounds__(DYN_B, DYN_MIN_CTAS)
 dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
@@ -77,77 +173,8 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
 #pragma unroll 1
     for (int k = 0; k < 20; ++k) asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
 
-    // episode constants are only needed from here on: loaded late to keep them out of the sub-step loop's registers
-    double progress = dyn[(long long)D_PROGRESS * n];
-    const double* epi = s.epi + i;
-    const double psx = epi[(long long)E_PSX * n], psy = epi[(long long)E_PSY * n];
-    const double pex = epi[(long long)E_PEX * n], pey = epi[(long long)E_PEY * n];
-    const double ma0 = epi[(long long)E_MA0 * n], ma2 = epi[(long long)E_MA2 * n];
-    const double vref = epi[(long long)E_VREF * n];
-
-    // ---- UsvSimpleEnv.step(zeros(2)): kinematic post-step, simple_env.py:311-324 -------------
-    // action = 0.8*last_action + 0.2*(max_action*0) and last_action is 0 for the whole life of
-    // this env, so the commanded velocity is 0.
-    if (!fl.skip_kinematic) {
-        const double du = np_clip(0.0 - p.u, -MAX_ACC_U, MAX_ACC_U);
-        p.u = np_clip(p.u + du, -ma0, ma0);
-        p.v = 0.0;  // clip(v + clip(-v, -0, 0), -0, 0): max_acceleration[1] = max_action[1] = 0
-        const double dr = np_clip(0.0 - p.r, -MAX_ACC_R, MAX_ACC_R);
-        p.r = np_clip(p.r + dr, -ma2, ma2);
-        if (p.u != 0.0) {  // only when |u| > 1.75: the carried cos/sin are good to ~1e-15
-            p.x = p.x + (p.u * cs) * DT;
-            p.y = p.y + (p.u * sn) * DT;
-        }
-        p.psi = p.psi + p.r * DT;
-    }
-    sincos(p.psi, &sn, &cs);  // heading of the pose the sensors see (usv_asmc_ca_env.py:420-424)
-
-    // ---- closest point on the path, simple_env.py:139-148 ------------------------------------
-    const double pdx = pex - psx, pdy = pey - psy;
-    const double det = pdx * pdx + pdy * pdy;
-    double a = div_k(pdy * (p.y - psy) + pdx * (p.x - psx), det);
-    a += (0.005 / 10) * ENV_HI;
-    a = np_clip(a, progress, 1.0);
-    const double tgx = psx + a * pdx, tgy = psy + a * pdy;
-    progress = a;
-
-    // ---- truncation, simple_env.py:336 + TimeLimit (gym_usv/__init__.py:33) ------------------
-    const bool oob = (p.x > ENV_HI) || (p.y > ENV_HI) || (p.x < 0.0) || (p.y < 0.0);
-    steps += 1;
-    const bool tlimit = (fl.max_episode_steps > 0) && (steps >= fl.max_episode_steps);
-
-    // ---- observation header, simple_env.py:72-96 ---------------------------------------------
-    double half_inv_len;
-    sqrt_k(det, half_inv_len);
-    const double inv_len = 2.0 * half_inv_len;
-    const double ye = -(p.x - psx) * (pdy * inv_len) + (p.y - psy) * (pdx * inv_len);  // :133-137
-    const double ang = wrap_pi(atan2(tgy - p.y, tgx - p.x) - p.psi);                  // :67-69
-    const double tdx = p.x - tgx, tdy = p.y - tgy;
-    const double tdist = sqrt_k(fma(tdx, tdx, tdy * tdy));
-    // the reference divides (x / 10, angle / pi, ...): multiplying by the rounded reciprocal differs by at
-    // most one float64 ulp before the float32 rounding.  Columns 7, 8 (last_action), 10 (max_action[1]) and
-    // 13 (max_acceleration[1]) are 0 for the whole life of this env.
-    float4* hrow = reinterpret_cast<float4*>(s.hdr16 + i * HDR_PAD);
-    hrow[0] = make_float4((float)(p.u * 0.1), (float)(p.v * 0.1), (float)(p.r * 0.1), (float)(ang * (1.0 / PI)));
-    hrow[1] = make_float4((float)(tdist * (1.0 / DIST_NORM)), (float)(ye * 0.1), (float)(vref * 0.1), 0.0f);
-    hrow[2] = make_float4(0.0f, (float)(ma0 * 0.1), 0.0f, (float)(ma2 * 0.1));
-    hrow[3] = make_float4((float)(MAX_ACC_U / 10), 0.0f, (float)(MAX_ACC_R / 10), 0.0f);
-
-    // ---- reward without the collision term, simple_env.py:150-201 ----------------------------
-    const double t = ye * (1.0 / 0.075);
-    const double at = fabs(t);
-    const double ye_reward = exp(-fmin(at, t * t));  // max(exp(-|t|), exp(-t^2)): exp is monotone
-    const double angle_reward = exp(-fabs(ang));
-    const double vel_reward = exp(-fabs(sqrt_k(fma(p.u, p.u, p.v * p.v)) - vref)) * 0.05;
-    Hand hd;
-    hd.x = p.x;
-    hd.y = p.y;
-    hd.cs = cs;
-    hd.sn = sn;
-    hd.rew_part = ye_reward + angle_reward + vel_reward;  // delta_action_reward = -0, arrived = 0
-    hd.flags = (oob ? FLG_OOB : 0u) | (tlimit ? FLG_TLIMIT : 0u);
-    hd.pad = 0u;
-    s.hand[i] = hd;
+    double progress;
+    wrapper_tail<false>(s, fl, i, n, p, cs, sn, progress, steps, 0.0, 0.0);
     if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.psi))) atomicAdd(&s.stats->nonfinite, 1ull);
 
     // ---- store state ---------------------------------------------------------------------------
@@ -173,6 +200,42 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     dyn[(long long)D_EU_INT * n] = c.eu_int;
     dyn[(long long)D_KA_U * n] = c.ka_u;
     dyn[(long long)D_KA_PSI * n] = c.ka_psi;
+    dyn[(long long)D_PROGRESS * n] = progress;
+    s.steps[i] = steps;
+}
+
+// ---------------------------------------------------------------------------------------------
+// 'usv-simple' (UsvSimpleEnv.step, simple_env.py:310-346; the env train_test/sb3_train_vec.py:55 trains on): the
+// action drives the kinematic update directly, no controller.  Thread per env, 9 float64 columns in, 9 out, then the
+// same hand-over to sensor_kernel as dynamics_kernel.  HBM-bound.
+// ---------------------------------------------------------------------------------------------
+constexpr int KIN_B = 128;
+__global__ void __launch_bounds__(KIN_B)
+kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
+    const long long n = s.n;
+    const long long i = fl.lo + (long long)blockIdx.x * KIN_B + threadIdx.x;
+    if (i >= fl.hi) return;
+    double* dyn = s.dyn + i;
+    Pose p;
+    p.x = dyn[(long long)D_X * n];
+    p.y = dyn[(long long)D_Y * n];
+    p.psi = dyn[(long long)D_PSI * n];
+    p.u = dyn[(long long)D_U * n];
+    p.v = dyn[(long long)D_V * n];
+    p.r = dyn[(long long)D_R * n];
+    int steps = s.steps[i];
+    const float2 af = reinterpret_cast<const float2*>(actions)[i];
+    double sn, cs;
+    sincos(p.psi, &sn, &cs);  // theta = position[2] before the update, simple_env.py:321
+    double progress;
+    wrapper_tail<true>(s, fl, i, n, p, cs, sn, progress, steps, (double)af.x, (double)af.y);
+    if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.psi))) atomicAdd(&s.stats->nonfinite, 1ull);
+    dyn[(long long)D_X * n] = p.x;
+    dyn[(long long)D_Y * n] = p.y;
+    dyn[(long long)D_PSI * n] = p.psi;
+    dyn[(long long)D_U * n] = p.u;
+    dyn[(long long)D_V * n] = p.v;
+    dyn[(long long)D_R * n] = p.r;
     dyn[(long long)D_PROGRESS * n] = progress;
     s.steps[i] = steps;
 }

@@ -127,7 +127,10 @@ __device__ void reset_env(const StatePtrs& s, long long i, float* hdr) {
     }
     s.n_obs[i] = kept;
 #pragma unroll
-    for (int k = 0; k < N_DYN; ++k) s.dyn[(long long)k * n + i] = reset_dyn_row(q, k);  // fresh UsvAsmc(), progress = 0
+    for (int k = 0; k < N_DYN; ++k) {  // fresh UsvAsmc(), progress = 0
+        if (s.kinematic && (k == D_LA0 || k == D_LA2)) continue;
+        s.dyn[(long long)k * n + i] = reset_dyn_row(q, k);
+    }
 #pragma unroll
     for (int k = 0; k < N_EPI; ++k) s.epi[(long long)k * n + i] = reset_epi_row(q, k);
     if (hdr) {
@@ -191,7 +194,7 @@ __device__ float reset_env_warp(const StatePtrs& s, long long i, int lane) {
         s.ep_return[i] = 0.0;
         s.n_obs[i] = kept;
     }
-    if (lane < N_DYN) s.dyn[(long long)lane * n + i] = reset_dyn_row(q, lane);
+    if (lane < N_DYN && !(s.kinematic && (lane == D_LA0 || lane == D_LA2))) s.dyn[(long long)lane * n + i] = reset_dyn_row(q, lane);
     if (lane < N_EPI) s.epi[(long long)lane * n + i] = reset_epi_row(q, lane);
     float h[HDR];
     reset_header(q, h);

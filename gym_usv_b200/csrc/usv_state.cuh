@@ -30,6 +30,9 @@ enum DynRow {
     N_DYN
 };
 static_assert(N_DYN == USV_DYN_ROWS, "header/kernel row count mismatch");
+// 'usv-simple' (UsvSimpleEnv itself, no ASMC controller): the controller rows are unused and two of them hold
+// last_action[0] and last_action[2] (simple_env.py:41,343), which a reset does NOT clear
+constexpr int D_LA0 = D_XD_L, D_LA2 = D_YD_L;
 // rows of USV_FIELD_EPI
 enum EpiRow { E_PSX = 0, E_PSY, E_PEX, E_PEY, E_MA0, E_MA2, E_VREF, N_EPI };
 static_assert(N_EPI == USV_EPI_ROWS, "header/kernel row count mismatch");
@@ -77,6 +80,7 @@ struct StatePtrs {
     long long n;
     long long global_offset;
     unsigned long long seed;
+    int kinematic;          // env kind 'usv-simple': rows D_LA0 / D_LA2 survive resets
 };
 
 struct StepFlags {

@@ -116,7 +116,9 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
         return USV_OK;
     }
     const unsigned dblocks = (unsigned)((hi - lo + DYN_B - 1) / DYN_B);
-    if (h->cfg.do_perturb) dynamics_kernel<true><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
+    if (h->cfg.env_kind == USV_ENV_SIMPLE)
+        kinematic_kernel<<<(unsigned)((hi - lo + KIN_B - 1) / KIN_B), KIN_B, 0, st>>>(h->sp, fl, actions);
+    else if (h->cfg.do_perturb) dynamics_kernel<true><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
     else dynamics_kernel<false><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("dynamics launch: ") + cudaGetErrorString(e));
@@ -168,7 +170,7 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     if (!cfg || !out) return fail(nullptr, USV_ERR_INVALID, "cfg/out is NULL");
     *out = nullptr;
     if (n_envs <= 0) return fail(nullptr, USV_ERR_INVALID, "n_envs must be positive");
-    if (cfg->env_kind != USV_ENV_ASMC_SIMPLE && cfg->env_kind != USV_ENV_ASMC_V0)
+    if (cfg->env_kind != USV_ENV_ASMC_SIMPLE && cfg->env_kind != USV_ENV_ASMC_V0 && cfg->env_kind != USV_ENV_SIMPLE)
         return fail(nullptr, USV_ERR_INVALID, "unknown env_kind");
     if (cfg->precision != USV_PREC_F64) return fail(nullptr, USV_ERR_INVALID, "precision not supported by this build");
     int rc = check_device(nullptr, device);
@@ -202,6 +204,7 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->sp.n = n_envs;
     h->sp.global_offset = global_env_offset;
     h->sp.seed = seed;
+    h->sp.kinematic = cfg->env_kind == USV_ENV_SIMPLE;
     const size_t n = (size_t)n_envs;
     cudaError_t e = cudaSetDevice(device);
     auto alloc = [&](void** p, size_t bytes) {

@@ -26,8 +26,8 @@ from . import spaces
 
 ENV_ID = "usv-asmc-simple"
 # gym_usv/__init__.py:30-34 registers a 1000-step TimeLimit for 'usv-asmc-simple' and none for 'usv-asmc-v0' (:3-6)
-MAX_EPISODE_STEPS = {"usv-asmc-simple": 1000, "usv-asmc-v0": 0}
-ENV_KINDS = {"usv-asmc-simple": nat.ENV_ASMC_SIMPLE, "usv-asmc-v0": nat.ENV_ASMC_V0}
+MAX_EPISODE_STEPS = {"usv-asmc-simple": 1000, "usv-asmc-v0": 0, "usv-simple": 500}  # usv-simple: __init__.py:24-28
+ENV_KINDS = {"usv-asmc-simple": nat.ENV_ASMC_SIMPLE, "usv-asmc-v0": nat.ENV_ASMC_V0, "usv-simple": nat.ENV_SIMPLE}
 
 
 class LazyInfos(Sequence):

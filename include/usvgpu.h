@@ -39,7 +39,11 @@ typedef enum UsvStatus {
 
 typedef enum UsvEnvKind {
     USV_ENV_ASMC_SIMPLE = 0, /* 'usv-asmc-simple' gym_usv/__init__.py:30-34 -> envs/simple_env_asmc.py */
-    USV_ENV_ASMC_V0 = 1      /* 'usv-asmc-v0'     gym_usv/__init__.py:3-6   -> envs/usv_asmc_env.py    */
+    USV_ENV_ASMC_V0 = 1,     /* 'usv-asmc-v0'     gym_usv/__init__.py:3-6   -> envs/usv_asmc_env.py    */
+    USV_ENV_SIMPLE = 2       /* 'usv-simple'      gym_usv/__init__.py:24-28 -> envs/simple_env.py: the kinematic
+                              * env train_test/sb3_train_vec.py:55 trains on (TimeLimit 500).  Same spaces, state
+                              * fields and entry points as 'usv-asmc-simple'; USV_FIELD_DYN rows 6 and 7 hold
+                              * last_action[0] and last_action[2] (simple_env.py:41,343), rows 8..21 are unused */
 } UsvEnvKind;
 
 typedef enum UsvPrecision {

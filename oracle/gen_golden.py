@@ -121,7 +121,7 @@ def _reset_record(env, obs):
                 v_ref=float(env.reference_velocity), n_obs=n, ox=ox, oy=oy, rad=rad, obs=np.array(obs))
 
 
-def gen_simple_env(R, name, seeds, steps, ignore_obstacles):
+def gen_simple_env(R, name, seeds, steps, ignore_obstacles, cls="UsvSimpleASMCEnv", limit=1000):
     acts = action_stream(steps)
     E = len(seeds)
     obs = np.zeros((E, steps, 143), np.float32)
@@ -133,9 +133,9 @@ def gen_simple_env(R, name, seeds, steps, ignore_obstacles):
     prog = np.zeros((E, steps))
     resets = []  # (env, step index BEFORE which the reset happened, record)
     for e, seed in enumerate(seeds):
-        env = R.UsvSimpleASMCEnv()
+        env = getattr(R, cls)()
         env.ignore_obstacles = ignore_obstacles
-        tl = rh.TimeLimit(env, 1000)  # gym_usv/__init__.py:30-34
+        tl = rh.TimeLimit(env, limit)  # gym_usv/__init__.py:24-34
         o, _ = tl.reset(seed=seed)
         resets.append((e, 0, _reset_record(env, o)))
         for t in range(steps):
@@ -225,7 +225,7 @@ def gen_legacy(R):
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     R = rh.load_reference()
-    which = sys.argv[1:] or ["asmc", "sensors", "simple", "simple_noobs", "resets", "legacy"]
+    which = sys.argv[1:] or ["asmc", "sensors", "simple", "simple_noobs", "resets", "legacy", "kinematic"]
     if "asmc" in which:
         gen_asmc(R)
     if "sensors" in which:
@@ -238,3 +238,6 @@ if __name__ == "__main__":
         gen_reset_samples(R)
     if "legacy" in which:
         gen_legacy(R)
+    if "kinematic" in which:  # 'usv-simple' = UsvSimpleEnv itself, TimeLimit 500 (gym_usv/__init__.py:24-28)
+        gen_simple_env(R, "simple_kinematic_env.npz", seeds=[200, 201, 202], steps=700, ignore_obstacles=False,
+                       cls="UsvSimpleEnv", limit=500)

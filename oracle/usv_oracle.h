@@ -66,7 +66,8 @@ typedef struct UsvOracleConfig {
     int32_t auto_reset;           /* SB3 VecEnv semantics                     */
     int32_t obstacles_f32;        /* round reset obstacle tables to float32   */
     int32_t n_threads;            /* OpenMP threads for the vec entry points  */
-    int32_t pad_;
+    int32_t kinematic;            /* 1: 'usv-simple' = UsvSimpleEnv.step itself (simple_env.py:310-346, the action
+                                   * drives the kinematic update); 0: 'usv-asmc-simple' (simple_env_asmc.py:18-27) */
 } UsvOracleConfig;
 
 int  usv_oracle_sizeof_env(void);
@@ -94,7 +95,7 @@ void usv_oracle_simple_reset_obs(const UsvOracleEnv* e, float* obs);
 /* first construction: simple_env.py:32-54 defaults */
 void usv_oracle_simple_init(UsvOracleEnv* e);
 
-/* simple_env_asmc.py:18-27 -> simple_env.py:310-346 (+ TimeLimit) */
+/* simple_env_asmc.py:18-27 -> simple_env.py:310-346 (+ TimeLimit); cfg->kinematic: simple_env.py:310-346 alone */
 void usv_oracle_simple_step(UsvOracleEnv* e, const UsvOracleConfig* cfg, const float action[2],
                             float* obs, double* reward, uint8_t* terminated, uint8_t* truncated);
 

@@ -82,7 +82,7 @@ class Config(C.Structure):
         ("auto_reset", C.c_int32),
         ("obstacles_f32", C.c_int32),
         ("n_threads", C.c_int32),
-        ("pad_", C.c_int32),
+        ("kinematic", C.c_int32),
     ]
 
 
@@ -148,9 +148,9 @@ def _p(a):
 
 
 def make_config(ignore_obstacles=False, do_perturb=False, skip_kinematic=False, max_episode_steps=1000,
-                auto_reset=True, obstacles_f32=False, n_threads=0) -> Config:
+                auto_reset=True, obstacles_f32=False, n_threads=0, kinematic=False) -> Config:
     return Config(int(ignore_obstacles), int(do_perturb), int(skip_kinematic), int(max_episode_steps),
-                  int(auto_reset), int(obstacles_f32), int(n_threads), 0)
+                  int(auto_reset), int(obstacles_f32), int(n_threads), int(kinematic))
 
 
 # ---------------------------------------------------------------------------------------

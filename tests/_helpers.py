@@ -44,10 +44,14 @@ def inject_oracle(env_arr, i, g, k):
     env_arr["ep_return"][i] = 0
 
 
-def inject_gpu(state, i, g, k):
-    """Put golden reset record k into column i of a UsvGpuVecEnv.get_state() dict (in place)."""
+def inject_gpu(state, i, g, k, keep_rows=()):
+    """Put golden reset record k into column i of a UsvGpuVecEnv.get_state() dict (in place); keep_rows of
+    USV_FIELD_DYN are left as they are ('usv-simple': last_action survives a reset)."""
     dyn, epi = state["dyn"], state["epi"]
+    kept = [dyn[r, i] for r in keep_rows]
     dyn[:, i] = 0
+    for r, v in zip(keep_rows, kept):
+        dyn[r, i] = v
     dyn[0:3, i] = g["reset_position"][k]
     dyn[3:6, i] = g["reset_velocity"][k]
     epi[0:2, i] = g["reset_path_start"][k]

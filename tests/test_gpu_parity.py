@@ -250,15 +250,16 @@ def test_sensors_key_ties_take_the_exact_path(usv):
 # ------------------------------------------------------------------------------------------
 # env step: golden replay (reference states injected) and oracle lock-step
 # ------------------------------------------------------------------------------------------
-def _gpu_replay(usv, gname, ignore_obstacles):
+def _gpu_replay(usv, gname, ignore_obstacles, env_id="usv-asmc-simple"):
     g = load_golden(gname)
     acts = g["actions"]
     E, T = g["obs"].shape[:2]
     rmap = golden_reset_maps(g)
-    env = usv.UsvGpuVecEnv(E, device=0, ignore_obstacles=ignore_obstacles, auto_reset=False)
+    env = usv.UsvGpuVecEnv(E, device=0, ignore_obstacles=ignore_obstacles, auto_reset=False, env_id=env_id)
+    keep = (6, 7) if env_id == "usv-simple" else ()  # last_action survives resets (simple_env.py:41,343)
     st = env.get_state()
     for e in range(E):
-        inject_gpu(st, e, g, rmap[e][0])
+        inject_gpu(st, e, g, rmap[e][0], keep_rows=keep)
     env.set_state(st)
     worst = dict(pos=0.0, vel=0.0, rew=0.0, obs=0.0)
     ndone = 0
@@ -277,7 +278,7 @@ def _gpu_replay(usv, gname, ignore_obstacles):
         if done.size:
             st = env.get_state()
             for e in done:
-                inject_gpu(st, int(e), g, rmap[int(e)][t + 1])
+                inject_gpu(st, int(e), g, rmap[int(e)][t + 1], keep_rows=keep)
                 ndone += 1
             env.set_state(st)
     env.close()
@@ -295,14 +296,23 @@ def test_env_golden_replay_ignore_obstacles(usv):
     assert w["pos"] < POSE_ATOL and w["vel"] < POSE_ATOL and w["rew"] < 2e-5 and w["obs"] < OBS_ATOL, w
 
 
-@pytest.mark.parametrize("ignore_obstacles,obstacles_f32", [(False, False), (False, True), (True, False)])
-def test_vec_env_lockstep_vs_oracle_with_autoreset(usv, ignore_obstacles, obstacles_f32):
+def test_kinematic_env_golden_replay(usv):
+    """'usv-simple' (UsvSimpleEnv itself, TimeLimit 500): 3 reference rollouts of 700 steps."""
+    w, ndone = _gpu_replay(usv, "simple_kinematic_env.npz", False, env_id="usv-simple")
+    assert ndone >= 3
+    assert w["pos"] < POSE_ATOL and w["vel"] < POSE_ATOL and w["rew"] < 2e-5 and w["obs"] < OBS_ATOL, w
+
+
+@pytest.mark.parametrize("ignore_obstacles,obstacles_f32,env_id", [
+    (False, False, "usv-asmc-simple"), (False, True, "usv-asmc-simple"), (True, False, "usv-asmc-simple"),
+    (False, False, "usv-simple"), (False, True, "usv-simple")])
+def test_vec_env_lockstep_vs_oracle_with_autoreset(usv, ignore_obstacles, obstacles_f32, env_id):
     """N envs, in-kernel Philox reset on both sides, SB3 auto-reset, 400 steps: flags and episode
     lengths exact, observations (incl. 128 sensor columns), rewards and terminal observations to tolerance."""
     N, T, seed, off = 1536, 400, 5, 1000
     kw = dict(ignore_obstacles=ignore_obstacles, obstacles_f32=obstacles_f32, max_episode_steps=150)
-    env = usv.UsvGpuVecEnv(N, device=0, seed=seed, global_env_offset=off, **kw)
-    ov = uo.OracleVecEnv(N, seed=seed, global_offset=off, **kw)
+    env = usv.UsvGpuVecEnv(N, device=0, seed=seed, global_env_offset=off, env_id=env_id, **kw)
+    ov = uo.OracleVecEnv(N, seed=seed, global_offset=off, kinematic=(env_id == "usv-simple"), **kw)
     o_gpu = env.reset_tensor().cpu().numpy()
     o_cpu = ov.reset()
     np.testing.assert_allclose(o_gpu[:, :15], o_cpu[:, :15], rtol=0, atol=OBS_ATOL)
@@ -336,6 +346,8 @@ def test_vec_env_lockstep_vs_oracle_with_autoreset(usv, ignore_obstacles, obstac
     assert np.array_equal(st["steps"], want["steps"]) and np.array_equal(st["episode"], want["episode"])
     assert np.array_equal(st["n_obs"], want["n_obs"])
     np.testing.assert_allclose(st["dyn"][:6], want["dyn"][:6], rtol=0, atol=POSE_ATOL)
+    if env_id == "usv-simple":  # last_action[0], last_action[2] live in rows 6, 7 and survive the resets
+        np.testing.assert_allclose(st["dyn"][6:8].T, ov.envs["last_action"][:, [0, 2]], rtol=0, atol=1e-12)
     np.testing.assert_allclose(st["epi"], want["epi"], rtol=1e-13, atol=1e-13)
     k = np.arange(32)[None, :] < want["n_obs"][:, None]
     for f in range(3):

@@ -106,12 +106,13 @@ def test_sensors_match_reference():
 # ------------------------------------------------------------------------------------------
 # UsvSimpleASMCEnv.step (simple_env_asmc.py:18-27 -> simple_env.py:310-346) + TimeLimit
 # ------------------------------------------------------------------------------------------
-def _replay(gname, ignore_obstacles):
+def _replay(gname, ignore_obstacles, kinematic=False, limit=1000):
     g = load_golden(gname)
     acts = g["actions"]
     E, T = g["obs"].shape[:2]
     rmap = golden_reset_maps(g)
-    ov = uo.OracleVecEnv(E, ignore_obstacles=ignore_obstacles, auto_reset=False, max_episode_steps=1000)
+    ov = uo.OracleVecEnv(E, ignore_obstacles=ignore_obstacles, auto_reset=False, max_episode_steps=limit,
+                         kinematic=kinematic)
     for e in range(E):
         inject_oracle(ov.envs, e, g, rmap[e][0])
     # reset observation: header from the state, sensors stale (zeros on the very first reset)
@@ -152,6 +153,14 @@ def test_simple_asmc_env_with_obstacles_1000_steps():
 
 def test_simple_asmc_env_ignore_obstacles_1000_steps():
     s = _replay("simple_asmc_env_noobs.npz", ignore_obstacles=True)
+    assert s["pos"] < 1e-9 and s["vel"] < 1e-9 and s["rew"] < 1e-9 and s["obs"] < 1e-6, s
+
+
+def test_simple_kinematic_env_700_steps():
+    """'usv-simple' (UsvSimpleEnv itself, what train_test/sb3_train_vec.py:55 trains on): the action drives the
+    kinematic update (simple_env.py:311-324), last_action survives resets (W9), TimeLimit 500."""
+    s = _replay("simple_kinematic_env.npz", ignore_obstacles=False, kinematic=True, limit=500)
+    assert s["done"] >= 3
     assert s["pos"] < 1e-9 and s["vel"] < 1e-9 and s["rew"] < 1e-9 and s["obs"] < 1e-6, s
 
 
