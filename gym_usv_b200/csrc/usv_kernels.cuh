@@ -398,6 +398,45 @@ gather_rows_kernel(const float* __restrict__ src, const double2* __restrict__ ep
 }
 
 // ---------------------------------------------------------------------------------------------
+// On-device VecFrameStack (stable_baselines3 StackedObservations.update, used at train_test/sb3_train_vec.py:70 with
+// n_stack = 5) WITHOUT moving old frames: per env a ring of 2 * n_stack slots, every new frame is stored twice (slot
+// pos and slot pos + n_stack), so the n_stack most recent frames are always one contiguous run of the row, slots
+// pos + 1 .. pos + n_stack.  np.roll over [N][n_stack * obs_dim] would read 4 and write 5 frames per env-step; this
+// writes 2.  Done envs: the stacked terminal observation (previous n_stack - 1 frames + terminal_observation) goes to
+// terminal_stack, the older frames are zeroed (SB3: stacked_obs[env] = 0 before the reset observation is stored).
+// One warp per env.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+frame_push_kernel(long long n, int obs_dim, int n_stack, int pos, float* __restrict__ ring, const float* __restrict__ obs,
+                  const uint8_t* __restrict__ terminated, const uint8_t* __restrict__ truncated,
+                  const float* __restrict__ terminal_obs, float* __restrict__ terminal_stack) {
+    const long long i = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const int lane = threadIdx.x & 31;
+    float* row = ring + i * 2 * n_stack * obs_dim;
+    const bool done = (terminated && terminated[i]) || (truncated && truncated[i]);
+    if (done) {
+        // previous window = slots pos .. pos + n_stack - 1 (frames t - n_stack .. t - 1); SB3 keeps its last
+        // n_stack - 1 frames and appends the terminal observation
+        if (terminal_stack && terminal_obs) {
+            float* ts = terminal_stack + i * n_stack * obs_dim;
+            const float* prev = row + (pos + 1) * obs_dim;
+            for (int c = lane; c < (n_stack - 1) * obs_dim; c += 32) ts[c] = prev[c];
+            for (int c = lane; c < obs_dim; c += 32) ts[(n_stack - 1) * obs_dim + c] = terminal_obs[i * obs_dim + c];
+        }
+        __syncwarp();
+        for (int c = lane; c < 2 * n_stack * obs_dim; c += 32) row[c] = 0.0f;
+        __syncwarp();
+    }
+    const float* o = obs + i * obs_dim;
+    for (int c = lane; c < obs_dim; c += 32) {
+        const float v = o[c];
+        row[pos * obs_dim + c] = v;
+        row[(pos + n_stack) * obs_dim + c] = v;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Unit-parity kernels
 // ---------------------------------------------------------------------------------------------
 template <bool PERTURB>

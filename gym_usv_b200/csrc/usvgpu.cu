@@ -631,6 +631,20 @@ int usvgpu_sensors(int device, int64_t n, const double* pose, const double* obst
     return USV_OK;
 }
 
+int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_stack, int32_t pos, float* ring,
+                            const float* obs, const uint8_t* terminated, const uint8_t* truncated,
+                            const float* terminal_obs, float* terminal_stack, void* stream) {
+    if (!ring || !obs || n <= 0 || obs_dim <= 0 || n_stack <= 0 || pos < 0 || pos >= n_stack)
+        return fail(nullptr, USV_ERR_INVALID, "bad frame_stack_push arguments");
+    int rc = check_device(nullptr, device);
+    if (rc) return rc;
+    CU_TRY(nullptr, cudaSetDevice(device));
+    frame_push_kernel<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(n, obs_dim, n_stack, pos, ring, obs, terminated,
+                                                                              truncated, terminal_obs, terminal_stack);
+    CU_TRY(nullptr, cudaGetLastError());
+    return USV_OK;
+}
+
 int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, double* out, void* stream) {
     if (!in || !out || n <= 0 || which < 0 || which > 3) return fail(nullptr, USV_ERR_INVALID, "bad math_probe arguments");
     int rc = check_device(nullptr, device);

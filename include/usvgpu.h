@@ -211,6 +211,19 @@ int usvgpu_asmc_compute(int device, int64_t n, double* state, const double* acti
 int usvgpu_sensors(int device, int64_t n, const double* pose, const double* obstacles, const int32_t* n_obs,
                    double* out, void* stream);
 
+/* Replaces stable_baselines3 VecFrameStack / StackedObservations.update (train_test/sb3_train_vec.py:70,
+ * train_test/sb3_train.py:50-51: n_stack = 5) for device-resident observations, without moving old frames.
+ * ring: float32 [N][2 * n_stack][obs_dim], zero-initialised by the caller.  Call k (k = 0 for the reset observation)
+ * passes pos = k % n_stack; afterwards the stacked observation of env i (oldest frame first, SB3's layout for 1-D
+ * observations) is the contiguous run ring[i][pos + 1 .. pos + n_stack] -- a [N][n_stack * obs_dim] view with row
+ * stride 2 * n_stack * obs_dim.  Envs with terminated | truncated set (either pointer may be NULL; pass both NULL for
+ * the reset observation) get their older frames zeroed, and, when terminal_obs and terminal_stack are given,
+ * terminal_stack[i] = the previous n_stack - 1 frames followed by terminal_obs[i] (SB3's stacked
+ * infos[i]["terminal_observation"]); terminal_stack float32 [N][n_stack * obs_dim], rows of other envs untouched. */
+int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_stack, int32_t pos, float* ring,
+                            const float* obs, const uint8_t* terminated, const uint8_t* truncated,
+                            const float* terminal_obs, float* terminal_stack, void* stream);
+
 /* Device-math probe (test / measurement surface, no reference counterpart): evaluates one of the float64
  * routines of csrc/usv_math.cuh that replace libm calls of the reference (np.sqrt, '/', np.math.asin at
  * usv_asmc.py:72,103,150; np.cos / np.sin at :179-181) on n inputs.  which: 0 sqrt_k(in[i]) | 1 div_k(in[i],

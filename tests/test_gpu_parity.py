@@ -630,3 +630,45 @@ def test_legacy_host_face_and_ragged(usv):
                 assert dones.all() and all(infos[i]["TimeLimit.truncated"] for i in range(n))
                 assert infos[0]["terminal_observation"].shape == (6,) and infos[0]["episode"]["l"] == 9
         env.close()
+
+
+# ------------------------------------------------------------------------------------------
+# on-device VecFrameStack (train_test/sb3_train_vec.py:70), SURVEY 8f rank 1
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("env_id,n_stack", [("usv-asmc-simple", 5), ("usv-simple", 5), ("usv-asmc-v0", 3)])
+def test_frame_stack_matches_sb3_restatement(usv, env_id, n_stack):
+    from sb3_frame_stack import StackedObservations
+    N, T = 700, 60
+    limit = 13
+    plain = usv.UsvGpuVecEnv(N, device=0, seed=8, env_id=env_id, max_episode_steps=limit)
+    fs = usv.UsvGpuVecFrameStack(usv.UsvGpuVecEnv(N, device=0, seed=8, env_id=env_id, max_episode_steps=limit), n_stack)
+    d = plain.obs_dim
+    assert fs.observation_space.shape == (n_stack * d,)
+    ref = StackedObservations(N, n_stack, d)
+    want = ref.reset(plain.reset_tensor().cpu().numpy())
+    got = fs.reset_tensor()
+    assert got.shape == (N, n_stack * d) and got.stride() == (2 * n_stack * d, 1)
+    assert np.array_equal(got.cpu().numpy(), want)
+    rng = np.random.default_rng(0)
+    n_done = 0
+    for t in range(T):
+        a = torch.tensor(rng.uniform(plain.action_space.low, plain.action_space.high, (N, plain.act_dim)).astype(np.float32),
+                         device=plain.device)
+        obs, rew, term, trunc = [x.cpu().numpy() for x in plain.step_tensor(a)]
+        dones = (term | trunc).astype(bool)
+        tob = plain.terminal_obs.cpu().numpy()
+        infos = [({"terminal_observation": tob[i]} if dones[i] else {}) for i in range(N)]
+        want, infos = ref.update(obs, dones, infos)
+        got, rew2, term2, trunc2 = fs.step_tensor(a)
+        assert np.array_equal(got.cpu().numpy(), want), t
+        assert np.array_equal(rew2.cpu().numpy(), rew) and np.array_equal(term2.cpu().numpy(), term)
+        ts = fs.terminal_stack.cpu().numpy()
+        for i in np.flatnonzero(dones):
+            n_done += 1
+            assert np.array_equal(ts[i], infos[i]["terminal_observation"])
+    assert n_done >= 3 * N
+    # a policy can consume the strided view directly
+    w = torch.randn(n_stack * d, 8, device=plain.device)
+    assert torch.allclose(got @ w, got.contiguous() @ w)
+    plain.close()
+    fs.close()
