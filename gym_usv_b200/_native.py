@@ -123,6 +123,7 @@ _SIGNATURES = {
                                       C.c_int32, C.c_void_p, C.c_void_p]),
     "usvgpu_sensors": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_frame_stack_push": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 7),
+    "usvgpu_gae": (C.c_int, [C.c_int, C.c_int32, C.c_int64] + [C.c_void_p] * 5 + [C.c_float, C.c_float] + [C.c_void_p] * 3),
     "usvgpu_math_probe": (C.c_int, [C.c_int, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_fp64_peak": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.c_void_p]),
 }

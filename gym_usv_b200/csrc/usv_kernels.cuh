@@ -437,6 +437,35 @@ frame_push_kernel(long long n, int obs_dim, int n_stack, int pos, float* __restr
 }
 
 // ---------------------------------------------------------------------------------------------
+// stable_baselines3 RolloutBuffer.compute_returns_and_advantage (GAE(lambda)) for a device-resident rollout of
+// n_steps x N: one thread per env walks its column backwards; rows are coalesced.  float32, the operation order of
+// SB3's numpy code, no FMA contraction, so the result is bit-identical to the numpy restatement.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gae_kernel(int n_steps, long long n, const float* __restrict__ rewards, const float* __restrict__ values,
+           const float* __restrict__ episode_starts, const float* __restrict__ last_values,
+           const uint8_t* __restrict__ last_dones, float gamma, float gae_lambda, float* __restrict__ advantages,
+           float* __restrict__ returns) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float last_gae_lam = 0.0f;
+    float next_non_terminal = 1.0f - (last_dones[i] ? 1.0f : 0.0f);
+    float next_values = last_values[i];
+    for (int t = n_steps - 1; t >= 0; --t) {
+        const long long k = (long long)t * n + i;
+        const float v = values[k];
+        // delta = rewards + gamma * next_values * next_non_terminal - values
+        const float delta = __fsub_rn(__fadd_rn(rewards[k], __fmul_rn(__fmul_rn(gamma, next_values), next_non_terminal)), v);
+        // last_gae_lam = delta + gamma * gae_lambda * next_non_terminal * last_gae_lam
+        last_gae_lam = __fadd_rn(delta, __fmul_rn(__fmul_rn(__fmul_rn(gamma, gae_lambda), next_non_terminal), last_gae_lam));
+        advantages[k] = last_gae_lam;
+        returns[k] = __fadd_rn(last_gae_lam, v);
+        next_non_terminal = 1.0f - episode_starts[k];
+        next_values = v;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Unit-parity kernels
 // ---------------------------------------------------------------------------------------------
 template <bool PERTURB>

@@ -645,6 +645,22 @@ int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_st
     return USV_OK;
 }
 
+int usvgpu_gae(int device, int32_t n_steps, int64_t n, const float* rewards, const float* values,
+               const float* episode_starts, const float* last_values, const uint8_t* last_dones, float gamma,
+               float gae_lambda, float* advantages, float* returns, void* stream) {
+    if (!rewards || !values || !episode_starts || !last_values || !last_dones || !advantages || !returns || n <= 0 ||
+        n_steps <= 0)
+        return fail(nullptr, USV_ERR_INVALID, "bad gae arguments");
+    int rc = check_device(nullptr, device);
+    if (rc) return rc;
+    CU_TRY(nullptr, cudaSetDevice(device));
+    gae_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n_steps, n, rewards, values, episode_starts,
+                                                                           last_values, last_dones, gamma, gae_lambda,
+                                                                           advantages, returns);
+    CU_TRY(nullptr, cudaGetLastError());
+    return USV_OK;
+}
+
 int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, double* out, void* stream) {
     if (!in || !out || n <= 0 || which < 0 || which > 3) return fail(nullptr, USV_ERR_INVALID, "bad math_probe arguments");
     int rc = check_device(nullptr, device);

@@ -224,6 +224,13 @@ int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_st
                             const float* obs, const uint8_t* terminated, const uint8_t* truncated,
                             const float* terminal_obs, float* terminal_stack, void* stream);
 
+/* Replaces stable_baselines3 RolloutBuffer.compute_returns_and_advantage (what PPO.learn of
+ * train_test/config.py:3-15 runs after every n_steps = 2048 rollout) on device-resident buffers: rewards, values,
+ * episode_starts, advantages, returns float32 [n_steps][N]; last_values float32 [N]; last_dones uint8 [N]. */
+int usvgpu_gae(int device, int32_t n_steps, int64_t n, const float* rewards, const float* values,
+               const float* episode_starts, const float* last_values, const uint8_t* last_dones, float gamma,
+               float gae_lambda, float* advantages, float* returns, void* stream);
+
 /* Device-math probe (test / measurement surface, no reference counterpart): evaluates one of the float64
  * routines of csrc/usv_math.cuh that replace libm calls of the reference (np.sqrt, '/', np.math.asin at
  * usv_asmc.py:72,103,150; np.cos / np.sin at :179-181) on n inputs.  which: 0 sqrt_k(in[i]) | 1 div_k(in[i],
