@@ -67,6 +67,18 @@ def kernel_bytes(obstacles: bool, obstacles_f32: bool) -> dict:
 LEGACY_BYTES = (19 * 4 + 4 * 8 + 4 + 4 + 8) + (19 * 4 + 6 * 4 + 4 + 2 + 4 + 8)
 
 
+def ncu_traffic(kernel: str, n_envs: int):
+    """dram bytes per launch of `kernel` from the committed ncu --set full capture (profiles/ncu_traffic.json), or None
+    when the capture was taken at another batch size."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            d = json.load(f)
+        want = 1048576 if "legacy" in kernel else 65536
+        return d.get(kernel) if n_envs == want else None
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -400,7 +412,7 @@ def run_ours(args, rank, local_rank, world):
                            "(usvgpu_step_host: page-locked host buffers, H2D + kernels + D2H + sync per step)"},
             "gpu_launches": (1 if legacy else 2) * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": knames[dom],
+                         "traffic": ncu_traffic(knames[dom], n), "peak_source": peak_src, "kernel": knames[dom],
                          "algorithmic_bytes_per_env_step": kb[knames[dom]], "launch_us": dom_s * 1e6,
                          "kernels_us": {knames[0]: kms[0] * 1e3, knames[1]: kms[1] * 1e3},
                          "kernels_bytes_per_env_step": kb,
