@@ -102,7 +102,7 @@ __device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags
     // the reference divides (x / 10, angle / pi, ...): multiplying by the rounded reciprocal differs by at
     // most one float64 ulp before the float32 rounding.  Columns 7, 8 (last_action), 10 (max_action[1]) and
     // 13 (max_acceleration[1]) are 0 for the whole life of this env.
-    float4* hrow = reinterpret_cast<float4*>(s.hdr16 + i * HDR_PAD);
+    float4* hrow = reinterpret_cast<float4*>(hdr_of(s, i));
     hrow[0] = make_float4((float)(p.u * 0.1), (float)(p.v * 0.1), (float)(p.r * 0.1), (float)(ang * (1.0 / PI)));
     // columns 7, 8: the PREVIOUS last_action[[0, 2]] / max_action[[0, 2]] (:338 runs before :343)
     hrow[1] = make_float4((float)(tdist * (1.0 / DIST_NORM)), (float)(ye * 0.1), (float)(vref * 0.1),
@@ -125,7 +125,7 @@ __device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags
     if (KIN) hd.rew_part += -((fabs(la0 - c0) + fabs(la2 - c2)) / 2) * 0.15;  // delta_action_reward, :176
     hd.flags = (oob ? FLG_OOB : 0u) | (tlimit ? FLG_TLIMIT : 0u);
     hd.pad = 0u;
-    s.hand[i] = hd;
+    *hand_of(s, i) = hd;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -253,23 +253,24 @@ struct alignas(16) SensorStage {
     int pad[3];
 };
 
+static_assert(sizeof(SensorStage<float>) == sizeof(float) * OBST_ROW + SIN_TAIL_BYTES, "stage == sensor-input row");
+static_assert(sizeof(SensorStage<double>) == sizeof(double) * OBST_ROW + SIN_TAIL_BYTES, "stage == sensor-input row");
+
+// The stage has the layout of the env's sensor-input row (usv_state.cuh): the prefetch is a straight 16-byte-chunk
+// copy, one cp.async per lane for a float32 table.  Without obstacles only the 128-byte tail is fetched.
 template <bool OBST, typename ObT>
 __device__ __forceinline__ void sensor_prefetch(SensorStage<ObT>& st, const StatePtrs& s, long long i, int lane) {
-    constexpr int ROW_CHUNKS = (int)(sizeof(ObT) * OBST_ROW / 16);  // 24 (float32 table) or 48 (float64)
+    constexpr int TABLE_CHUNKS = (int)(sizeof(ObT) * OBST_ROW / 16);  // 24 (float32 table) or 48 (float64)
+    constexpr int ROW_CHUNKS = TABLE_CHUNKS + SIN_TAIL_BYTES / 16;    // 32 or 56
+    const char* row = reinterpret_cast<const char*>(obst_row<ObT>(s, i));
+    char* dst = reinterpret_cast<char*>(&st);
     if (OBST) {
-        const char* row = reinterpret_cast<const char*>(obst_row<ObT>(s, i));
-        char* dst = reinterpret_cast<char*>(st.obst);
 #pragma unroll
         for (int c = lane; c < ROW_CHUNKS; c += 32) __pipeline_memcpy_async(dst + 16 * c, row + 16 * c, 16);
-        if (lane == 31) __pipeline_memcpy_async(&st.nob, s.n_obs + i, 4);
+    } else {
+        if (lane < SIN_TAIL_BYTES / 16)
+            __pipeline_memcpy_async(dst + 16 * (TABLE_CHUNKS + lane), row + 16 * (TABLE_CHUNKS + lane), 16);
     }
-    // lanes 24..26: the 48-byte hand-over record; lanes 27..30: the 64-byte header row
-    if (lane >= 24 && lane < 27)
-        __pipeline_memcpy_async(reinterpret_cast<char*>(&st.hd) + 16 * (lane - 24),
-                                reinterpret_cast<const char*>(s.hand + i) + 16 * (lane - 24), 16);
-    if (lane >= 27 && lane < 31)
-        __pipeline_memcpy_async(reinterpret_cast<char*>(st.head) + 16 * (lane - 27),
-                                reinterpret_cast<const char*>(s.hdr16 + i * HDR_PAD) + 16 * (lane - 27), 16);
     __pipeline_commit();
 }
 

@@ -67,14 +67,17 @@ static_assert(sizeof(DeviceStats) == sizeof(UsvStats), "UsvStats layout");
 struct StatePtrs {
     double* dyn;        // [N_DYN][n]
     double* epi;        // [N_EPI][n]
-    void* obst;         // [n][3][32]  double or float (x[32], y[32], radius[32] per env)
-    int* n_obs;         // [n]
+    // Sensor-input rows [n][sin_row bytes], 128-byte aligned: everything sensor_kernel needs for one env in one
+    // contiguous block -- obstacle table x[32] y[32] radius[32] (float or double) | Hand 48 B | observation header row
+    // 64 B | n_obs int32 | 12 B pad.  512 B per env with a float32 table (one 16-byte cp.async per lane), 896 B with
+    // float64.  The dynamics kernel writes Hand + header (one 128-byte line), the reset writes table + n_obs.
+    char* sin;
+    int sin_row;        // bytes per env row
+    int sin_tail;       // byte offset of the Hand record inside a row (= table bytes)
     int* steps;         // [n]
     int* episode;       // [n]
     double* ep_return;  // [n]
     double2* ep_done;   // [n]  (return, length) of the env's last finished episode (SB3 infos[i]["episode"])
-    Hand* hand;         // [n]      dynamics -> sensor hand-over
-    float* hdr16;       // [n][16]  observation header rows
     DeviceStats* stats;
     const double2* raytab;  // [128] cos/sin of the ray angles relative to the bow
     long long n;
@@ -89,9 +92,18 @@ struct StepFlags {
                        // copy-out of one chunk overlaps the kernels of the next
 };
 
+constexpr int SIN_TAIL_BYTES = 128;  // Hand (48) + header row (64) + n_obs (4) + pad (12)
 template <typename ObT>
 __device__ __forceinline__ ObT* obst_row(const StatePtrs& s, long long i) {
-    return static_cast<ObT*>(s.obst) + i * OBST_ROW;
+    return reinterpret_cast<ObT*>(s.sin + i * (long long)(sizeof(ObT) * OBST_ROW + SIN_TAIL_BYTES));
+}
+__device__ __forceinline__ char* sin_tail(const StatePtrs& s, long long i) { return s.sin + i * s.sin_row + s.sin_tail; }
+__device__ __forceinline__ Hand* hand_of(const StatePtrs& s, long long i) { return reinterpret_cast<Hand*>(sin_tail(s, i)); }
+__device__ __forceinline__ float* hdr_of(const StatePtrs& s, long long i) {
+    return reinterpret_cast<float*>(sin_tail(s, i) + sizeof(Hand));
+}
+__device__ __forceinline__ int* nobs_of(const StatePtrs& s, long long i) {
+    return reinterpret_cast<int*>(sin_tail(s, i) + sizeof(Hand) + HDR_PAD * sizeof(float));
 }
 
 }  // namespace usv

@@ -150,8 +150,9 @@ static int field_ptr(UsvGpu* h, int32_t field, void** p, int64_t* bytes) {
         case USV_FIELD_LEGACY_POS0: if (!h->legacy) return -1; *p = h->lp.pos0; *bytes = n * 3 * 8; return 0;
         case USV_FIELD_DYN: if (h->legacy) return -1; *p = h->sp.dyn; *bytes = n * N_DYN * 8; return 0;
         case USV_FIELD_EPI: if (h->legacy) return -1; *p = h->sp.epi; *bytes = n * N_EPI * 8; return 0;
-        case USV_FIELD_OBSTACLES: if (h->legacy) return -1; *p = h->sp.obst; *bytes = n * MAX_OBST * 3 * (int64_t)h->obst_elem; return 0;
-        case USV_FIELD_N_OBS: if (h->legacy) return -1; *p = h->sp.n_obs; *bytes = n * 4; return 0;
+        // these two live inside the interleaved sensor-input rows: *p is the first element, copies are pitched
+        case USV_FIELD_OBSTACLES: if (h->legacy) return -1; *p = h->sp.sin; *bytes = n * MAX_OBST * 3 * (int64_t)h->obst_elem; return 0;
+        case USV_FIELD_N_OBS: if (h->legacy) return -1; *p = h->sp.sin + h->sp.sin_tail + sizeof(Hand) + HDR_PAD * sizeof(float); *bytes = n * 4; return 0;
         case USV_FIELD_STEPS: *p = h->sp.steps; *bytes = n * 4; return 0;
         case USV_FIELD_EPISODE: *p = h->sp.episode; *bytes = n * 4; return 0;
         case USV_FIELD_EP_RETURN: *p = h->sp.ep_return; *bytes = n * 8; return 0;
@@ -218,10 +219,9 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     } else {
         alloc((void**)&h->sp.dyn, n * N_DYN * sizeof(double));
         alloc((void**)&h->sp.epi, n * N_EPI * sizeof(double));
-        alloc((void**)&h->sp.obst, n * MAX_OBST * 3 * h->obst_elem);
-        alloc((void**)&h->sp.n_obs, n * sizeof(int));
-        alloc((void**)&h->sp.hand, n * sizeof(Hand));
-        alloc((void**)&h->sp.hdr16, n * HDR_PAD * sizeof(float));
+        h->sp.sin_tail = (int)(MAX_OBST * 3 * h->obst_elem);
+        h->sp.sin_row = h->sp.sin_tail + SIN_TAIL_BYTES;
+        alloc((void**)&h->sp.sin, n * (size_t)h->sp.sin_row);
     }
     alloc((void**)&h->sp.steps, n * sizeof(int));
     alloc((void**)&h->sp.episode, n * sizeof(int));
@@ -265,14 +265,11 @@ int usvgpu_destroy(usvgpu_handle h) {
     cudaFree(h->lp.target);
     cudaFree(h->sp.dyn);
     cudaFree(h->sp.epi);
-    cudaFree(h->sp.obst);
-    cudaFree(h->sp.n_obs);
+    cudaFree(h->sp.sin);
     cudaFree(h->sp.steps);
     cudaFree(h->sp.episode);
     cudaFree(h->sp.ep_return);
     cudaFree(h->sp.ep_done);
-    cudaFree(h->sp.hand);
-    cudaFree(h->sp.hdr16);
     cudaFree(h->sp.stats);
     cudaFree((void*)h->sp.raytab);
     if (h->own_staging) {
@@ -561,7 +558,12 @@ int usvgpu_get_state(usvgpu_handle h, int32_t field, void* buf, int64_t bytes, v
     if (field_ptr(h, field, &p, &b)) return fail(h, USV_ERR_INVALID, "unknown field");
     if (bytes != b) return fail(h, USV_ERR_INVALID, "buffer size does not match usvgpu_field_bytes()");
     CU_TRY(h, cudaSetDevice(h->device));
-    CU_TRY(h, cudaMemcpyAsync(buf, p, (size_t)b, cudaMemcpyDefault, (cudaStream_t)stream));
+    if (field == USV_FIELD_OBSTACLES || field == USV_FIELD_N_OBS) {  // rows of the interleaved sensor-input block
+        const size_t w = (size_t)(b / h->sp.n);
+        CU_TRY(h, cudaMemcpy2DAsync(buf, w, p, (size_t)h->sp.sin_row, w, (size_t)h->sp.n, cudaMemcpyDefault, (cudaStream_t)stream));
+    } else {
+        CU_TRY(h, cudaMemcpyAsync(buf, p, (size_t)b, cudaMemcpyDefault, (cudaStream_t)stream));
+    }
     CU_TRY(h, cudaStreamSynchronize((cudaStream_t)stream));
     return USV_OK;
 }
@@ -573,7 +575,12 @@ int usvgpu_set_state(usvgpu_handle h, int32_t field, const void* buf, int64_t by
     if (field_ptr(h, field, &p, &b)) return fail(h, USV_ERR_INVALID, "unknown field");
     if (bytes != b) return fail(h, USV_ERR_INVALID, "buffer size does not match usvgpu_field_bytes()");
     CU_TRY(h, cudaSetDevice(h->device));
-    CU_TRY(h, cudaMemcpyAsync(p, buf, (size_t)b, cudaMemcpyDefault, (cudaStream_t)stream));
+    if (field == USV_FIELD_OBSTACLES || field == USV_FIELD_N_OBS) {
+        const size_t w = (size_t)(b / h->sp.n);
+        CU_TRY(h, cudaMemcpy2DAsync(p, (size_t)h->sp.sin_row, buf, w, w, (size_t)h->sp.n, cudaMemcpyDefault, (cudaStream_t)stream));
+    } else {
+        CU_TRY(h, cudaMemcpyAsync(p, buf, (size_t)b, cudaMemcpyDefault, (cudaStream_t)stream));
+    }
     CU_TRY(h, cudaStreamSynchronize((cudaStream_t)stream));
     return USV_OK;
 }
