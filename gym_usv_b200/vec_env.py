@@ -349,5 +349,14 @@ class UsvGpuVecEnv:
         return st.as_dict()
 
     def stats_tensor(self) -> torch.Tensor:
-        """The device-side UsvStats block viewed as 8 x 8 bytes (for an optional NCCL all-reduce)."""
-        raise NotImplementedError
+        """The device-side UsvStats block as 8 raw 64-bit words (int64 view, no copy): words 0-1 are the float64
+        return / length sums (``.view(torch.float64)[:2]``), words 2-7 the counters episodes, terminated,
+        out_of_bounds, time_limit, env_steps (kept on the host: 0 here), nonfinite.  For a caller that wants to
+        all-reduce the statistics with NCCL without a host round trip."""
+        ptr = C.c_void_p()
+        self._check(self._lib.usvgpu_stats_device_ptr(self._h, C.byref(ptr)))
+
+        class _Block:
+            __cuda_array_interface__ = {"shape": (8,), "typestr": "<i8", "data": (int(ptr.value), False), "version": 2}
+
+        return torch.as_tensor(_Block(), device=self.device)

@@ -460,6 +460,9 @@ def test_vecenv_host_face_sb3_semantics(usv):
     assert seen_done >= 2 * N - 5
     assert env.env_is_wrapped(object) == [False] * N
     assert len(env.get_attr("position")) == N
+    st, words = env.episode_stats(), env.stats_tensor()
+    assert int(words[2]) == st["episodes"] == seen_done and int(words[5]) == st["time_limit"]
+    assert abs(float(words.view(torch.float64)[1]) - st["length_sum"]) < 0.5
     env.close()
 
 
