@@ -172,13 +172,14 @@ def gen_reset_samples(R, n=1500):
 
 
 # -----------------------------------------------------------------------------------------
-def _legacy_rollout(R, np_seed, act_seed, steps, full, hold=1):
-    """UsvAsmcEnv (usv-asmc-v0): np.random.seed(np_seed), scalar f32 actions U(+-pi/2) each held for `hold` steps,
-    auto-reset on done."""
+def _legacy_rollout(R, np_seed, act_seed, steps, full, hold=1, cls="UsvAsmcEnv"):
+    """UsvAsmcEnv (usv-asmc-v0) or one of its float64 siblings: np.random.seed(np_seed), scalar f32 actions U(+-pi/2)
+    each held for `hold` steps, auto-reset on done."""
     np.random.seed(np_seed)
     acts = np.random.default_rng(act_seed).uniform(-np.pi / 2, np.pi / 2, (steps + hold - 1) // hold)
     acts = np.repeat(acts, hold)[:steps].astype(np.float32)
-    env = R.UsvAsmcEnv()
+    env = getattr(R, cls)()
+    f64 = cls != "UsvAsmcEnv"  # the siblings return and keep float64 everywhere
     resets = []
 
     def rec():
@@ -188,8 +189,10 @@ def _legacy_rollout(R, np_seed, act_seed, steps, full, hold=1):
 
     o = env.reset()
     resets.append((0, rec(), o))
-    obs, rew, done = np.zeros((steps, 6), np.float32), np.zeros(steps), np.zeros(steps, np.uint8)
-    pos, vel, aux, last = np.zeros((steps, 3)), np.zeros((steps, 3)), np.zeros((steps, 3)), np.zeros((steps, 9))
+    na, nl = len(env.aux_vars), len(env.last)
+    obs = np.zeros((steps, 6), np.float64 if f64 else np.float32)
+    rew, done = np.zeros(steps), np.zeros(steps, np.uint8)
+    pos, vel, aux, last = np.zeros((steps, 3)), np.zeros((steps, 3)), np.zeros((steps, na)), np.zeros((steps, nl))
     for t in range(steps):
         o, r, d, _ = env.step(acts[t])
         obs[t], rew[t], done[t] = o, r, d
@@ -201,6 +204,8 @@ def _legacy_rollout(R, np_seed, act_seed, steps, full, hold=1):
                reset_step=np.array([r[0] for r in resets]), reset_obs=np.array([r[2] for r in resets]))
     if full:
         out.update(aux=aux, last=last)
+    elif f64:
+        pass
     else:  # after a step the arrays hold float32 values (usv_asmc_env.py:247-251): store them as such
         out["pos"], out["vel"] = pos.astype(np.float32), vel.astype(np.float32)
         assert np.array_equal(out["pos"].astype(np.float64), pos) and np.array_equal(out["vel"].astype(np.float64), vel)
@@ -222,10 +227,24 @@ def gen_legacy(R):
     np.savez_compressed(os.path.join(OUT, "legacy_asmc_env.npz"), **out)
 
 
+def gen_legacy_siblings(R):
+    """'usv-asmc-ye-int-v0' and 'usv-pid-v0' (gym_usv/__init__.py:8-16): 1500 steps with a new action every step and
+    every array recorded, plus 6000 steps with actions held for 250 / 500 steps (keys 'L1_*') so that the |ye| > 10 /
+    x < -10 terminations and the resets after them are on file."""
+    for name, cls, s0, l1 in (("ye_int", "UsvAsmcYeIntEnv", 10, (12, 13, 6000, 250)),
+                              ("pid", "UsvPidEnv", 20, (24, 25, 6000, 500))):
+        out, nres, nd = _legacy_rollout(R, s0, s0 + 1, 1500, full=True, cls=cls)
+        print(f"legacy {name}: resets", nres, "done", nd)
+        o, nres, nd = _legacy_rollout(R, l1[0], l1[1], l1[2], full=False, hold=l1[3], cls=cls)
+        print(f"legacy {name} L1: resets", nres, "done", nd)
+        out.update({f"L1_{k}": v for k, v in o.items()})
+        np.savez_compressed(os.path.join(OUT, f"legacy_{name}_env.npz"), **out)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     R = rh.load_reference()
-    which = sys.argv[1:] or ["asmc", "sensors", "simple", "simple_noobs", "resets", "legacy", "kinematic"]
+    which = sys.argv[1:] or ["asmc", "sensors", "simple", "simple_noobs", "resets", "legacy", "legacy_siblings", "kinematic"]
     if "asmc" in which:
         gen_asmc(R)
     if "sensors" in which:
@@ -238,6 +257,8 @@ if __name__ == "__main__":
         gen_reset_samples(R)
     if "legacy" in which:
         gen_legacy(R)
+    if "legacy_siblings" in which:
+        gen_legacy_siblings(R)
     if "kinematic" in which:  # 'usv-simple' = UsvSimpleEnv itself, TimeLimit 500 (gym_usv/__init__.py:24-28)
         gen_simple_env(R, "simple_kinematic_env.npz", seeds=[200, 201, 202], steps=700, ignore_obstacles=False,
                        cls="UsvSimpleEnv", limit=500)

@@ -112,6 +112,8 @@ def load_reference():
     from gym_usv.envs.simple_env_asmc import UsvSimpleASMCEnv
     from gym_usv.envs.usv_asmc_ca_env import UsvAsmcCaEnv
     from gym_usv.envs.usv_asmc_env import UsvAsmcEnv
+    from gym_usv.envs.usv_asmc_ye_int_env import UsvAsmcYeIntEnv
+    from gym_usv.envs.usv_pid_env import UsvPidEnv
 
     return types.SimpleNamespace(
         UsvAsmc=UsvAsmc,
@@ -119,6 +121,8 @@ def load_reference():
         UsvSimpleASMCEnv=UsvSimpleASMCEnv,
         UsvAsmcCaEnv=UsvAsmcCaEnv,
         UsvAsmcEnv=UsvAsmcEnv,
+        UsvAsmcYeIntEnv=UsvAsmcYeIntEnv,
+        UsvPidEnv=UsvPidEnv,
     )
 
 

@@ -117,11 +117,18 @@ typedef struct UsvOracleLegacy {
     double last[9];      /* eta_dot_last[3], upsilon_dot_last[3], e_u_last, Ka_dot_u_last, Ka_dot_psi_last */
     double target[6];    /* x_0, y_0, desired_speed, ak, x_d, y_d                    */
     double ep_return;
-    int32_t f32_state;   /* 0 after reset() (float64 arrays), 1 after a step()       */
+    double ye_int;       /* usv_asmc_ye_int_env.py: aux_vars[3]                      */
+    double ye_last;      /* usv_asmc_ye_int_env.py: last[9]                          */
+    int32_t f32_state;   /* 0 after reset() (float64 arrays), 1 after a step() of variant 0 */
     int32_t steps;
     int32_t episode;
-    int32_t pad_;
+    int32_t variant;     /* USV_ORACLE_LEGACY_* ; set by the caller after _init      */
 } UsvOracleLegacy;
+
+/* the three envs that share UsvAsmcEnv's step(): gym_usv/__init__.py:3-16 */
+#define USV_ORACLE_LEGACY_ASMC_V0 0    /* usv_asmc_env.py        (float32 / float64 mixed flow)      */
+#define USV_ORACLE_LEGACY_YE_INT 1     /* usv_asmc_ye_int_env.py (float64 throughout, ye integral)   */
+#define USV_ORACLE_LEGACY_PID 2        /* usv_pid_env.py         (float64 throughout, PID law)       */
 
 int  usv_oracle_sizeof_legacy(void);
 void usv_oracle_legacy_init(UsvOracleLegacy* e);

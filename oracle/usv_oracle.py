@@ -64,13 +64,17 @@ LEGACY_DTYPE = np.dtype(
         ("last", "<f8", (9,)),
         ("target", "<f8", (6,)),
         ("ep_return", "<f8"),
+        ("ye_int", "<f8"),
+        ("ye_last", "<f8"),
         ("f32_state", "<i4"),
         ("steps", "<i4"),
         ("episode", "<i4"),
-        ("pad_", "<i4"),
+        ("variant", "<i4"),
     ],
     align=True,
 )
+# gym_usv/__init__.py:3-16: the three registered ids that share UsvAsmcEnv's step()
+LEGACY_VARIANTS = {"usv-asmc-v0": 0, "usv-asmc-ye-int-v0": 1, "usv-pid-v0": 2}
 
 
 class Config(C.Structure):
@@ -220,17 +224,19 @@ class OracleVecEnv:
 
 
 # ---------------------------------------------------------------------------------------
-# usv-asmc-v0 legacy vector env (gym_usv/envs/usv_asmc_env.py)
+# legacy path-following vector envs: usv-asmc-v0 (gym_usv/envs/usv_asmc_env.py) and its two float64 siblings
+# usv-asmc-ye-int-v0 (usv_asmc_ye_int_env.py) and usv-pid-v0 (usv_pid_env.py)
 # ---------------------------------------------------------------------------------------
 class OracleLegacyVecEnv:
-    """N UsvAsmcEnv instances in lock-step (usv_asmc_env.py:99-300), SB3 auto-reset semantics."""
+    """N UsvAsmcEnv / UsvAsmcYeIntEnv / UsvPidEnv instances in lock-step, SB3 auto-reset semantics."""
 
-    def __init__(self, n, seed=0, global_offset=0, auto_reset=True, n_threads=1):
+    def __init__(self, n, seed=0, global_offset=0, auto_reset=True, n_threads=1, env_id="usv-asmc-v0"):
         self.n, self.seed, self.global_offset = int(n), int(seed), int(global_offset)
         self.auto_reset, self.n_threads = bool(auto_reset), int(n_threads)
         self.envs = np.zeros(self.n, dtype=LEGACY_DTYPE)
         lib()
         self.envs["episode"] = -1
+        self.envs["variant"] = LEGACY_VARIANTS[env_id]
         self.obs = np.zeros((self.n, 6), dtype=np.float32)
         self.terminal_obs = np.zeros((self.n, 6), dtype=np.float32)
         self.reward = np.zeros(self.n)

@@ -60,6 +60,7 @@
 /* usv_asmc_env.py:66-69, 77-78 */
 #define L_MAX_YE 10.0
 #define L_MAX_X 30.0
+#define L_MIN_X (-10.0) /* usv_asmc_ye_int_env.py:63, usv_pid_env.py:60 */
 #define L_W_ACTION 0.2
 
 /* :132-133  1.1+0.0045*(1.01/0.09) - 0.1*(0.27/0.09)+0.016*(np.power((0.27/0.09), 2)) -- an np.float64 */
@@ -84,6 +85,9 @@ static void l_mass_inverse(double Minv[3][3]) {
 }
 
 /* float64 flow: the first step after reset() */
+#define LEGACY_VARIANT 0
+#define ARR_T float
+#define STORE(x) ((double)(float)(x))
 #define S double
 #define LEGACY_FN(n) n##_f64
 #define S_ABS fabs
@@ -112,12 +116,43 @@ static void l_mass_inverse(double Minv[3][3]) {
 #undef S_SQRT
 #undef S_COS
 #undef S_SIN
+#undef LEGACY_VARIANT
+#undef ARR_T
+#undef STORE
+
+/* the two float64 siblings: no dtype=np.float32 anywhere, so S = ARR_T = double and nothing is rounded on store */
+#define ARR_T double
+#define STORE(x) ((double)(x))
+#define S double
+#define S_ABS fabs
+#define S_SQRT sqrt
+#define S_COS cos
+#define S_SIN sin
+#define LEGACY_VARIANT 1
+#define LEGACY_FN(n) n##_ye_int
+#include "usv_oracle_legacy_step.inc"
+#undef LEGACY_VARIANT
+#undef LEGACY_FN
+#define LEGACY_VARIANT 2
+#define LEGACY_FN(n) n##_pid
+#include "usv_oracle_legacy_step.inc"
+#undef LEGACY_VARIANT
+#undef LEGACY_FN
+#undef S
+#undef S_ABS
+#undef S_SQRT
+#undef S_COS
+#undef S_SIN
+#undef ARR_T
+#undef STORE
 
 int usv_oracle_sizeof_legacy(void) { return (int)sizeof(UsvOracleLegacy); }
 
 /* usv_asmc_env.py:99-255 */
 void usv_oracle_legacy_step(UsvOracleLegacy* e, float action, float obs[6], double* reward, uint8_t* done) {
-    if (e->f32_state) legacy_step_f32(e, action, obs, reward, done);
+    if (e->variant == USV_ORACLE_LEGACY_YE_INT) legacy_step_ye_int(e, action, obs, reward, done);
+    else if (e->variant == USV_ORACLE_LEGACY_PID) legacy_step_pid(e, action, obs, reward, done);
+    else if (e->f32_state) legacy_step_f32(e, action, obs, reward, done);
     else legacy_step_f64(e, action, obs, reward, done);
     e->steps += 1;
     e->ep_return += *reward;
@@ -148,6 +183,8 @@ void usv_oracle_legacy_reset_from_draws(UsvOracleLegacy* e, const double d[7], f
     e->target[3] = ak;
     e->target[4] = x_d;
     e->target[5] = y_d;
+    e->ye_int = 0.0;   /* usv_asmc_ye_int_env.py:268, 273 */
+    e->ye_last = 0.0;
     e->f32_state = 0;  /* float64 arrays until the first step() */
     e->steps = 0;
     e->ep_return = 0.0;
@@ -162,8 +199,12 @@ static inline double l_u53(uint32_t a, uint32_t b) {
 /* reset() with the global np.random (MT19937) replaced by Philox4x32-10 keyed like the other env:
  * draw k = half (k & 1) of block (k >> 1) of (seed, global env id, episode) */
 void usv_oracle_legacy_reset(UsvOracleLegacy* e, uint64_t seed, uint64_t global_id, float obs[6]) {
-    static const double lo[7] = {-2.5, -2.5, -M_PI, -2.5, -2.5, 15, 1.4};
-    static const double hi[7] = {2.5, 2.5, M_PI, 2.5, 2.5, 30, 2.4};
+    /* usv_asmc_env.py:260-281; usv_asmc_ye_int_env.py:258-279 (x, y in +-5, speed 0.4..1.4);
+     * usv_pid_env.py:238-257 (speed 0.4..1.4) */
+    const double xy = (e->variant == USV_ORACLE_LEGACY_YE_INT) ? 5.0 : 2.5;
+    const double s0 = (e->variant == USV_ORACLE_LEGACY_ASMC_V0) ? 1.4 : 0.4;
+    const double lo[7] = {-xy, -xy, -M_PI, -2.5, -2.5, 15, s0};
+    const double hi[7] = {xy, xy, M_PI, 2.5, 2.5, 30, s0 + 1.0};
     double d[7];
     e->episode += 1;
     for (uint32_t b = 0; b < 4; ++b) {

@@ -108,6 +108,7 @@ def test_sensors_match_reference():
 # ------------------------------------------------------------------------------------------
 def _replay(gname, ignore_obstacles, kinematic=False, limit=1000):
     g = load_golden(gname)
+    g = {k: g[k] for k in g.keys()}  # an NpzFile decompresses the member on every access
     acts = g["actions"]
     E, T = g["obs"].shape[:2]
     rmap = golden_reset_maps(g)
@@ -216,6 +217,7 @@ def test_philox_known_answer():
 def legacy_replay(g, prefix, step_fn, inject_fn):
     """Replays a golden UsvAsmcEnv rollout: inject_fn(k) installs the reference's k-th reset state, step_fn(action)
     -> (obs[6], reward, done, position[3], velocity[3]).  Returns the worst absolute differences; done flags exact."""
+    g = {k: g[k] for k in g.keys() if k.startswith(prefix)}  # an NpzFile decompresses the member on every access
     acts, reset_step = g[prefix + "actions"], list(g[prefix + "reset_step"])
     worst = dict(obs=0.0, rew=0.0, pos=0.0, vel=0.0)
     for t in range(len(acts)):
@@ -298,3 +300,85 @@ def test_legacy_reset_from_reference_draws():
     assert np.all((tg[:, 4] >= 15) & (tg[:, 4] <= 30)) and np.all((tg[:, 2] >= 1.4) & (tg[:, 2] <= 2.4))
     assert np.all(tg[:, 3] == 0) and np.all(tg[:, 5] == tg[:, 1])
     assert abs(p[:, 0].mean()) < 0.15 and abs(tg[:, 4].mean() - 22.5) < 0.4 and abs(tg[:, 2].mean() - 1.9) < 0.03
+
+
+# ------------------------------------------------------------------------------------------
+# the float64 siblings 'usv-asmc-ye-int-v0' (usv_asmc_ye_int_env.py) and 'usv-pid-v0' (usv_pid_env.py), SURVEY 8f rank 3
+# ------------------------------------------------------------------------------------------
+SIBLINGS = [("usv-asmc-ye-int-v0", "legacy_ye_int_env.npz"), ("usv-pid-v0", "legacy_pid_env.npz")]
+
+
+def legacy_sibling_inject(e, g, prefix, k):
+    """Installs the reference's k-th reset state (aux_vars[3] / last[9] are the ye integral of the ye-int env)."""
+    for name in ("state", "velocity", "position", "target"):
+        e[name] = g[prefix + "reset_" + name][k]
+    aux, last = g[prefix + "reset_aux"][k], g[prefix + "reset_last"][k]
+    e["aux"], e["last"] = aux[:3], last[:9]
+    e["ye_int"] = aux[3] if len(aux) > 3 else 0.0
+    e["ye_last"] = last[9] if len(last) > 9 else 0.0
+    e["f32_state"] = 0
+
+
+def legacy_sibling_oracle_replay(env_id, g, prefix):
+    ov = uo.OracleLegacyVecEnv(1, auto_reset=False, env_id=env_id)
+
+    def step(a):
+        _, rew, done = ov.step(np.array([a], dtype=np.float32))
+        e = ov.envs[0]
+        return e["state"].copy(), rew[0], done[0], e["position"].copy(), e["velocity"].copy()  # float64 observation
+
+    return legacy_replay(g, prefix, step, lambda k: legacy_sibling_inject(ov.envs[0], g, prefix, k))
+
+
+# Both envs compute in float64 throughout, so the only differences left are numpy's exp / cos / sin against glibc's
+# (an ulp on some inputs) fed back through the closed loop.  Measured here: 5.3e-15 worst over 6000 steps.
+SIBLING_ATOL = 1e-12
+
+
+@pytest.mark.parametrize("env_id,gname", SIBLINGS)
+@pytest.mark.parametrize("prefix", ["", "L1_"])
+def test_legacy_sibling_oracle_vs_reference_rollout(env_id, gname, prefix):
+    g = load_golden(gname)
+    w = legacy_sibling_oracle_replay(env_id, g, prefix)
+    assert max(w.values()) < SIBLING_ATOL, w
+    if prefix == "L1_":
+        assert int(g["L1_done"].sum()) >= 1  # |ye| > 10 terminations and the resets after them are replayed
+
+
+@pytest.mark.parametrize("env_id,gname", SIBLINGS)
+def test_legacy_sibling_internal_arrays(env_id, gname):
+    """aux_vars and last (incl. the ye integral and ye_last of the ye-int env) follow the reference over 1500 steps."""
+    g = load_golden(gname)
+    g = {k: g[k] for k in ("actions", "aux", "last") + tuple("reset_" + n for n in
+                                                               ("state", "velocity", "position", "target", "aux", "last"))}
+    ov = uo.OracleLegacyVecEnv(1, auto_reset=False, env_id=env_id)
+    legacy_sibling_inject(ov.envs[0], g, "", 0)
+    worst = 0.0
+    for t in range(len(g["actions"])):
+        ov.step(g["actions"][t:t + 1])
+        e = ov.envs[0]
+        aux = np.concatenate([e["aux"], [e["ye_int"]]])[:g["aux"].shape[1]]
+        last = np.concatenate([e["last"], [e["ye_last"]]])[:g["last"].shape[1]]
+        worst = max(worst, float(np.abs(aux - g["aux"][t]).max()), float(np.abs(last - g["last"][t]).max()))
+    assert worst < SIBLING_ATOL, worst
+
+
+@pytest.mark.parametrize("env_id,gname,xy,seed", [("usv-asmc-ye-int-v0", "legacy_ye_int_env.npz", 5.0, 10),
+                                                  ("usv-pid-v0", "legacy_pid_env.npz", 2.5, 20)])
+def test_legacy_sibling_reset_from_reference_draws(env_id, gname, xy, seed):
+    """reset() from the reference's seven np.random draws (usv_asmc_ye_int_env.py:256-296, usv_pid_env.py:236-274)."""
+    g = load_golden(gname)
+    np.random.seed(seed)
+    draws = [np.random.uniform(-xy, xy), np.random.uniform(-xy, xy), np.random.uniform(-np.pi, np.pi),
+             np.random.uniform(-2.5, 2.5), np.random.uniform(-2.5, 2.5), np.random.uniform(15, 30),
+             np.random.uniform(0.4, 1.4)]
+    ov = uo.OracleLegacyVecEnv(1, env_id=env_id)
+    ov.reset_from_draws(np.array([draws]))
+    e = ov.envs[0]
+    for name in ("state", "velocity", "position", "target"):
+        assert np.array_equal(e[name], g["reset_" + name][0]), name
+    ov = uo.OracleLegacyVecEnv(4000, seed=5, env_id=env_id)
+    ov.reset()
+    p, tg = ov.envs["position"], ov.envs["target"]
+    assert np.all(np.abs(p[:, :2]) <= xy) and np.abs(p[:, :2]).max() > 0.95 * xy
+    assert np.all((tg[:, 2] >= 0.4) & (tg[:, 2] <= 1.4)) and abs(tg[:, 2].mean() - 0.9) < 0.03
