@@ -65,6 +65,20 @@ def kernel_bytes(obstacles: bool, obstacles_f32: bool) -> dict:
 #   read : 19 f32 state + 4 f64 target + f32 action + i32 steps + f64 episode return            = 124 B
 #   write: 19 f32 state + 6 f32 observation + f32 reward + 2 flag bytes + i32 steps + f64 return = 118 B
 LEGACY_BYTES = (19 * 4 + 4 * 8 + 4 + 4 + 8) + (19 * 4 + 6 * 4 + 4 + 2 + 4 + 8)
+# the float64 siblings keep float64 state columns: 21 (ye-int) / 19 (pid) rows read and written
+LEGACY_IDS = ("usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0")
+
+
+def legacy_bytes(env_id: str) -> int:
+    if env_id == "usv-asmc-v0":
+        return LEGACY_BYTES
+    rows = 21 if env_id == "usv-asmc-ye-int-v0" else 19
+    return (rows * 8 + 4 * 8 + 4 + 4 + 8) + (rows * 8 + 6 * 4 + 4 + 2 + 4 + 8)
+
+
+def legacy_kernel(env_id: str) -> str:
+    return {"usv-asmc-v0": "usv::legacy_step_kernel", "usv-asmc-ye-int-v0": "usv::legacy64_step_kernel<1>",
+            "usv-pid-v0": "usv::legacy64_step_kernel<2>"}[env_id]
 
 
 def ncu_traffic(kernel: str, n_envs: int):
@@ -168,13 +182,13 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------------------------
 def cpu_oracle_rate(n_envs: int, budget_s: float, threads: int, ignore_obstacles: bool, seed: int = 0,
-                    legacy: bool = False):
+                    legacy: bool = False, env_id: str = "usv-asmc-v0"):
     """env-steps/s of the CPU oracle (all `threads` host threads) on n_envs lock-step envs, for ~budget_s."""
     import numpy as np
     import usv_oracle as uo
     rng = np.random.default_rng(0)
     if legacy:
-        ov = uo.OracleLegacyVecEnv(n_envs, seed=seed, n_threads=threads)
+        ov = uo.OracleLegacyVecEnv(n_envs, seed=seed, n_threads=threads, env_id=env_id)
         acts = rng.uniform(-np.pi / 2, np.pi / 2, (8, n_envs)).astype(np.float32)
     else:
         ov = uo.OracleVecEnv(n_envs, seed=seed, ignore_obstacles=ignore_obstacles, n_threads=threads)
@@ -211,8 +225,8 @@ def run_reference(args, rank, world):
     threads = host_threads()
     n = args.ref_envs
     rng = np.random.default_rng(0)
-    if args.env == "usv-asmc-v0":
-        ov = uo.OracleLegacyVecEnv(n, seed=args.seed, n_threads=threads)
+    if args.env in LEGACY_IDS:
+        ov = uo.OracleLegacyVecEnv(n, seed=args.seed, n_threads=threads, env_id=args.env)
         acts = rng.uniform(-np.pi / 2, np.pi / 2, (8, n)).astype(np.float32)
     else:
         ov = uo.OracleVecEnv(n, seed=args.seed, ignore_obstacles=bool(args.no_obstacles), n_threads=threads)
@@ -241,12 +255,16 @@ def run_reference(args, rank, world):
 def dtype_of(args):
     if args.env == "usv-asmc-v0":
         return "f32 state / f64 control terms (the reference's own mix)"
+    if args.env in LEGACY_IDS:
+        return "f64"
     return "f64" if args.precision == "f64" else "f64 state / f32 force terms"
 
 
 def workload_config(args, world, reference_sample=None):
-    if args.env == "usv-asmc-v0":
-        cfg = {"workload": f"usv-asmc-v0 (legacy UsvAsmcEnv: ASMC path following without obstacles, one 0.01 s sub-step "
+    if args.env in LEGACY_IDS:
+        what = {"usv-asmc-v0": "legacy UsvAsmcEnv: ASMC path following", "usv-pid-v0": "UsvPidEnv: PID path following",
+                "usv-asmc-ye-int-v0": "UsvAsmcYeIntEnv: ASMC path following with the cross-track integral"}[args.env]
+        cfg = {"workload": f"{args.env} ({what} without obstacles, one 0.01 s sub-step "
                            f"per env-step), {args.envs_per_gpu} envs per GPU, BASELINE.json configs[1] secondary reading",
                "envs_per_gpu": args.envs_per_gpu, "envs_total": args.envs_per_gpu * world, "sub_steps_per_env_step": 1,
                "max_episode_steps": 0, "auto_reset": True,
@@ -299,7 +317,7 @@ def run_ours(args, rank, local_rank, world):
         envs.append(e)
     A = 8
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    legacy = args.env == "usv-asmc-v0"
+    legacy = args.env in LEGACY_IDS
     if legacy:
         acts = ((torch.rand((A, n, 1), generator=gen, device=dev) - 0.5) * float(np.pi)).contiguous()
     else:
@@ -394,8 +412,8 @@ def run_ours(args, rank, local_rank, world):
         step_s = (ms * 1e-3) / args.steps  # rank-0 device time per step (two kernels)
         kb = kernel_bytes(not args.no_obstacles, bool(args.obstacles_f32))
         if legacy:
-            abytes = LEGACY_BYTES
-            kb = {"usv::legacy_step_kernel": LEGACY_BYTES, "-": 0}
+            abytes = legacy_bytes(args.env)
+            kb = {legacy_kernel(args.env): abytes, "-": 0}
         knames = list(kb)
         dom = 0 if kms[0] >= kms[1] else 1
         dom_s = kms[dom] * 1e-3
@@ -418,7 +436,8 @@ def run_ours(args, rank, local_rank, world):
                          "kernels_bytes_per_env_step": kb,
                          "whole_step": {"algorithmic_bytes_per_env_step": abytes, "us": step_s * 1e6,
                                         "achieved": abytes * n / step_s / 1e9, "frac": abytes * n / step_s / 1e9 / peak},
-                         "note": ("one kernel per step; float32 SoA state" if legacy else
+                         "note": (("one kernel per step; float32 SoA state" if args.env == "usv-asmc-v0" else
+                                   "one kernel per step; float64 SoA state") if legacy else
                                   "both kernels are float64-issue bound, not HBM bound: see DESIGN.md and profiles/")},
             "clocks": clocks,
             "host_wall_s": t_wall,
@@ -427,9 +446,9 @@ def run_ours(args, rank, local_rank, world):
         if world == 1 and not args.no_cpu_baseline:
             threads = host_threads()
             v, st, el = cpu_oracle_rate(args.ref_envs, args.cpu_budget_s, threads, bool(args.no_obstacles), args.seed,
-                                        legacy)
+                                        legacy, args.env)
             v1, st1, el1 = cpu_oracle_rate(min(args.ref_envs, 1024), max(2.0, args.cpu_budget_s / 4), 1,
-                                           bool(args.no_obstacles), args.seed, legacy)
+                                           bool(args.no_obstacles), args.seed, legacy, args.env)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"{args.ref_envs} lock-step envs x {st} steps ({el:.1f} s), C oracle, OpenMP",
                                     "single_core_value": v1}
@@ -447,7 +466,7 @@ def main():
     ap.add_argument("--steps", type=int, default=600)
     ap.add_argument("--warmup", type=int, default=30)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--env", default="usv-asmc-simple", choices=["usv-asmc-simple", "usv-asmc-v0"])
+    ap.add_argument("--env", default="usv-asmc-simple", choices=["usv-asmc-simple", "usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0"])
     ap.add_argument("--envs-per-gpu", type=int, default=65536)
     ap.add_argument("--batches", type=int, default=3)
     ap.add_argument("--preroll", type=int, default=40, help="untimed steps per batch before warm-up (episode mixing)")

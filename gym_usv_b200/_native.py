@@ -32,12 +32,14 @@ EPI_ROWS = 7
 ENV_ASMC_SIMPLE = 0
 ENV_ASMC_V0 = 1
 ENV_SIMPLE = 2
+ENV_ASMC_YE_INT_V0, ENV_PID_V0 = 3, 4
 PREC_F64 = 0
 PREC_MIXED = 1
 
 FIELD_DYN, FIELD_EPI, FIELD_OBSTACLES, FIELD_N_OBS, FIELD_STEPS, FIELD_EPISODE, FIELD_EP_RETURN = range(7)
-FIELD_LEGACY, FIELD_LEGACY_TARGET, FIELD_LEGACY_POS0 = 7, 8, 9
+FIELD_LEGACY, FIELD_LEGACY_TARGET, FIELD_LEGACY_POS0, FIELD_LEGACY64 = 7, 8, 9, 10
 LEGACY_ROWS = 19
+LEGACY64_ROWS = 21
 LEGACY_OBS_DIM = 6
 LEGACY_NAMES = ("action_last", "u", "v", "r", "x", "y", "psi", "e_u_int", "ka_u", "ka_psi", "x_dot_last", "y_dot_last",
                 "psi_dot_last", "u_dot_last", "v_dot_last", "r_dot_last", "e_u_last", "ka_dot_u_last", "ka_dot_psi_last")

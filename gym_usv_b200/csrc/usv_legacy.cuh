@@ -12,10 +12,17 @@
 // Storage follows the same observation: after a step every state value IS a float32, so the state lives in HBM as
 // float32 [19][N] (half the traffic of a float64 layout); the only float64 state a fresh reset holds is the pose,
 // kept in pos0 [3][N] and read by the first step of the episode only.
+//
+// The two registered siblings share this step() (gym_usv/__init__.py:8-16): 'usv-asmc-ye-int-v0'
+// (usv_asmc_ye_int_env.py: integral of the cross-track error in the observation, other reward / termination) and
+// 'usv-pid-v0' (usv_pid_env.py: PID law instead of the adaptive sliding mode).  Neither has a dtype=np.float32
+// anywhere, so they run legacy_step<double, V> with no rounding and keep their state as float64 [21][N] (st64).
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+
+#include <type_traits>
 
 #include "usv_philox.cuh"
 #include "usv_state.cuh"
@@ -23,7 +30,9 @@
 namespace usv {
 
 constexpr int LEG_ROWS = 19;  // action_last | u v r | x y psi | e_u_int Ka_uKa_psi | last[9]
+constexpr int LEG64_ROWS = 21;  // the 19 rows above | ye_int | ye_last, float64 (ye-int / pid envs)
 constexpr int LEG_OBS = USVGPU_LEGACY_OBS_DIM;
+enum LegVariant { LEG_ASMC_V0 = 0, LEG_YE_INT = 1, LEG_PID = 2 };
 enum LegRow {
     G_ALAST = 0, G_U, G_V, G_R, G_X, G_Y, G_PSI, G_EUI, G_KAU, G_KAP,
     G_XDL, G_YDL, G_PDL, G_UDL, G_VDL, G_RDL, G_EUL, G_KADUL, G_KADPL
@@ -32,6 +41,7 @@ enum LegRow {
 struct LegacyPtrs {
     float* st;          // [19][n]  float32 state (valid when steps > 0; zeros + pos0 when steps == 0)
     double* pos0;       // [3][n]   float64 pose of a freshly reset env (usv_asmc_env.py:293)
+    double* st64;       // [21][n]  float64 state of the ye-int / pid envs (st and pos0 are null for them)
     double* target;     // [6][n]   x_0 y_0 desired_speed ak x_d y_d (usv_asmc_env.py:296), float64
     int* steps;         // [n]
     int* episode;       // [n]
@@ -41,6 +51,7 @@ struct LegacyPtrs {
     long long n;
     long long global_offset;
     unsigned long long seed;
+    int variant;        // LegVariant
 };
 
 // ---- round-to-nearest arithmetic without contraction, float and double --------------------------------------
@@ -73,6 +84,7 @@ __device__ __forceinline__ double l_wrap(double a) {
 
 struct LegacyState {
     double alast, u, v, r, x, y, psi, eui, kau, kap, xdl, ydl, pdl, udl, vdl, rdl, eul, kadul, kadpl;
+    double yeint, yelast;  // usv_asmc_ye_int_env.py: aux_vars[3], last[9]
 };
 struct LegacyOut {
     float obs[LEG_OBS];
@@ -88,6 +100,9 @@ constexpr double M = 30.0, IZ = 4.1, B = 0.41, C = 0.78;
 constexpr double K_U = 0.1, K_PSI = 0.2, KMIN_U = 0.05, KMIN_PSI = 0.2, K2_U = 0.02, K2_PSI = 0.1, MU_U = 0.05,
                  MU_PSI = 0.1, LAMBDA_U = 0.001, LAMBDA_PSI = 1.0, K_AK = 5.72, K_YE = 0.5, SIGMA_YE = 1.0;
 constexpr double MAX_YE = 10.0, MAX_X = 30.0, W_ACTION = 0.2;
+constexpr double MIN_X = -10.0;                                    // usv_asmc_ye_int_env.py:63, usv_pid_env.py:60
+constexpr double K_I = 0.001;                                      // usv_asmc_ye_int_env.py: k_i
+constexpr double KP_U = 1.1, KI_U = 0.2, KD_U = 0.1, KP_PSI = 0.8, KD_PSI = 3.0;  // usv_pid_env.py:37-41
 // :132-133  1.1+0.0045*(1.01/0.09) - 0.1*(0.27/0.09)+0.016*(np.power((0.27/0.09), 2))  (an np.float64)
 constexpr double YV_K = 1.1 + 0.0045 * (1.01 / 0.09) - 0.1 * (0.27 / 0.09) + 0.016 * ((0.27 / 0.09) * (0.27 / 0.09));
 // :77  1. / np.power((max_action/2 - min_action/2) / integral_step, 2)
@@ -98,11 +113,14 @@ constexpr double M00 = M - XUD, M11 = M - YVD, M12 = 0 - YRD, M21 = 0 - NVD, M22
 constexpr double DET = M11 * M22 - M12 * M21;
 constexpr double MI00 = 1.0 / M00, MI11 = M22 / DET, MI12 = -M12 / DET, MI21 = -M21 / DET, MI22 = M11 / DET;
 // UsvAsmcEnv.step (usv_asmc_env.py:99-255).  S: the dtype numpy gives to expressions built from the unpacked state
-// scalars and Python literals (double on the first step of an episode, float afterwards).
-template <typename S>
+// scalars and Python literals (double on the first step of an episode, float afterwards).  V: LegVariant; the
+// siblings (V != 0) are S = double with arrays and stores left in float64.
+template <typename S, int V = LEG_ASMC_V0>
 __device__ __forceinline__ void legacy_step(LegacyState& e, const double x_0, const double y_0,
                                             const double desired_speed, const double ak, const float action,
                                             LegacyOut& out) {
+    static_assert(V == LEG_ASMC_V0 || std::is_same<S, double>::value, "the siblings are float64 throughout");
+    using A = typename std::conditional<V == LEG_ASMC_V0, float, double>::type;  // dtype of T, CRB, CA, Dl, Dn, J
     // :108-115 unpack
     const S action_last = (S)e.alast, u = (S)e.u, v = (S)e.v, r = (S)e.r, x = (S)e.x, y = (S)e.y, psi = (S)e.psi;
     const S e_u_int0 = (S)e.eui, Ka_u0 = (S)e.kau, Ka_psi0 = (S)e.kap;
@@ -143,22 +161,34 @@ __device__ __forceinline__ void legacy_step(LegacyState& e, const double x_0, co
     // :158-162  e_u_last is read but never written by the reference: it stays 0
     const double e_u = r_sub(u_d, (double)u);
     const double e_u_int = r_add(r_div(r_mul(H, r_add(e_u, (double)e_u_last)), 2.0), (double)e_u_int0);
-    const double sigma_u = r_add(e_u, r_mul(LAMBDA_U, e_u_int));
-    const double sigma_psi = r_add((double)e_psi_dot, r_mul(LAMBDA_PSI, e_psi));
+    double Ka_dot_u, Ka_dot_psi, Ka_u, Ka_psi, Tx, Tz;
+    if constexpr (V == LEG_PID) {
+        // usv_pid_env.py:149-155  PID law; the adaptive gains are carried along untouched (they stay 0)
+        const double e_u_dot = r_div(r_sub(e_u, (double)e_u_last), H);
+        const double ua_u = r_add(r_add(r_mul(KP_U, e_u), r_mul(KI_U, e_u_int)), r_mul(KD_U, e_u_dot));
+        const double ua_psi = r_add(r_mul(KP_PSI, e_psi), r_mul(KD_PSI, (double)e_psi_dot));
+        Ka_u = (double)Ka_u0, Ka_psi = (double)Ka_psi0;
+        Ka_dot_u = (double)Ka_dot_u_last, Ka_dot_psi = (double)Ka_dot_psi_last;
+        Tx = r_div(r_add(-(double)f_u, ua_u), g_u);
+        Tz = r_div(r_add(-(double)f_psi, ua_psi), g_psi);
+    } else {
+        const double sigma_u = r_add(e_u, r_mul(LAMBDA_U, e_u_int));
+        const double sigma_psi = r_add((double)e_psi_dot, r_mul(LAMBDA_PSI, e_psi));
 
-    // :164-171
-    const double Ka_dot_u = (Ka_u0 > (S)KMIN_U) ? r_mul(K_U, l_sign(r_sub(fabs(sigma_u), MU_U))) : KMIN_U;
-    const double Ka_dot_psi = (Ka_psi0 > (S)KMIN_PSI) ? r_mul(K_PSI, l_sign(r_sub(fabs(sigma_psi), MU_PSI))) : KMIN_PSI;
-    const double Ka_u = r_add(r_div(r_mul(H, r_add(Ka_dot_u, (double)Ka_dot_u_last)), 2.0), (double)Ka_u0);
-    const double Ka_psi = r_add(r_div(r_mul(H, r_add(Ka_dot_psi, (double)Ka_dot_psi_last)), 2.0), (double)Ka_psi0);
+        // :164-171
+        Ka_dot_u = (Ka_u0 > (S)KMIN_U) ? r_mul(K_U, l_sign(r_sub(fabs(sigma_u), MU_U))) : KMIN_U;
+        Ka_dot_psi = (Ka_psi0 > (S)KMIN_PSI) ? r_mul(K_PSI, l_sign(r_sub(fabs(sigma_psi), MU_PSI))) : KMIN_PSI;
+        Ka_u = r_add(r_div(r_mul(H, r_add(Ka_dot_u, (double)Ka_dot_u_last)), 2.0), (double)Ka_u0);
+        Ka_psi = r_add(r_div(r_mul(H, r_add(Ka_dot_psi, (double)Ka_dot_psi_last)), 2.0), (double)Ka_psi0);
 
-    // :173-174  np.power(., 0.5) == sqrt
-    const double ua_u = r_sub(r_mul(r_mul(-Ka_u, r_sqrt(fabs(sigma_u))), l_sign(sigma_u)), r_mul(K2_U, sigma_u));
-    const double ua_psi = r_sub(r_mul(r_mul(-Ka_psi, r_sqrt(fabs(sigma_psi))), l_sign(sigma_psi)), r_mul(K2_PSI, sigma_psi));
+        // :173-174  np.power(., 0.5) == sqrt
+        const double ua_u = r_sub(r_mul(r_mul(-Ka_u, r_sqrt(fabs(sigma_u))), l_sign(sigma_u)), r_mul(K2_U, sigma_u));
+        const double ua_psi = r_sub(r_mul(r_mul(-Ka_psi, r_sqrt(fabs(sigma_psi))), l_sign(sigma_psi)), r_mul(K2_PSI, sigma_psi));
 
-    // :176-185
-    const double Tx = r_div(r_sub(r_sub(r_mul(LAMBDA_U, e_u), (double)f_u), ua_u), g_u);
-    const double Tz = r_div(r_sub(r_sub(r_mul(LAMBDA_PSI, e_psi), (double)f_psi), ua_psi), g_psi);
+        // :176-185
+        Tx = r_div(r_sub(r_sub(r_mul(LAMBDA_U, e_u), (double)f_u), ua_u), g_u);
+        Tz = r_div(r_sub(r_sub(r_mul(LAMBDA_PSI, e_psi), (double)f_psi), ua_psi), g_psi);
+    }
     double Tport = r_add(r_div(Tx, 2.0), r_div(Tz, B));
     double Tstbd = r_sub(r_div(Tx, 2 * C), r_div(Tz, B * C));
     if (Tport > 36.5) Tport = 36.5;
@@ -167,30 +197,30 @@ __device__ __forceinline__ void legacy_step(LegacyState& e, const double x_0, co
     if (Tstbd < -30) Tstbd = -30;
 
     // :191  dtype=np.float32
-    const float T0 = (float)r_add(Tport, r_mul(C, Tstbd));
-    const float T2 = (float)r_mul(0.5 * B, r_sub(Tport, r_mul(C, Tstbd)));
+    const A T0 = (A)r_add(Tport, r_mul(C, Tstbd));
+    const A T2 = (A)r_mul(0.5 * B, r_sub(Tport, r_mul(C, Tstbd)));
 
     // :193-201  entries evaluated in S, stored float32; C = CRB + CA in float32
-    const float CRB02 = (float)r_sub((S)0, r_mul((S)M, v)), CRB12 = (float)r_mul((S)M, u);
-    const float CRB20 = (float)r_mul((S)M, v), CRB21 = (float)r_sub((S)0, r_mul((S)M, u));
+    const A CRB02 = (A)r_sub((S)0, r_mul((S)M, v)), CRB12 = (A)r_mul((S)M, u);
+    const A CRB20 = (A)r_mul((S)M, v), CRB21 = (A)r_sub((S)0, r_mul((S)M, u));
     const S half_yn = (S)((YRD + NVD) / 2);
-    const float CA02 = (float)r_mul((S)2, r_add(r_mul((S)YVD, v), r_mul(half_yn, r)));
-    const float CA12 = (float)r_sub((S)0, r_mul((S)(XUD * M), u));
-    const float CA20 = (float)r_mul((S)2, r_sub(r_mul((S)(0 - YVD), v), r_mul(half_yn, r)));
-    const float CA21 = (float)r_mul((S)(XUD * M), u);
-    const float C02 = r_add(CRB02, CA02), C12 = r_add(CRB12, CA12), C20 = r_add(CRB20, CA20), C21 = r_add(CRB21, CA21);
+    const A CA02 = (A)r_mul((S)2, r_add(r_mul((S)YVD, v), r_mul(half_yn, r)));
+    const A CA12 = (A)r_sub((S)0, r_mul((S)(XUD * M), u));
+    const A CA20 = (A)r_mul((S)2, r_sub(r_mul((S)(0 - YVD), v), r_mul(half_yn, r)));
+    const A CA21 = (A)r_mul((S)(XUD * M), u);
+    const A C02 = r_add(CRB02, CA02), C12 = r_add(CRB12, CA12), C20 = r_add(CRB20, CA20), C21 = r_add(CRB21, CA21);
 
     // :203-212
-    const float Dl00 = (float)(0 - Xu), Dl11 = (float)(0 - Yv), Dl12 = (float)r_sub((S)0, Yr);
-    const float Dl21 = (float)r_sub((S)0, Nv), Dl22 = (float)r_sub((S)0, Nr);
+    const A Dl00 = (A)(0 - Xu), Dl11 = (A)(0 - Yv), Dl12 = (A)r_sub((S)0, Yr);
+    const A Dl21 = (A)r_sub((S)0, Nv), Dl22 = (A)r_sub((S)0, Nr);
     const S au = r_abs(u), av = r_abs(v), ar = r_abs(r);
-    const float Dn00 = (float)r_mul((S)Xuu, au);
-    const float Dn11 = (float)r_add(r_mul((S)YVV, av), r_mul((S)YVR, ar));
-    const float Dn12 = (float)r_add(r_mul((S)YRV, av), r_mul((S)YRR, ar));
-    const float Dn21 = (float)r_add(r_mul((S)NVV, av), r_mul((S)NVR, ar));
-    const float Dn22 = (float)r_add(r_mul((S)NRV, av), r_mul((S)NRR, ar));
-    const float D00 = r_sub(Dl00, Dn00), D11 = r_sub(Dl11, Dn11), D12 = r_sub(Dl12, Dn12);
-    const float D21 = r_sub(Dl21, Dn21), D22 = r_sub(Dl22, Dn22);
+    const A Dn00 = (A)r_mul((S)Xuu, au);
+    const A Dn11 = (A)r_add(r_mul((S)YVV, av), r_mul((S)YVR, ar));
+    const A Dn12 = (A)r_add(r_mul((S)YRV, av), r_mul((S)YRR, ar));
+    const A Dn21 = (A)r_add(r_mul((S)NVV, av), r_mul((S)NVR, ar));
+    const A Dn22 = (A)r_add(r_mul((S)NRV, av), r_mul((S)NRR, ar));
+    const A D00 = r_sub(Dl00, Dn00), D11 = r_sub(Dl11, Dn11), D12 = r_sub(Dl12, Dn12);
+    const A D21 = r_sub(Dl21, Dn21), D22 = r_sub(Dl22, Dn22);
 
     // :214-218  matmul(float32 3x3, S vector) and T - . - . are S; inv(M) @ . is float64
     const S Cv0 = r_mul((S)C02, r), Cv1 = r_mul((S)C12, r), Cv2 = r_add(r_mul((S)C20, u), r_mul((S)C21, v));
@@ -207,7 +237,7 @@ __device__ __forceinline__ void legacy_step(LegacyState& e, const double x_0, co
     // :220-229  J is float32: np.cos / np.sin of the S heading, rounded
     S sn_s, cs_s;
     r_sincos(psi, sn_s, cs_s);
-    const float Jc = (float)cs_s, Js = (float)sn_s;
+    const A Jc = (A)cs_s, Js = (A)sn_s;
     const double xd = r_add(r_mul((double)Jc, un), r_mul((double)(-Js), vn));
     const double yd = r_add(r_mul((double)Js, un), r_mul((double)Jc, vn));
     const double pd = rn;
@@ -226,10 +256,23 @@ __device__ __forceinline__ void legacy_step(LegacyState& e, const double x_0, co
     const double ad2 = (double)r_mul(action_dot, action_dot);
     const double a_psi_ak = fabs(psi_ak);
     const double reward_action = r_mul(W_ACTION, tanh(r_mul(-C_ACTION, ad2)));
-    const double reward_ye = (ye_abs > SIGMA_YE) ? exp(r_mul(-K_YE, ye_abs))
-                                                 : exp(r_div(r_mul(-K_YE, r_mul(ye_abs, ye_abs)), SIGMA_YE));
     const double reward_ak = -exp(r_mul(K_AK, r_sub(a_psi_ak, PI)));
-    double reward = (a_psi_ak < PI / 2) ? r_add(reward_action, reward_ye) : reward_ak;
+    double reward, ye_obs = ye;
+    if constexpr (V == LEG_YE_INT) {
+        // usv_asmc_ye_int_env.py:230-236, 350-360
+        double ye_int = e.yeint;
+        if (l_sign(ye) != l_sign(e.yelast)) ye_int = 0;
+        ye_int = r_add(r_mul(H, r_add(ye, e.yelast)), ye_int);
+        ye_obs = r_add(ye, r_mul(K_I, ye_int));
+        e.yeint = ye_int;
+        e.yelast = ye;
+        const double reward_ye = exp(r_mul(-K_YE, ye_abs));
+        reward = r_add(reward_action, (a_psi_ak < PI / 2) ? reward_ye : reward_ak);
+    } else {
+        const double reward_ye = (ye_abs > SIGMA_YE) ? exp(r_mul(-K_YE, ye_abs))
+                                                     : exp(r_div(r_mul(-K_YE, r_mul(ye_abs, ye_abs)), SIGMA_YE));
+        reward = (a_psi_ak < PI / 2) ? r_add(reward_action, reward_ye) : reward_ak;
+    }
 
     // :239, 376-401
     double spa, cpa;
@@ -238,35 +281,36 @@ __device__ __forceinline__ void legacy_step(LegacyState& e, const double x_0, co
 
     // :241-245
     bool done = false;
-    if (ye_abs > MAX_YE || fabs(xn) > MAX_X) {
+    // siblings: usv_asmc_ye_int_env.py:241, usv_pid_env.py:219
+    if (ye_abs > MAX_YE || (V == LEG_ASMC_V0 ? fabs(xn) > MAX_X : xn < MIN_X)) {
         done = true;
         reward = -1;
     }
 
-    // :247-251  everything re-stored as float32
+    // :247-251  everything re-stored as float32 (the siblings keep float64)
     e.alast = (double)action;
-    e.u = (float)un;
-    e.v = (float)vn;
-    e.r = (float)rn;
-    e.x = (float)xn;
-    e.y = (float)yn;
-    e.psi = (float)psin;
-    e.eui = (float)e_u_int;
-    e.kau = (float)Ka_u;
-    e.kap = (float)Ka_psi;
-    e.xdl = (float)xd;
-    e.ydl = (float)yd;
-    e.pdl = (float)pd;
-    e.udl = (float)ud0;
-    e.vdl = (float)ud1;
-    e.rdl = (float)ud2;
-    e.eul = (float)(double)e_u_last;
-    e.kadul = (float)Ka_dot_u;
-    e.kadpl = (float)Ka_dot_psi;
+    e.u = (double)(A)un;
+    e.v = (double)(A)vn;
+    e.r = (double)(A)rn;
+    e.x = (double)(A)xn;
+    e.y = (double)(A)yn;
+    e.psi = (double)(A)psin;
+    e.eui = (double)(A)e_u_int;
+    e.kau = (double)(A)Ka_u;
+    e.kap = (double)(A)Ka_psi;
+    e.xdl = (double)(A)xd;
+    e.ydl = (double)(A)yd;
+    e.pdl = (double)(A)pd;
+    e.udl = (double)(A)ud0;
+    e.vdl = (double)(A)ud1;
+    e.rdl = (double)(A)ud2;
+    e.eul = (double)(A)(double)e_u_last;
+    e.kadul = (double)(A)Ka_dot_u;
+    e.kadpl = (double)(A)Ka_dot_psi;
     out.obs[0] = (float)un;
     out.obs[1] = (float)v_ak;
     out.obs[2] = (float)rn;
-    out.obs[3] = (float)ye;
+    out.obs[3] = (float)ye_obs;
     out.obs[4] = (float)psi_ak;
     out.obs[5] = action;
     out.reward = reward;
@@ -285,20 +329,28 @@ __device__ __forceinline__ void legacy_reset_env(const LegacyPtrs& s, long long 
     double d[8];
 #pragma unroll
     for (int b = 0; b < 4; ++b) dk.pair(b, d[2 * b], d[2 * b + 1]);
-    const double x = -2.5 + (2.5 - -2.5) * d[0], y = -2.5 + (2.5 - -2.5) * d[1], psi = -PI + (PI - -PI) * d[2];
+    // usv_asmc_ye_int_env.py:258-259 draws x, y from +-5; both siblings draw the speed from 0.4..1.4 (:279, usv_pid_env.py:257)
+    const double xy = (s.variant == LEG_YE_INT) ? 5.0 : 2.5, sp0 = (s.variant == LEG_ASMC_V0) ? 1.4 : 0.4;
+    const double x = -xy + (xy - -xy) * d[0], y = -xy + (xy - -xy) * d[1], psi = -PI + (PI - -PI) * d[2];
     const double x_0 = -2.5 + (2.5 - -2.5) * d[3], y_0 = -2.5 + (2.5 - -2.5) * d[4];
-    const double x_d = 15 + (30 - 15) * d[5], desired_speed = 1.4 + (2.4 - 1.4) * d[6];
+    const double x_d = 15 + (30 - 15) * d[5], desired_speed = sp0 + ((sp0 + 1.0) - sp0) * d[6];
     const double y_d = y_0;                                                        // :280
     const double ak = (double)(float)atan2(r_sub(y_d, y_0), r_sub(x_d, x_0));      // :283-284 np.float32(ak)
     const double psi_ak = (double)(float)l_wrap(r_sub(psi, ak));                   // :286-288
     double sak, cak;
     sincos(ak, &sak, &cak);
     const double ye = r_add(r_mul(-r_sub(x, x_0), sak), r_mul(r_sub(y, y_0), cak));  // :289
+    if (s.variant == LEG_ASMC_V0) {
 #pragma unroll
-    for (int k = 0; k < LEG_ROWS; ++k) s.st[(long long)k * n + i] = 0.0f;
-    s.pos0[i] = x;
-    s.pos0[n + i] = y;
-    s.pos0[2 * n + i] = psi;
+        for (int k = 0; k < LEG_ROWS; ++k) s.st[(long long)k * n + i] = 0.0f;
+        s.pos0[i] = x;
+        s.pos0[n + i] = y;
+        s.pos0[2 * n + i] = psi;
+    } else {
+#pragma unroll
+        for (int k = 0; k < LEG64_ROWS; ++k)
+            s.st64[(long long)k * n + i] = (k == G_X) ? x : (k == G_Y) ? y : (k == G_PSI) ? psi : 0.0;
+    }
     double* tg = s.target + i;
     tg[0] = x_0;
     tg[n] = y_0;
@@ -398,6 +450,74 @@ legacy_step_kernel(LegacyPtrs s, StepFlags fl, const float* __restrict__ actions
                                    (float)e.kadul, (float)e.kadpl};
 #pragma unroll
         for (int k = 0; k < LEG_ROWS; ++k) st[(long long)k * n] = g[k];
+        s.steps[i] = steps;
+    }
+    float2* row = reinterpret_cast<float2*>(obs + i * LEG_OBS);
+    row[0] = make_float2(o[0], o[1]);
+    row[1] = make_float2(o[2], o[3]);
+    row[2] = make_float2(o[4], o[5]);
+}
+
+// One VecEnv.step() of N UsvAsmcYeIntEnv (V = LEG_YE_INT) or UsvPidEnv (V = LEG_PID): the same thread-per-env
+// shape over the float64 state columns st64 [21][N] (the pid env never touches rows 19, 20).
+template <int V>
+__global__ void __launch_bounds__(LEG_B)
+legacy64_step_kernel(LegacyPtrs s, StepFlags fl, const float* __restrict__ actions, float* __restrict__ obs,
+                     float* __restrict__ reward, uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated,
+                     float* __restrict__ terminal_obs) {
+    constexpr int ROWS = (V == LEG_YE_INT) ? LEG64_ROWS : LEG_ROWS;
+    const long long n = s.n;
+    const long long i = fl.lo + (long long)blockIdx.x * LEG_B + threadIdx.x;
+    if (i >= fl.hi) return;
+    double* st = s.st64 + i;
+    double f[LEG64_ROWS];
+#pragma unroll
+    for (int k = 0; k < LEG64_ROWS; ++k) f[k] = (k < ROWS) ? st[(long long)k * n] : 0.0;
+    int steps = s.steps[i];
+    const double* tg = s.target + i;
+    const double x_0 = tg[0], y_0 = tg[n], desired_speed = tg[2 * n], ak = tg[3 * n];
+    const float action = actions[i];
+    LegacyState e = {f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7], f[8], f[9], f[10], f[11], f[12], f[13], f[14],
+                     f[15], f[16], f[17], f[18], f[19], f[20]};
+    LegacyOut out;
+    leg::legacy_step<double, V>(e, x_0, y_0, desired_speed, ak, action, out);
+    steps += 1;
+    const bool tlimit = (fl.max_episode_steps > 0) && (steps >= fl.max_episode_steps);
+    const bool done = out.done || tlimit;
+    reward[i] = (float)out.reward;
+    terminated[i] = out.done ? 1 : 0;
+    truncated[i] = (tlimit && !out.done) ? 1 : 0;
+    if (!(isfinite(e.x) && isfinite(e.y) && isfinite(e.psi))) atomicAdd(&s.stats->nonfinite, 1ull);
+
+    float* o = out.obs;
+    if (done) {
+        const double ep_ret = s.ep_return[i] + out.reward;
+        s.ep_done[i] = make_double2(ep_ret, (double)steps);
+        DeviceStats* ds = s.stats;
+        atomicAdd(&ds->return_sum, ep_ret);
+        atomicAdd(&ds->length_sum, (double)steps);
+        atomicAdd(&ds->episodes, 1ull);
+        if (out.done) atomicAdd(&ds->terminated, 1ull);
+        else atomicAdd(&ds->time_limit, 1ull);
+        if (fl.auto_reset) {
+            if (terminal_obs) {
+                float2* trow = reinterpret_cast<float2*>(terminal_obs + i * LEG_OBS);
+                trow[0] = make_float2(o[0], o[1]);
+                trow[1] = make_float2(o[2], o[3]);
+                trow[2] = make_float2(o[4], o[5]);
+            }
+            legacy_reset_env(s, i, o);  // rewrites the state columns, steps and ep_return
+        } else {
+            s.ep_return[i] = ep_ret;
+        }
+    } else {
+        s.ep_return[i] += out.reward;
+    }
+    if (!(done && fl.auto_reset)) {
+        const double g[LEG64_ROWS] = {e.alast, e.u, e.v, e.r, e.x, e.y, e.psi, e.eui, e.kau, e.kap, e.xdl,
+                                      e.ydl, e.pdl, e.udl, e.vdl, e.rdl, e.eul, e.kadul, e.kadpl, e.yeint, e.yelast};
+#pragma unroll
+        for (int k = 0; k < ROWS; ++k) st[(long long)k * n] = g[k];
         s.steps[i] = steps;
     }
     float2* row = reinterpret_cast<float2*>(obs + i * LEG_OBS);

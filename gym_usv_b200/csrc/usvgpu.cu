@@ -105,9 +105,14 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
                      float* tobs, cudaStream_t st, cudaEvent_t mid = nullptr, long long lo = 0, long long hi = -1) {
     if (hi < 0) hi = h->sp.n;
     const StepFlags fl = {h->cfg.do_perturb, h->cfg.skip_kinematic, h->cfg.max_episode_steps, h->cfg.auto_reset, lo, hi};
-    if (h->legacy) {  // 'usv-asmc-v0': one kernel, thread per env
-        legacy_step_kernel<<<(unsigned)((hi - lo + LEG_B - 1) / LEG_B), LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term,
-                                                                                    trunc, tobs);
+    if (h->legacy) {  // 'usv-asmc-v0' and its float64 siblings: one kernel, thread per env
+        const unsigned lblocks = (unsigned)((hi - lo + LEG_B - 1) / LEG_B);
+        if (h->lp.variant == LEG_YE_INT)
+            legacy64_step_kernel<LEG_YE_INT><<<lblocks, LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term, trunc, tobs);
+        else if (h->lp.variant == LEG_PID)
+            legacy64_step_kernel<LEG_PID><<<lblocks, LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term, trunc, tobs);
+        else
+            legacy_step_kernel<<<lblocks, LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term, trunc, tobs);
         cudaError_t le = cudaGetLastError();
         if (le != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("legacy step launch: ") + cudaGetErrorString(le));
         if (mid) cudaEventRecord(mid, st);
@@ -145,9 +150,10 @@ static bool bad_alignment(const UsvGpu* h, const void* obs, const void* actions)
 static int field_ptr(UsvGpu* h, int32_t field, void** p, int64_t* bytes) {
     const int64_t n = h->sp.n;
     switch (field) {
-        case USV_FIELD_LEGACY: if (!h->legacy) return -1; *p = h->lp.st; *bytes = n * LEG_ROWS * 4; return 0;
+        case USV_FIELD_LEGACY: if (!h->lp.st) return -1; *p = h->lp.st; *bytes = n * LEG_ROWS * 4; return 0;
         case USV_FIELD_LEGACY_TARGET: if (!h->legacy) return -1; *p = h->lp.target; *bytes = n * 6 * 8; return 0;
-        case USV_FIELD_LEGACY_POS0: if (!h->legacy) return -1; *p = h->lp.pos0; *bytes = n * 3 * 8; return 0;
+        case USV_FIELD_LEGACY_POS0: if (!h->lp.pos0) return -1; *p = h->lp.pos0; *bytes = n * 3 * 8; return 0;
+        case USV_FIELD_LEGACY64: if (!h->lp.st64) return -1; *p = h->lp.st64; *bytes = n * LEG64_ROWS * 8; return 0;
         case USV_FIELD_DYN: if (h->legacy) return -1; *p = h->sp.dyn; *bytes = n * N_DYN * 8; return 0;
         case USV_FIELD_EPI: if (h->legacy) return -1; *p = h->sp.epi; *bytes = n * N_EPI * 8; return 0;
         // these two live inside the interleaved sensor-input rows: *p is the first element, copies are pitched
@@ -171,7 +177,7 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     if (!cfg || !out) return fail(nullptr, USV_ERR_INVALID, "cfg/out is NULL");
     *out = nullptr;
     if (n_envs <= 0) return fail(nullptr, USV_ERR_INVALID, "n_envs must be positive");
-    if (cfg->env_kind != USV_ENV_ASMC_SIMPLE && cfg->env_kind != USV_ENV_ASMC_V0 && cfg->env_kind != USV_ENV_SIMPLE)
+    if (cfg->env_kind < USV_ENV_ASMC_SIMPLE || cfg->env_kind > USV_ENV_PID_V0)
         return fail(nullptr, USV_ERR_INVALID, "unknown env_kind");
     if (cfg->precision != USV_PREC_F64) return fail(nullptr, USV_ERR_INVALID, "precision not supported by this build");
     int rc = check_device(nullptr, device);
@@ -180,7 +186,8 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     if (!h) return fail(nullptr, USV_ERR_ALLOC, "host allocation failed");
     h->cfg = *cfg;
     h->device = device;
-    h->legacy = cfg->env_kind == USV_ENV_ASMC_V0;
+    const int variant = cfg->env_kind == USV_ENV_ASMC_YE_INT_V0 ? LEG_YE_INT : cfg->env_kind == USV_ENV_PID_V0 ? LEG_PID : LEG_ASMC_V0;
+    h->legacy = cfg->env_kind == USV_ENV_ASMC_V0 || variant != LEG_ASMC_V0;
     h->obs_dim = h->legacy ? LEG_OBS : OBS_DIM;
     h->act_dim = h->legacy ? 1 : 2;
     memset(&h->lp, 0, sizeof(h->lp));
@@ -213,8 +220,12 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
         if (e == cudaSuccess) e = cudaMemset(*p, 0, bytes);
     };
     if (h->legacy) {
-        alloc((void**)&h->lp.st, n * LEG_ROWS * sizeof(float));
-        alloc((void**)&h->lp.pos0, n * 3 * sizeof(double));
+        if (variant == LEG_ASMC_V0) {
+            alloc((void**)&h->lp.st, n * LEG_ROWS * sizeof(float));
+            alloc((void**)&h->lp.pos0, n * 3 * sizeof(double));
+        } else {
+            alloc((void**)&h->lp.st64, n * LEG64_ROWS * sizeof(double));
+        }
         alloc((void**)&h->lp.target, n * 6 * sizeof(double));
     } else {
         alloc((void**)&h->sp.dyn, n * N_DYN * sizeof(double));
@@ -250,6 +261,7 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->lp.n = n_envs;
     h->lp.global_offset = global_env_offset;
     h->lp.seed = seed;
+    h->lp.variant = variant;
     *out = h;
     return USV_OK;
 }
@@ -262,6 +274,7 @@ int usvgpu_destroy(usvgpu_handle h) {
     cudaSetDevice(h->device);
     cudaFree(h->lp.st);
     cudaFree(h->lp.pos0);
+    cudaFree(h->lp.st64);
     cudaFree(h->lp.target);
     cudaFree(h->sp.dyn);
     cudaFree(h->sp.epi);

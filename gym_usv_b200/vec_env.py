@@ -26,8 +26,12 @@ from . import spaces
 
 ENV_ID = "usv-asmc-simple"
 # gym_usv/__init__.py:30-34 registers a 1000-step TimeLimit for 'usv-asmc-simple' and none for 'usv-asmc-v0' (:3-6)
-MAX_EPISODE_STEPS = {"usv-asmc-simple": 1000, "usv-asmc-v0": 0, "usv-simple": 500}  # usv-simple: __init__.py:24-28
-ENV_KINDS = {"usv-asmc-simple": nat.ENV_ASMC_SIMPLE, "usv-asmc-v0": nat.ENV_ASMC_V0, "usv-simple": nat.ENV_SIMPLE}
+# 'usv-pid-v0' (:8-11) and 'usv-asmc-ye-int-v0' (:13-16) are registered without a limit as well
+MAX_EPISODE_STEPS = {"usv-asmc-simple": 1000, "usv-asmc-v0": 0, "usv-simple": 500,  # usv-simple: __init__.py:24-28
+                     "usv-asmc-ye-int-v0": 0, "usv-pid-v0": 0}
+ENV_KINDS = {"usv-asmc-simple": nat.ENV_ASMC_SIMPLE, "usv-asmc-v0": nat.ENV_ASMC_V0, "usv-simple": nat.ENV_SIMPLE,
+             "usv-asmc-ye-int-v0": nat.ENV_ASMC_YE_INT_V0, "usv-pid-v0": nat.ENV_PID_V0}
+LEGACY_IDS = ("usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0")  # UsvAsmcEnv's step() and its two float64 siblings
 
 
 class LazyInfos(Sequence):
@@ -67,7 +71,8 @@ class UsvGpuVecEnv:
         if env_id not in ENV_KINDS:
             raise nat.UsvError(f"unknown env id '{env_id}' (have: {sorted(ENV_KINDS)})")
         self.env_id = env_id
-        self.legacy = env_id == "usv-asmc-v0"  # UsvAsmcEnv, gym_usv/envs/usv_asmc_env.py
+        self.legacy = env_id in LEGACY_IDS  # UsvAsmcEnv, gym_usv/envs/usv_asmc_env.py, UsvAsmcYeIntEnv, UsvPidEnv
+        self.legacy64 = self.legacy and env_id != "usv-asmc-v0"  # float64 state (USV_FIELD_LEGACY64)
         self.obs_dim = nat.LEGACY_OBS_DIM if self.legacy else nat.OBS_DIM
         self.act_dim = 1 if self.legacy else nat.ACT_DIM
         self.observation_space = spaces.legacy_observation_space() if self.legacy else spaces.simple_observation_space()
@@ -286,8 +291,9 @@ class UsvGpuVecEnv:
             return [getattr(self, attr_name)] * len(idx)
         fields = self.get_state()
         if attr_name in ("position", "velocity"):
-            if self.legacy:  # rows of USV_FIELD_LEGACY: action_last | u v r | x y psi | ...
-                rows = fields["legacy"][4:7] if attr_name == "position" else fields["legacy"][1:4]
+            if self.legacy:  # rows of USV_FIELD_LEGACY / LEGACY64: action_last | u v r | x y psi | ...
+                st = fields["legacy64" if self.legacy64 else "legacy"]
+                rows = st[4:7] if attr_name == "position" else st[1:4]
             else:
                 rows = fields["dyn"][0:3] if attr_name == "position" else fields["dyn"][3:6]
             return [rows[:, i].copy() for i in idx]
@@ -319,9 +325,14 @@ class UsvGpuVecEnv:
                       "pos0": (nat.FIELD_LEGACY_POS0, np.float64, (3,), ()),
                       "steps": (nat.FIELD_STEPS, np.int32, (), ()), "episode": (nat.FIELD_EPISODE, np.int32, (), ()),
                       "ep_return": (nat.FIELD_EP_RETURN, np.float64, (), ())}
+    _LEGACY64_FIELDS = {"legacy64": (nat.FIELD_LEGACY64, np.float64, (nat.LEGACY64_ROWS,), ()),
+                        **{k: v for k, v in _LEGACY_FIELDS.items() if k not in ("legacy", "pos0")}}
+
+    def _field_table(self):
+        return self._LEGACY64_FIELDS if self.legacy64 else self._LEGACY_FIELDS if self.legacy else self._FIELDS
 
     def _field_array(self, name):
-        fid, dt, lead, trail = (self._LEGACY_FIELDS if self.legacy else self._FIELDS)[name]
+        fid, dt, lead, trail = self._field_table()[name]
         if dt is None:
             dt = np.float32 if self.cfg.obstacles_f32 else np.float64
         return fid, np.zeros(lead + (self.num_envs,) + trail, dtype=dt)
@@ -329,7 +340,7 @@ class UsvGpuVecEnv:
     def get_state(self, names: Optional[Sequence[str]] = None) -> dict:
         """Host copies of the state field groups ([rows][N]; obstacles [N][3][32]); see include/usvgpu.h UsvField."""
         out = {}
-        for name in (names or (self._LEGACY_FIELDS if self.legacy else self._FIELDS)):
+        for name in (names or self._field_table()):
             fid, arr = self._field_array(name)
             self._check(self._lib.usvgpu_get_state(self._h, fid, arr.ctypes.data_as(C.c_void_p), arr.nbytes,
                                                    self._stream()))

@@ -40,10 +40,14 @@ typedef enum UsvStatus {
 typedef enum UsvEnvKind {
     USV_ENV_ASMC_SIMPLE = 0, /* 'usv-asmc-simple' gym_usv/__init__.py:30-34 -> envs/simple_env_asmc.py */
     USV_ENV_ASMC_V0 = 1,     /* 'usv-asmc-v0'     gym_usv/__init__.py:3-6   -> envs/usv_asmc_env.py    */
-    USV_ENV_SIMPLE = 2       /* 'usv-simple'      gym_usv/__init__.py:24-28 -> envs/simple_env.py: the kinematic
+    USV_ENV_SIMPLE = 2,      /* 'usv-simple'      gym_usv/__init__.py:24-28 -> envs/simple_env.py: the kinematic
                               * env train_test/sb3_train_vec.py:55 trains on (TimeLimit 500).  Same spaces, state
                               * fields and entry points as 'usv-asmc-simple'; USV_FIELD_DYN rows 6 and 7 hold
                               * last_action[0] and last_action[2] (simple_env.py:41,343), rows 8..21 are unused */
+    /* the two float64 siblings of 'usv-asmc-v0': same spaces (obs [N][6], actions [N][1]) and entry points; their
+     * state is USV_FIELD_LEGACY64 (+ USV_FIELD_LEGACY_TARGET), USV_FIELD_LEGACY / _POS0 do not exist for them */
+    USV_ENV_ASMC_YE_INT_V0 = 3, /* 'usv-asmc-ye-int-v0' gym_usv/__init__.py:13-16 -> envs/usv_asmc_ye_int_env.py */
+    USV_ENV_PID_V0 = 4          /* 'usv-pid-v0'         gym_usv/__init__.py:8-11  -> envs/usv_pid_env.py         */
 } UsvEnvKind;
 
 typedef enum UsvPrecision {
@@ -102,10 +106,15 @@ typedef enum UsvField {
     USV_FIELD_LEGACY_TARGET = 8, /* float64 [6][N]: x_0 y_0 desired_speed ak x_d y_d (usv_asmc_env.py:296) */
     /* float64 [3][N]: pose x y psi of an env that was reset and has not stepped yet (STEPS == 0): reset() stores
      * float64 arrays (usv_asmc_env.py:293) and the first step computes in float64 from them */
-    USV_FIELD_LEGACY_POS0 = 9
+    USV_FIELD_LEGACY_POS0 = 9,
+    /* USV_ENV_ASMC_YE_INT_V0 / USV_ENV_PID_V0, float64 [21][N]: the 19 rows of USV_FIELD_LEGACY in float64 (these
+     * envs never round to float32) | ye_int (aux_vars[3]) | ye_last (last[9]) of usv_asmc_ye_int_env.py:247-251;
+     * the last two rows stay 0 for the pid env */
+    USV_FIELD_LEGACY64 = 10
 } UsvField;
 
 #define USV_LEGACY_ROWS 19
+#define USV_LEGACY64_ROWS 21
 #define USV_DYN_ROWS 23
 #define USV_EPI_ROWS 7
 

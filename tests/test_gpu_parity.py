@@ -636,6 +636,129 @@ def test_legacy_host_face_and_ragged(usv):
 
 
 # ------------------------------------------------------------------------------------------
+# the float64 siblings 'usv-asmc-ye-int-v0' / 'usv-pid-v0' (SURVEY 8f rank 3): float64 state and arithmetic end to
+# end, so the state matches the reference to CUDA-vs-numpy libm differences (an ulp of exp / sincos / tanh fed back
+# through the closed loop); the float32 observation the VecEnv hands out is that state rounded once.
+SIBLING_STATE_ATOL = 1e-9
+SIBLING_OBS_ATOL = 1e-6   # float32 rounding of |ye| <= 10, |psi| <= pi
+SIBLINGS = [("usv-asmc-ye-int-v0", "legacy_ye_int_env.npz"), ("usv-pid-v0", "legacy_pid_env.npz")]
+
+
+def _sibling_inject(env, k_env, g, prefix, k):
+    st = env.get_state()
+    col = np.zeros(21)
+    col[0] = g[prefix + "reset_state"][k][5]
+    col[1:4] = g[prefix + "reset_velocity"][k]
+    col[4:7] = g[prefix + "reset_position"][k]
+    aux, last = g[prefix + "reset_aux"][k], g[prefix + "reset_last"][k]
+    col[7:10], col[10:19] = aux[:3], last[:9]
+    col[19] = aux[3] if len(aux) > 3 else 0.0
+    col[20] = last[9] if len(last) > 9 else 0.0
+    st["legacy64"][:, k_env] = col
+    st["target"][:, k_env] = g[prefix + "reset_target"][k]
+    st["steps"][k_env] = 0
+    st["ep_return"][k_env] = 0.0
+    env.set_state(st)
+
+
+@pytest.mark.parametrize("env_id,gname", SIBLINGS)
+@pytest.mark.parametrize("prefix", ["", "L1_"])
+def test_legacy_sibling_golden_replay(usv, env_id, gname, prefix):
+    from test_oracle_golden import legacy_replay
+    g = load_golden(gname)
+    g = {k: g[k] for k in g.keys()}
+    env = usv.UsvGpuVecEnv(3, device=0, seed=0, env_id=env_id, auto_reset=False)
+    assert env.observation_space.shape == (6,) and env.action_space.shape == (1,)
+    env.reset_tensor()
+    worst = dict(obs32=0.0, aux=0.0)
+    t_now = [0]
+
+    def inject(k):
+        for j in range(3):
+            _sibling_inject(env, j, g, prefix, k)
+
+    def step(a):
+        obs, rew, term, trunc = env.step_tensor(torch.full((3, 1), float(a), device=env.device))
+        o, r, d = obs.cpu().numpy(), rew.cpu().numpy(), term.cpu().numpy()
+        assert np.all(o == o[:1]) and np.all(r == r[0]) and not trunc.any()
+        st = env.get_state(["legacy64"])["legacy64"][:, 0]
+        t = t_now[0]
+        t_now[0] += 1
+        worst["obs32"] = max(worst["obs32"], float(np.abs(o[0].astype(np.float64) - g[prefix + "obs"][t]).max()))
+        if prefix == "":  # every internal array is on file for the short rollout
+            aux = np.concatenate([st[7:10], st[19:20]])[:g["aux"].shape[1]]
+            last = np.concatenate([st[10:19], st[20:21]])[:g["last"].shape[1]]
+            worst["aux"] = max(worst["aux"], float(np.abs(aux - g["aux"][t]).max()),
+                               float(np.abs(last - g["last"][t]).max()))
+        # float64 observation entries that are state: u, r (v_ak, ye, psi_ak are outputs only -> checked as float32)
+        ob64 = g[prefix + "obs"][t].copy()
+        ob64[[0, 2]] = st[[1, 3]]
+        return ob64, r[0], d[0], st[4:7].copy(), st[1:4].copy()
+
+    w = legacy_replay(g, prefix, step, inject)
+    print(env_id, prefix, w, worst)
+    assert w["pos"] < SIBLING_STATE_ATOL and w["vel"] < SIBLING_STATE_ATOL and worst["aux"] < SIBLING_STATE_ATOL, (w, worst)
+    assert w["rew"] < 1e-6 and worst["obs32"] < SIBLING_OBS_ATOL, (w, worst)  # reward is handed out as float32
+    env.close()
+
+
+@pytest.mark.parametrize("env_id", ["usv-asmc-ye-int-v0", "usv-pid-v0"])
+def test_legacy_sibling_lockstep_vs_oracle_with_autoreset(usv, env_id):
+    """2048 envs, 3000 steps, actions held for 750 steps so that episodes end (|ye| > 10, x < -10) and the in-kernel
+    Philox reset runs: float32 observations / rewards to rounding, float64 state to 1e-9, flags and episode counters
+    exact (an env is dropped only if the oracle itself sits within 1e-6 of a threshold)."""
+    N, T, HOLD = 2048, 3000, 750
+    env = usv.UsvGpuVecEnv(N, device=0, seed=33, env_id=env_id)
+    ov = uo.OracleLegacyVecEnv(N, seed=33, n_threads=8, env_id=env_id)
+    assert np.array_equal(env.reset_tensor().cpu().numpy(), ov.reset())
+    rng = np.random.default_rng(6)
+    alive = np.ones(N, dtype=bool)
+    n_done, worst_obs, worst_rew = 0, 0.0, 0.0
+    for t in range(T):
+        if t % HOLD == 0:
+            a = rng.uniform(-np.pi / 2, np.pi / 2, N).astype(np.float32)
+        obs, rew, term, trunc = [x.cpu().numpy() for x in env.step_tensor(torch.tensor(a[:, None], device=env.device))]
+        oc, rc, dc = ov.step(a)
+        bad = alive & (term.astype(bool) != dc.astype(bool))
+        for i in np.flatnonzero(bad):
+            tob = ov.terminal_obs[i] if dc[i] else oc[i]
+            assert abs(abs(tob[3]) - 10.0) < 1e-4 or abs(ov.envs["position"][i, 0] + 10.0) < 1e-6, (t, i, tob)
+        alive &= ~bad
+        n_done += int(dc[alive].sum())
+        worst_obs = max(worst_obs, float(np.abs(obs[alive] - oc[alive]).max()))
+        worst_rew = max(worst_rew, float(np.abs(rew[alive] - rc[alive]).max()))
+    st = env.get_state()
+    pos_err = float(np.abs(st["legacy64"][4:7, alive].T - ov.envs["position"][alive]).max())
+    vel_err = float(np.abs(st["legacy64"][1:4, alive].T - ov.envs["velocity"][alive]).max())
+    print(f"{env_id} lock-step: {n_done} episodes ended, worst obs {worst_obs:.3g}, reward {worst_rew:.3g}, "
+          f"final pose {pos_err:.3g}, velocity {vel_err:.3g}, dropped {N - int(alive.sum())}")
+    assert n_done > N // 16, n_done
+    assert alive.sum() >= N - 2, int(alive.sum())
+    assert worst_obs < SIBLING_OBS_ATOL and worst_rew < 1e-6, (worst_obs, worst_rew)
+    assert pos_err < SIBLING_STATE_ATOL and vel_err < SIBLING_STATE_ATOL, (pos_err, vel_err)
+    assert np.array_equal(st["steps"][alive], ov.envs["steps"][alive])
+    assert np.array_equal(st["episode"][alive], ov.envs["episode"][alive])
+    stats = env.episode_stats()
+    assert stats["episodes"] >= n_done and stats["nonfinite"] == 0 and stats["env_steps"] == N * T
+    env.close()
+
+
+def test_legacy_sibling_host_face(usv):
+    for env_id in ("usv-asmc-ye-int-v0", "usv-pid-v0"):
+        env = usv.UsvGpuVecEnv(130, device=0, seed=4, env_id=env_id, max_episode_steps=7)
+        ov = uo.OracleLegacyVecEnv(130, seed=4, env_id=env_id)
+        assert np.array_equal(env.reset(), ov.reset())
+        for t in range(15):
+            a = action_stream(130, seed=t)[:, 1] * np.float32(np.pi / 2)
+            obs, rew, dones, infos = env.step(a)
+            assert obs.shape == (130, 6) and obs.dtype == np.float32
+            if t % 7 == 6:
+                assert dones.all() and infos[3]["TimeLimit.truncated"] and infos[3]["episode"]["l"] == 7
+        assert len(env.get_attr("position", [0, 1])) == 2
+        env.close()
+
+
+# ------------------------------------------------------------------------------------------
 # on-device VecFrameStack (train_test/sb3_train_vec.py:70), SURVEY 8f rank 1
 # ------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("env_id,n_stack", [("usv-asmc-simple", 5), ("usv-simple", 5), ("usv-asmc-v0", 3)])
