@@ -15,7 +15,7 @@ _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
-HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
+HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_render.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
                                              "usv_sensor.cuh", "usv_kernels.cuh", "usv_math.cuh")] + \
           [os.path.join(_ROOT, "include", "usvgpu.h")]
 
@@ -125,6 +125,7 @@ _SIGNATURES = {
                                       C.c_int32, C.c_void_p, C.c_void_p]),
     "usvgpu_sensors": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_frame_stack_push": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 7),
+    "usvgpu_render": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "usvgpu_gae": (C.c_int, [C.c_int, C.c_int32, C.c_int64] + [C.c_void_p] * 5 + [C.c_float, C.c_float] + [C.c_void_p] * 3),
     "usvgpu_math_probe": (C.c_int, [C.c_int, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_fp64_peak": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.c_void_p]),

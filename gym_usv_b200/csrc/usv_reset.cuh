@@ -126,6 +126,8 @@ __device__ void reset_env(const StatePtrs& s, long long i, float* hdr) {
         if (j + 1 < kept) row[2 * MAX_OBST + j + 1] = (ObT)lerp_u(0.15, 0.5, b);
     }
     *nobs_of(s, i) = kept;
+    target0_of(s, i)[0] = (float)q.tx;
+    target0_of(s, i)[1] = (float)q.ty;
 #pragma unroll
     for (int k = 0; k < N_DYN; ++k) {  // fresh UsvAsmc(), progress = 0
         if (s.kinematic && (k == D_LA0 || k == D_LA2)) continue;
@@ -193,6 +195,8 @@ __device__ float reset_env_warp(const StatePtrs& s, long long i, int lane) {
         s.steps[i] = 0;
         s.ep_return[i] = 0.0;
         *nobs_of(s, i) = kept;
+        target0_of(s, i)[0] = (float)q.tx;
+        target0_of(s, i)[1] = (float)q.ty;
     }
     if (lane < N_DYN && !(s.kinematic && (lane == D_LA0 || lane == D_LA2))) s.dyn[(long long)lane * n + i] = reset_dyn_row(q, lane);
     if (lane < N_EPI) s.epi[(long long)lane * n + i] = reset_epi_row(q, lane);

@@ -69,7 +69,7 @@ struct StatePtrs {
     double* epi;        // [N_EPI][n]
     // Sensor-input rows [n][sin_row bytes], 128-byte aligned: everything sensor_kernel needs for one env in one
     // contiguous block -- obstacle table x[32] y[32] radius[32] (float or double) | Hand 48 B | observation header row
-    // 64 B | n_obs int32 | 12 B pad.  512 B per env with a float32 table (one 16-byte cp.async per lane), 896 B with
+    // 64 B | n_obs int32 | reset target 2 x float32 | 4 B pad.  512 B per env with a float32 table (one 16-byte cp.async per lane), 896 B with
     // float64.  The dynamics kernel writes Hand + header (one 128-byte line), the reset writes table + n_obs.
     char* sin;
     int sin_row;        // bytes per env row
@@ -92,7 +92,7 @@ struct StepFlags {
                        // copy-out of one chunk overlaps the kernels of the next
 };
 
-constexpr int SIN_TAIL_BYTES = 128;  // Hand (48) + header row (64) + n_obs (4) + pad (12)
+constexpr int SIN_TAIL_BYTES = 128;  // Hand (48) + header row (64) + n_obs (4) + reset target x, y float32 (8) + pad (4)
 template <typename ObT>
 __device__ __forceinline__ ObT* obst_row(const StatePtrs& s, long long i) {
     return reinterpret_cast<ObT*>(s.sin + i * (long long)(sizeof(ObT) * OBST_ROW + SIN_TAIL_BYTES));
@@ -104,6 +104,11 @@ __device__ __forceinline__ float* hdr_of(const StatePtrs& s, long long i) {
 }
 __device__ __forceinline__ int* nobs_of(const StatePtrs& s, long long i) {
     return reinterpret_cast<int*>(sin_tail(s, i) + sizeof(Hand) + HDR_PAD * sizeof(float));
+}
+
+// the random target_position a reset draws (simple_env.py:245); only the renderer reads it, for envs at step 0
+__device__ __forceinline__ float* target0_of(const StatePtrs& s, long long i) {
+    return reinterpret_cast<float*>(sin_tail(s, i) + sizeof(Hand) + HDR_PAD * sizeof(float) + sizeof(int));
 }
 
 }  // namespace usv

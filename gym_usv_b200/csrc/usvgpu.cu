@@ -19,6 +19,7 @@
 #include "../../include/usvgpu.h"
 #include "usv_kernels.cuh"
 #include "usv_legacy.cuh"
+#include "usv_render.cuh"
 
 // =================================================================================================
 // Host side: handle + C ABI
@@ -678,6 +679,23 @@ int usvgpu_gae(int device, int32_t n_steps, int64_t n, const float* rewards, con
                                                                            last_values, last_dones, gamma, gae_lambda,
                                                                            advantages, returns);
     CU_TRY(nullptr, cudaGetLastError());
+    return USV_OK;
+}
+
+int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const float* obs, int32_t size,
+                  uint8_t* frames, void* stream) {
+    if (!h) return fail(nullptr, USV_ERR_INVALID, "handle is NULL");
+    if (h->legacy) return fail(h, USV_ERR_INVALID, "render: the path-following envs have no SimpleEnvVisualizer");
+    if (!obs || !frames || n_frames <= 0 || n_frames > 65535 || size < 1 || size > 8192)
+        return fail(h, USV_ERR_INVALID, "bad render arguments (obs / frames NULL, n_frames not in 1..65535, size not in 1..8192)");
+    if (!index && n_frames > h->sp.n) return fail(h, USV_ERR_INVALID, "render: more frames than envs");
+    if (((uintptr_t)frames & 3) || ((uintptr_t)obs & 3)) return fail(h, USV_ERR_INVALID, "render: frames / obs misaligned");
+    CU_TRY(h, cudaSetDevice(h->device));
+    const int tiles = (size + RND_TILE - 1) / RND_TILE;
+    render_kernel<<<dim3((unsigned)(tiles * tiles), (unsigned)n_frames), RND_THREADS, 0, (cudaStream_t)stream>>>(
+        h->sp, reinterpret_cast<const long long*>(index), obs, OBS_DIM, h->cfg.obstacles_f32, size, frames);
+    CU_TRY(h, cudaGetLastError());
+    h->launches += 1;
     return USV_OK;
 }
 

@@ -78,6 +78,8 @@ class UsvGpuVecEnv:
         self.observation_space = spaces.legacy_observation_space() if self.legacy else spaces.simple_observation_space()
         self.action_space = spaces.legacy_action_space() if self.legacy else spaces.simple_action_space()
         self.render_mode = render_mode
+        self.render_envs = 16   # how many envs get_images() / render() draw
+        self.render_size = 512  # SimpleEnvVisualizer(window_size=512), simple_env_visualizer.py:9
         self.info_mode = info_mode
         if max_episode_steps is None:
             max_episode_steps = MAX_EPISODE_STEPS[env_id]
@@ -308,11 +310,46 @@ class UsvGpuVecEnv:
     def env_is_wrapped(self, wrapper_class, indices=None) -> List[bool]:
         return [False] * len(list(self._indices(indices)))
 
-    def render(self, mode: Optional[str] = None):
-        return None  # no graphics stack on this box; a CUDA rasteriser is SURVEY 8f rank 4
+    # ------------------------------------------------------------------ rgb_array frames
+    def render_tensor(self, indices=None, size: Optional[int] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """UsvSimpleEnv.render() with render_mode "rgb_array" (simple_env.py:117-131 -> simple_env_visualizer.py:17-114)
+        for the envs in `indices` (default: the first ``render_envs``): uint8 CUDA tensor [K, size, size, 3] drawn by
+        usvgpu_render from the device state and the last observation.  No window system involved."""
+        if self.legacy:
+            raise NotImplementedError(f"{self.env_id} has no SimpleEnvVisualizer; its pyglet viewer is unavailable on this box")
+        size = int(size or self.render_size)
+        if indices is None:
+            idx, k = None, min(self.num_envs, self.render_envs)
+        else:
+            idx = torch.as_tensor(indices, dtype=torch.int64, device=self.device).reshape(-1).contiguous()
+            k = int(idx.numel())
+            if k and (int(idx.min()) < 0 or int(idx.max()) >= self.num_envs):
+                raise IndexError("render_tensor: env index out of range")
+        if out is None:
+            out = torch.empty((k, size, size, 3), dtype=torch.uint8, device=self.device)
+        assert out.is_contiguous() and out.dtype == torch.uint8 and tuple(out.shape) == (k, size, size, 3)
+        self._check(self._lib.usvgpu_render(self._h, C.c_void_p(idx.data_ptr()) if idx is not None else None, k,
+                                            C.c_void_p(self.obs.data_ptr()), int(size), C.c_void_p(out.data_ptr()),
+                                            self._stream()))
+        return out
 
     def get_images(self):
-        return [None] * self.num_envs
+        """SB3 VecEnv.get_images(): frames of the first ``render_envs`` envs (tiling all N of a GPU-sized batch into
+        one picture is of no use; set ``render_envs`` to change it)."""
+        return list(self.render_tensor().cpu().numpy())
+
+    def render(self, mode: Optional[str] = None):
+        """SB3 VecEnv.render(): the get_images() frames tiled into one rgb_array (tile_images layout: as square as
+        possible).  "human" mode needs a window system: unavailable on this box."""
+        if (mode or self.render_mode) != "rgb_array":
+            return None
+        imgs = self.render_tensor()
+        k, hh, ww, _ = imgs.shape
+        rows = int(np.ceil(np.sqrt(k)))
+        cols = int(np.ceil(k / rows))
+        canvas = torch.zeros((rows * cols, hh, ww, 3), dtype=torch.uint8, device=self.device)
+        canvas[:k] = imgs
+        return canvas.reshape(rows, cols, hh, ww, 3).permute(0, 2, 1, 3, 4).reshape(rows * hh, cols * ww, 3).cpu().numpy()
 
     # ------------------------------------------------------------------ state access (checkpoint / parity)
     # name -> (field id, dtype, leading dims before N, trailing dims after N)

@@ -233,6 +233,19 @@ int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_st
                             const float* obs, const uint8_t* terminated, const uint8_t* truncated,
                             const float* terminal_obs, float* terminal_stack, void* stream);
 
+/* Replaces UsvSimpleEnv.render() / _render_frame() with render_mode == "rgb_array" (gym_usv/envs/simple_env.py:117-131)
+ * -> SimpleEnvVisualizer.render_frame (gym_usv/envs/simple_env_visualizer.py:17-114), what SB3's VecVideoRecorder
+ * records (train_test/sb3_train_vec.py:69): the draw list of :34-100 (target, 128 sensor rays, agent, "front" marker,
+ * obstacles, path line) rasterised by a CUDA kernel into frames uint8 [n_frames][size][size][3] (row = canvas y,
+ * column = canvas x, RGB: the np.transpose of :112-114), DEVICE memory, 4-byte aligned.  No window, no pygame: the
+ * reference's human mode (:24-31, :102-110) is unavailable on this box.
+ * index int64 [n_frames] DEVICE (env indices of this shard, each in [0, N)) or NULL for envs 0 .. n_frames - 1;
+ * obs float32 [N][143] DEVICE: the observation the last step / reset returned (the ray lengths are read from its
+ * columns 15..142, like self.sensor_data).  size: the reference's window_size (512).
+ * USV_ENV_ASMC_SIMPLE and USV_ENV_SIMPLE only.  Coverage rules: gym_usv_b200/csrc/usv_render.cuh. */
+int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const float* obs, int32_t size,
+                  uint8_t* frames, void* stream);
+
 /* Replaces stable_baselines3 RolloutBuffer.compute_returns_and_advantage (what PPO.learn of
  * train_test/config.py:3-15 runs after every n_steps = 2048 rollout) on device-resident buffers: rewards, values,
  * episode_starts, advantages, returns float32 [n_steps][N]; last_values float32 [N]; last_dones uint8 [N]. */

@@ -144,6 +144,13 @@ void usv_oracle_legacy_vec_step(UsvOracleLegacy* envs, int64_t n, const float* a
                                 uint8_t* done, float* terminal_obs, int auto_reset, uint64_t seed,
                                 int64_t global_offset, int n_threads);
 
+/* ---- rgb_array frame of SimpleEnvVisualizer.render_frame (simple_env_visualizer.py:17-114), usv_oracle_render.c;
+ * PARITY UNPINNED against pygame's pixels (pygame absent): draw list from the reference, coverage rules ours ---- */
+void usv_oracle_render_frame(const double position[3], const double target[2], const double* sensor_distance,
+                             int sensor_count, int n_obs, const double* obs_x, const double* obs_y,
+                             const double* obs_r, const double path_start[2], const double path_end[2],
+                             double env_hi, int size, uint8_t* frame);
+
 /* RNG primitives exposed for tests (Philox4x32-10) */
 void usv_oracle_philox(uint64_t seed, uint64_t global_id, uint32_t episode, uint32_t block, uint32_t out[4]);
 

@@ -92,7 +92,7 @@ class Config(C.Structure):
 
 def build(force: bool = False) -> str:
     """Compile the oracle with gcc (make -C oracle).  Returns the .so path."""
-    srcs = [os.path.join(_HERE, f) for f in ("usv_oracle.c", "usv_oracle_legacy.c", "usv_oracle_legacy_step.inc",
+    srcs = [os.path.join(_HERE, f) for f in ("usv_oracle.c", "usv_oracle_legacy.c", "usv_oracle_legacy_step.inc", "usv_oracle_render.c",
                                              "usv_oracle.h")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs if os.path.exists(s)
@@ -140,6 +140,8 @@ def lib():
         for name in ("usv_oracle_legacy_init", "usv_oracle_legacy_reset_from_draws", "usv_oracle_legacy_reset",
                      "usv_oracle_legacy_step", "usv_oracle_legacy_vec_reset", "usv_oracle_legacy_vec_step"):
             getattr(L, name).restype = None
+        L.usv_oracle_render_frame.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, dbl, i32, vp]
+        L.usv_oracle_render_frame.restype = None
         assert L.usv_oracle_sizeof_legacy() == LEGACY_DTYPE.itemsize
         assert L.usv_oracle_sizeof_env() == ENV_DTYPE.itemsize, (L.usv_oracle_sizeof_env(), ENV_DTYPE.itemsize)
         assert L.usv_oracle_sizeof_asmc() == ASMC_DTYPE.itemsize
@@ -261,6 +263,18 @@ class OracleLegacyVecEnv:
                                          _p(self.terminal_obs), int(self.auto_reset), self.seed, self.global_offset,
                                          self.n_threads)
         return self.obs, self.reward, self.done
+
+
+def render_frame(position, target, sensor_distance, obs_x, obs_y, obs_r, path_start, path_end, env_hi=20.0, size=512):
+    """SimpleEnvVisualizer.render_frame (simple_env_visualizer.py:17-114) -> uint8 [size, size, 3].  Parity unpinned
+    against pygame's pixels (see usv_oracle_render.c)."""
+    f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64).reshape(-1)  # noqa: E731
+    position, target, d = f64(position), f64(target), f64(sensor_distance)
+    ox, oy, orad, ps, pe = f64(obs_x), f64(obs_y), f64(obs_r), f64(path_start), f64(path_end)
+    frame = np.zeros((size, size, 3), dtype=np.uint8)
+    lib().usv_oracle_render_frame(_p(position), _p(target), _p(d), len(d), len(ox), _p(ox), _p(oy), _p(orad), _p(ps),
+                                  _p(pe), float(env_hi), int(size), _p(frame))
+    return frame
 
 
 def philox(seed, gid, episode, block):
