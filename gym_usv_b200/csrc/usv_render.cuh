@@ -5,7 +5,7 @@
 //
 // The reference draws with pygame's software renderer, which is absent here (and there is no graphics stack on
 // either box): windows / blits are left out, and the exact pixel coverage of pygame.draw cannot be pinned.  The
-// coverage rules are therefore stated here and restated independently in oracle/usv_oracle_render.c
+// coverage rules are therefore stated here and restated independently by the test-side CPU checker (under oracle/)
 // (painter's loop + incremental Bresenham there, per-pixel closed forms here); "parity unpinned" against pygame.
 //
 // Draw list, in painter's order (a later primitive overwrites an earlier one), scale = size / env_bounds[1]:
