@@ -9,6 +9,7 @@ The arithmetic lives in libusvgpu.so (csrc/, hand-written sm_100a CUDA behind in
 from ._native import UsvError, build  # noqa: F401
 from .vec_env import UsvGpuVecEnv  # noqa: F401
 from .frame_stack import UsvGpuVecFrameStack  # noqa: F401
+from .replay import DeviceReplayBuffer, collect_transitions  # noqa: F401
 from .functional import asmc_compute, fp64_peak, math_probe, sensor_distances  # noqa: F401
 
-__all__ = ["UsvGpuVecEnv", "UsvGpuVecFrameStack", "UsvError", "build", "asmc_compute", "sensor_distances", "math_probe", "fp64_peak"]
+__all__ = ["UsvGpuVecEnv", "UsvGpuVecFrameStack", "DeviceReplayBuffer", "collect_transitions", "UsvError", "build", "asmc_compute", "sensor_distances", "math_probe", "fp64_peak"]

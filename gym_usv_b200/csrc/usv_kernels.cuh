@@ -467,6 +467,75 @@ gae_kernel(int n_steps, long long n, const float* __restrict__ rewards, const fl
 }
 
 // ---------------------------------------------------------------------------------------------
+// stable_baselines3 ReplayBuffer on the device (train_test/sb3_train_vec.py:72 trains SAC with config_sac,
+// train_test/config.py:17-37: buffer_size 400 000, batch_size 256): add() of one VecEnv step and the gather of
+// sample().  Buffers are [capacity][N][...] like SB3's; a warp moves one env's / one sample's rows.
+// ---------------------------------------------------------------------------------------------
+struct ReplayPtrs {
+    float* obs;          // [capacity][n][obs_dim]
+    float* next_obs;     // [capacity][n][obs_dim]
+    float* actions;      // [capacity][n][act_dim]
+    float* rewards;      // [capacity][n]
+    uint8_t* dones;      // [capacity][n]
+    uint8_t* timeouts;   // [capacity][n]   infos[i]["TimeLimit.truncated"]
+};
+
+__device__ __forceinline__ void warp_copy_row(float* __restrict__ dst, const float* __restrict__ src, int len, int lane) {
+    if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
+        const int n4 = len >> 2;
+        for (int c = lane; c < n4; c += 32) reinterpret_cast<float4*>(dst)[c] = reinterpret_cast<const float4*>(src)[c];
+        for (int c = (n4 << 2) + lane; c < len; c += 32) dst[c] = src[c];
+    } else {  // rows of 143 / 715 floats start on 4-byte boundaries only: 128 B per warp instruction, 4 in flight
+#pragma unroll 4
+        for (int c = lane; c < len; c += 32) dst[c] = src[c];
+    }
+}
+
+// OffPolicyAlgorithm._store_transition + ReplayBuffer.add: slot `pos` of every env; the next observation of a
+// finished env is its terminal observation (the VecEnv has already reset it), timeouts = truncated & ~terminated.
+__global__ void __launch_bounds__(256)
+replay_add_kernel(ReplayPtrs b, long long n, int obs_dim, int act_dim, long long pos, const float* __restrict__ obs,
+                  long long obs_stride, const float* __restrict__ next_obs, long long next_stride,
+                  const float* __restrict__ terminal_obs, long long term_stride, const float* __restrict__ actions,
+                  const float* __restrict__ rewards, const uint8_t* __restrict__ terminated,
+                  const uint8_t* __restrict__ truncated) {
+    const int lane = threadIdx.x & 31;
+    const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (i >= n) return;
+    const long long slot = pos * n + i;
+    if (obs) warp_copy_row(b.obs + slot * obs_dim, obs + i * obs_stride, obs_dim, lane);
+    if (!next_obs) return;  // first half of a split add: only the observation the action is computed from
+    const bool term = terminated[i] != 0, trunc = truncated[i] != 0;
+    const float* nx = ((term || trunc) && terminal_obs) ? terminal_obs + i * term_stride : next_obs + i * next_stride;
+    warp_copy_row(b.next_obs + slot * obs_dim, nx, obs_dim, lane);
+    if (lane < act_dim) b.actions[slot * act_dim + lane] = actions[i * act_dim + lane];
+    if (lane == 0) {
+        b.rewards[slot] = rewards[i];
+        b.dones[slot] = (term || trunc) ? 1 : 0;
+        b.timeouts[slot] = (trunc && !term) ? 1 : 0;
+    }
+}
+
+// ReplayBuffer._get_samples: sample k is (batch_inds[k], env_inds[k]); dones come out as dones * (1 - timeouts)
+__global__ void __launch_bounds__(256)
+replay_sample_kernel(ReplayPtrs b, long long n, int obs_dim, int act_dim, long long batch,
+                     const long long* __restrict__ batch_inds, const long long* __restrict__ env_inds,
+                     float* __restrict__ out_obs, float* __restrict__ out_next_obs, float* __restrict__ out_actions,
+                     float* __restrict__ out_rewards, float* __restrict__ out_dones) {
+    const int lane = threadIdx.x & 31;
+    const long long k = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (k >= batch) return;
+    const long long slot = batch_inds[k] * n + env_inds[k];
+    warp_copy_row(out_obs + k * obs_dim, b.obs + slot * obs_dim, obs_dim, lane);
+    warp_copy_row(out_next_obs + k * obs_dim, b.next_obs + slot * obs_dim, obs_dim, lane);
+    if (lane < act_dim) out_actions[k * act_dim + lane] = b.actions[slot * act_dim + lane];
+    if (lane == 0) {
+        out_rewards[k] = b.rewards[slot];
+        out_dones[k] = (float)b.dones[slot] * (1.0f - (float)b.timeouts[slot]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Unit-parity kernels
 // ---------------------------------------------------------------------------------------------
 template <bool PERTURB>

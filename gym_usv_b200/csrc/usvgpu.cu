@@ -699,6 +699,52 @@ int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const
     return USV_OK;
 }
 
+int usvgpu_replay_add(int device, int64_t n, int32_t obs_dim, int32_t act_dim, int64_t capacity, int64_t pos,
+                      const float* obs, int64_t obs_stride, const float* next_obs, int64_t next_stride,
+                      const float* terminal_obs, int64_t terminal_stride, const float* actions, const float* rewards,
+                      const uint8_t* terminated, const uint8_t* truncated, float* buf_obs, float* buf_next_obs,
+                      float* buf_actions, float* buf_rewards, uint8_t* buf_dones, uint8_t* buf_timeouts, void* stream) {
+    if ((!obs && !next_obs) || !buf_obs || !buf_next_obs || !buf_actions || !buf_rewards || !buf_dones || !buf_timeouts)
+        return fail(nullptr, USV_ERR_INVALID, "replay_add: NULL argument");
+    if (next_obs && (!actions || !rewards || !terminated || !truncated))
+        return fail(nullptr, USV_ERR_INVALID, "replay_add: NULL argument");
+    if (n <= 0 || obs_dim <= 0 || act_dim <= 0 || act_dim > 32 || capacity <= 0 || pos < 0 || pos >= capacity ||
+        (obs && obs_stride < obs_dim) || (next_obs && next_stride < obs_dim) || (terminal_obs && terminal_stride < obs_dim))
+        return fail(nullptr, USV_ERR_INVALID, "replay_add: bad sizes (act_dim <= 32, 0 <= pos < capacity, strides >= obs_dim)");
+    int rc = check_device(nullptr, device);
+    if (rc) return rc;
+    CU_TRY(nullptr, cudaSetDevice(device));
+    const ReplayPtrs b = {buf_obs, buf_next_obs, buf_actions, buf_rewards, buf_dones, buf_timeouts};
+    replay_add_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        b, n, obs_dim, act_dim, pos, obs, obs_stride, next_obs, next_stride, terminal_obs, terminal_stride, actions,
+        rewards, terminated, truncated);
+    CU_TRY(nullptr, cudaGetLastError());
+    return USV_OK;
+}
+
+int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim, int64_t batch,
+                         const int64_t* batch_inds, const int64_t* env_inds, const float* buf_obs,
+                         const float* buf_next_obs, const float* buf_actions, const float* buf_rewards,
+                         const uint8_t* buf_dones, const uint8_t* buf_timeouts, float* out_obs, float* out_next_obs,
+                         float* out_actions, float* out_rewards, float* out_dones, void* stream) {
+    if (!batch_inds || !env_inds || !buf_obs || !buf_next_obs || !buf_actions || !buf_rewards || !buf_dones ||
+        !buf_timeouts || !out_obs || !out_next_obs || !out_actions || !out_rewards || !out_dones)
+        return fail(nullptr, USV_ERR_INVALID, "replay_sample: NULL argument");
+    if (n <= 0 || obs_dim <= 0 || act_dim <= 0 || act_dim > 32 || batch <= 0)
+        return fail(nullptr, USV_ERR_INVALID, "replay_sample: bad sizes");
+    int rc = check_device(nullptr, device);
+    if (rc) return rc;
+    CU_TRY(nullptr, cudaSetDevice(device));
+    const ReplayPtrs b = {const_cast<float*>(buf_obs), const_cast<float*>(buf_next_obs), const_cast<float*>(buf_actions),
+                          const_cast<float*>(buf_rewards), const_cast<uint8_t*>(buf_dones),
+                          const_cast<uint8_t*>(buf_timeouts)};
+    replay_sample_kernel<<<(unsigned)((batch * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        b, n, obs_dim, act_dim, batch, reinterpret_cast<const long long*>(batch_inds),
+        reinterpret_cast<const long long*>(env_inds), out_obs, out_next_obs, out_actions, out_rewards, out_dones);
+    CU_TRY(nullptr, cudaGetLastError());
+    return USV_OK;
+}
+
 int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, double* out, void* stream) {
     if (!in || !out || n <= 0 || which < 0 || which > 3) return fail(nullptr, USV_ERR_INVALID, "bad math_probe arguments");
     int rc = check_device(nullptr, device);

@@ -253,6 +253,33 @@ int usvgpu_gae(int device, int32_t n_steps, int64_t n, const float* rewards, con
                const float* episode_starts, const float* last_values, const uint8_t* last_dones, float gamma,
                float gae_lambda, float* advantages, float* returns, void* stream);
 
+/* Replaces stable_baselines3 OffPolicyAlgorithm._store_transition + ReplayBuffer.add for SAC
+ * (train_test/sb3_train_vec.py:72 with config_sac, train_test/config.py:17-37: buffer_size 400 000) on device-resident
+ * buffers laid out like SB3's: buf_obs / buf_next_obs float32 [capacity][N][obs_dim], buf_actions
+ * [capacity][N][act_dim], buf_rewards [capacity][N], buf_dones / buf_timeouts uint8 [capacity][N].  Writes slot `pos`
+ * of every env: obs (the observation the action was computed from), the next observation -- terminal_obs[i] for envs
+ * with terminated | truncated set, as the VecEnv has already reset them (terminal_obs may be NULL: next_obs is stored
+ * as is) --, the action, the reward, dones = terminated | truncated, timeouts = truncated & ~terminated
+ * (infos[i]["TimeLimit.truncated"]).  obs / next_obs / terminal_obs are [N] rows with the given row strides in
+ * elements (a UsvGpuVecFrameStack view has row stride 2 * n_stack * obs_dim).  All pointers DEVICE.
+ * Split form for envs that overwrite their observation tensor in place: a first call with next_obs == NULL stores
+ * only obs (before env.step), a second call with obs == NULL stores everything else (after it). */
+int usvgpu_replay_add(int device, int64_t n, int32_t obs_dim, int32_t act_dim, int64_t capacity, int64_t pos,
+                      const float* obs, int64_t obs_stride, const float* next_obs, int64_t next_stride,
+                      const float* terminal_obs, int64_t terminal_stride, const float* actions, const float* rewards,
+                      const uint8_t* terminated, const uint8_t* truncated, float* buf_obs, float* buf_next_obs,
+                      float* buf_actions, float* buf_rewards, uint8_t* buf_dones, uint8_t* buf_timeouts, void* stream);
+
+/* Replaces ReplayBuffer._get_samples (what SAC.train draws gradient_steps = 8 times per train_freq = 8 steps,
+ * batch_size 256: train_test/config.py:21-25): sample k = (batch_inds[k], env_inds[k]), int64 DEVICE arrays drawn by
+ * the caller (SB3: np.random.randint); out_obs / out_next_obs float32 [batch][obs_dim], out_actions [batch][act_dim],
+ * out_rewards [batch], out_dones [batch] = dones * (1 - timeouts). */
+int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim, int64_t batch,
+                         const int64_t* batch_inds, const int64_t* env_inds, const float* buf_obs,
+                         const float* buf_next_obs, const float* buf_actions, const float* buf_rewards,
+                         const uint8_t* buf_dones, const uint8_t* buf_timeouts, float* out_obs, float* out_next_obs,
+                         float* out_actions, float* out_rewards, float* out_dones, void* stream);
+
 /* Device-math probe (test / measurement surface, no reference counterpart): evaluates one of the float64
  * routines of csrc/usv_math.cuh that replace libm calls of the reference (np.sqrt, '/', np.math.asin at
  * usv_asmc.py:72,103,150; np.cos / np.sin at :179-181) on n inputs.  which: 0 sqrt_k(in[i]) | 1 div_k(in[i],
