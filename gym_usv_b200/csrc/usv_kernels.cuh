@@ -382,6 +382,27 @@ __global__ void reset_kernel(StatePtrs s, const uint8_t* __restrict__ mask, floa
     }
 }
 
+// A warp copies one row.  Rows of 143 / 715 floats start on 4-byte boundaries only, so the unit is a 4-byte element
+// (128 B per warp instruction); what matters is how many loads a warp has in flight: a plain `dst[c] = src[c]` loop
+// issues load, dependent store, load, ... -- one outstanding 128 B request per warp (measured: 2.7 TB/s for the
+// replay add).  Here 8 loads are issued before the first store.
+__device__ __forceinline__ void warp_copy_row(float* __restrict__ dst, const float* __restrict__ src, int len, int lane) {
+    constexpr int B = 8;
+    for (int c0 = 0; c0 < len; c0 += 32 * B) {
+        float v[B];
+#pragma unroll
+        for (int k = 0; k < B; ++k) {
+            const int c = c0 + 32 * k + lane;
+            v[k] = (c < len) ? __ldg(src + c) : 0.0f;
+        }
+#pragma unroll
+        for (int k = 0; k < B; ++k) {
+            const int c = c0 + 32 * k + lane;
+            if (c < len) dst[c] = v[k];
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // rows[k][:] = src[index[k]][:] for the host-buffer face (terminal observations of the envs that finished this step):
 // one warp per row, 8 rows per CTA
@@ -394,7 +415,7 @@ gather_rows_kernel(const float* __restrict__ src, const double2* __restrict__ ep
     const int lane = threadIdx.x & 31;
     const long long i = index[k];
     if (i < 0 || i >= n) return;
-    for (int c = lane; c < row_len; c += 32) rows[k * row_len + c] = src[i * row_len + c];
+    warp_copy_row(rows + k * row_len, src + i * row_len, row_len, lane);
     if (lane == 0) ep_out[k] = ep_done[i];
 }
 
@@ -422,18 +443,29 @@ frame_push_kernel(long long n, int obs_dim, int n_stack, int pos, float* __restr
         if (terminal_stack && terminal_obs) {
             float* ts = terminal_stack + i * n_stack * obs_dim;
             const float* prev = row + (pos + 1) * obs_dim;
-            for (int c = lane; c < (n_stack - 1) * obs_dim; c += 32) ts[c] = prev[c];
-            for (int c = lane; c < obs_dim; c += 32) ts[(n_stack - 1) * obs_dim + c] = terminal_obs[i * obs_dim + c];
+            for (int c = lane; c < (n_stack - 1) * obs_dim; c += 32) ts[c] = prev[c];  // ring is rewritten below: plain loads
+            warp_copy_row(ts + (n_stack - 1) * obs_dim, terminal_obs + i * obs_dim, obs_dim, lane);
         }
         __syncwarp();
         for (int c = lane; c < 2 * n_stack * obs_dim; c += 32) row[c] = 0.0f;
         __syncwarp();
     }
     const float* o = obs + i * obs_dim;
-    for (int c = lane; c < obs_dim; c += 32) {
-        const float v = o[c];
-        row[pos * obs_dim + c] = v;
-        row[(pos + n_stack) * obs_dim + c] = v;
+    float v[5];  // obs_dim <= 160 on this path (143 / 6 columns); longer rows take more rounds
+    for (int c0 = 0; c0 < obs_dim; c0 += 160) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const int c = c0 + 32 * k + lane;
+            v[k] = (c < obs_dim) ? __ldg(o + c) : 0.0f;
+        }
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const int c = c0 + 32 * k + lane;
+            if (c < obs_dim) {
+                row[pos * obs_dim + c] = v[k];
+                row[(pos + n_stack) * obs_dim + c] = v[k];
+            }
+        }
     }
 }
 
@@ -479,17 +511,6 @@ struct ReplayPtrs {
     uint8_t* dones;      // [capacity][n]
     uint8_t* timeouts;   // [capacity][n]   infos[i]["TimeLimit.truncated"]
 };
-
-__device__ __forceinline__ void warp_copy_row(float* __restrict__ dst, const float* __restrict__ src, int len, int lane) {
-    if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
-        const int n4 = len >> 2;
-        for (int c = lane; c < n4; c += 32) reinterpret_cast<float4*>(dst)[c] = reinterpret_cast<const float4*>(src)[c];
-        for (int c = (n4 << 2) + lane; c < len; c += 32) dst[c] = src[c];
-    } else {  // rows of 143 / 715 floats start on 4-byte boundaries only: 128 B per warp instruction, 4 in flight
-#pragma unroll 4
-        for (int c = lane; c < len; c += 32) dst[c] = src[c];
-    }
-}
 
 // OffPolicyAlgorithm._store_transition + ReplayBuffer.add: slot `pos` of every env; the next observation of a
 // finished env is its terminal observation (the VecEnv has already reset it), timeouts = truncated & ~terminated.
