@@ -384,8 +384,11 @@ __global__ void legacy_reset_kernel(LegacyPtrs s, const uint8_t* __restrict__ ma
 
 // One VecEnv.step() of N UsvAsmcEnv: thread per env, state columns coalesced (float32 SoA), the float64 pose of a
 // freshly reset env is fetched only by the lanes whose episode is at step 0.  Bound: HBM.
-constexpr int LEG_B = 128;  // 5 CTAs per SM (96 registers): 20 warps per SM hide the HBM latency; 3 CTAs at 138 registers ran 104 us, this 81 us per 1 M envs
-__global__ void __launch_bounds__(LEG_B, 5)
+constexpr int LEG_B = 128;  // occupancy sweep in profiles/r01w_legacy_launch_bounds.txt: 3 CTAs per SM (138 registers) 104 us per 1 M envs, 5 CTAs 80 us, 8 CTAs 67.5 us, 10 CTAs 72 us
+#ifndef LEG_MIN_CTAS
+#define LEG_MIN_CTAS 8  // 64 registers (96 B spill), 32 warps per SM: 67.5 us per 1 M envs; 5 CTAs / 96 registers ran 80 us
+#endif
+__global__ void __launch_bounds__(LEG_B, LEG_MIN_CTAS)
 legacy_step_kernel(LegacyPtrs s, StepFlags fl, const float* __restrict__ actions, float* __restrict__ obs,
                    float* __restrict__ reward, uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated,
                    float* __restrict__ terminal_obs) {
@@ -460,8 +463,11 @@ legacy_step_kernel(LegacyPtrs s, StepFlags fl, const float* __restrict__ actions
 
 // One VecEnv.step() of N UsvAsmcYeIntEnv (V = LEG_YE_INT) or UsvPidEnv (V = LEG_PID): the same thread-per-env
 // shape over the float64 state columns st64 [21][N] (the pid env never touches rows 19, 20).
+#ifndef LEG64_MIN_CTAS
+#define LEG64_MIN_CTAS 5  // 96 registers, no spills: 79 / 75 us per 1 M envs; 3 CTAs (146 / 156 registers) ran 97 / 95 us
+#endif
 template <int V>
-__global__ void __launch_bounds__(LEG_B)
+__global__ void __launch_bounds__(LEG_B, LEG64_MIN_CTAS)
 legacy64_step_kernel(LegacyPtrs s, StepFlags fl, const float* __restrict__ actions, float* __restrict__ obs,
                      float* __restrict__ reward, uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated,
                      float* __restrict__ terminal_obs) {
