@@ -436,6 +436,14 @@ frame_push_kernel(long long n, int obs_dim, int n_stack, int pos, float* __restr
     if (i >= n) return;
     const int lane = threadIdx.x & 31;
     float* row = ring + i * 2 * n_stack * obs_dim;
+    // the new frame's loads go out first, together with the two flag bytes: one round trip to HBM per warp, not two
+    const float* o = obs + i * obs_dim;
+    float v[5];  // obs_dim <= 160 on this path (143 / 6 columns); longer rows take more rounds below
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const int c = 32 * k + lane;
+        v[k] = (c < obs_dim) ? __ldg(o + c) : 0.0f;
+    }
     const bool done = (terminated && terminated[i]) || (truncated && truncated[i]);
     if (done) {
         // previous window = slots pos .. pos + n_stack - 1 (frames t - n_stack .. t - 1); SB3 keeps its last
@@ -450,13 +458,13 @@ frame_push_kernel(long long n, int obs_dim, int n_stack, int pos, float* __restr
         for (int c = lane; c < 2 * n_stack * obs_dim; c += 32) row[c] = 0.0f;
         __syncwarp();
     }
-    const float* o = obs + i * obs_dim;
-    float v[5];  // obs_dim <= 160 on this path (143 / 6 columns); longer rows take more rounds
     for (int c0 = 0; c0 < obs_dim; c0 += 160) {
+        if (c0) {
 #pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            const int c = c0 + 32 * k + lane;
-            v[k] = (c < obs_dim) ? __ldg(o + c) : 0.0f;
+            for (int k = 0; k < 5; ++k) {
+                const int c = c0 + 32 * k + lane;
+                v[k] = (c < obs_dim) ? __ldg(o + c) : 0.0f;
+            }
         }
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
