@@ -10,6 +10,7 @@ from ._native import UsvError, build  # noqa: F401
 from .vec_env import UsvGpuVecEnv  # noqa: F401
 from .frame_stack import UsvGpuVecFrameStack  # noqa: F401
 from .replay import DeviceReplayBuffer, collect_transitions  # noqa: F401
+from .video import UsvGpuVecVideoRecorder, write_apng  # noqa: F401
 from .functional import asmc_compute, fp64_peak, math_probe, sensor_distances  # noqa: F401
 
-__all__ = ["UsvGpuVecEnv", "UsvGpuVecFrameStack", "DeviceReplayBuffer", "collect_transitions", "UsvError", "build", "asmc_compute", "sensor_distances", "math_probe", "fp64_peak"]
+__all__ = ["UsvGpuVecEnv", "UsvGpuVecFrameStack", "DeviceReplayBuffer", "collect_transitions", "UsvGpuVecVideoRecorder", "write_apng", "UsvError", "build", "asmc_compute", "sensor_distances", "math_probe", "fp64_peak"]

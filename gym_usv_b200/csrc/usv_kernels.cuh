@@ -209,7 +209,10 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
 // action drives the kinematic update directly, no controller.  Thread per env, 9 float64 columns in, 9 out, then the
 // same hand-over to sensor_kernel as dynamics_kernel.  HBM-bound.
 // ---------------------------------------------------------------------------------------------
-constexpr int KIN_B = 128;
+#ifndef USV_KIN_B
+#define USV_KIN_B 128
+#endif
+constexpr int KIN_B = USV_KIN_B;
 __global__ void __launch_bounds__(KIN_B)
 kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     const long long n = s.n;

@@ -114,8 +114,10 @@ def collect_transitions(env, actor, buf: DeviceReplayBuffer, last_obs: torch.Ten
     env: UsvGpuVecEnv or UsvGpuVecFrameStack; actor: callable obs -> actions in the action box, or None for the
     uniform warm-up before ``learning_starts`` (SB3 samples the action space).  Returns the new last_obs.
     """
-    venv = getattr(env, "venv", env)
-    stacked = env is not venv
+    venv = env
+    while hasattr(venv, "venv"):  # UsvGpuVecFrameStack / UsvGpuVecVideoRecorder wrappers
+        venv = venv.venv
+    stacked = hasattr(env, "terminal_stack")
     low = torch.as_tensor(venv.action_space.low, device=last_obs.device, dtype=torch.float32)
     high = torch.as_tensor(venv.action_space.high, device=last_obs.device, dtype=torch.float32)
     for _ in range(n_steps):

@@ -95,10 +95,12 @@ def collect_rollouts(env, policy, buf: DeviceRolloutBuffer, last_obs: torch.Tens
     that the env's share of the rollout time can be measured.
     """
     n_steps = buf.rewards.shape[0]
-    venv = getattr(env, "venv", env)
+    venv = env
+    while hasattr(venv, "venv"):  # UsvGpuVecFrameStack / UsvGpuVecVideoRecorder wrappers
+        venv = venv.venv
     low = torch.as_tensor(venv.action_space.low, device=last_obs.device)
     high = torch.as_tensor(venv.action_space.high, device=last_obs.device)
-    stacked = env is not venv
+    stacked = hasattr(env, "terminal_stack")
     values = None
     for t in range(n_steps):
         if step_policy:
