@@ -20,6 +20,9 @@
 
 namespace usv {
 
+#ifndef USV_DYN_SUBSTEPS
+#define USV_DYN_SUBSTEPS 20  // 2 x UsvAsmc.compute; other values only for timing experiments (tools/time_step.py)
+#endif
 constexpr int DYN_B = 32;        // threads (= envs) per CTA of the dynamics kernel: one warp, so that the 2048 warps of a
                                  // 65 536-env shard spread evenly over the 148 SMs (13.8 per SM)
 constexpr int DYN_MIN_CTAS = 16; // all of them resident at once (<= 128 registers): no second, nearly empty wave
@@ -171,7 +174,7 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     double sn, cs;
     sincos(p.psi, &sn, &cs);  // carried through the sub-steps by small rotations (usv_math.cuh)
 #pragma unroll 1
-    for (int k = 0; k < 20; ++k) asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
+    for (int k = 0; k < USV_DYN_SUBSTEPS; ++k) asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
 
     double progress;
     wrapper_tail<false>(s, fl, i, n, p, cs, sn, progress, steps, 0.0, 0.0);

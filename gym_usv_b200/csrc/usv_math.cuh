@@ -57,9 +57,22 @@ __device__ __forceinline__ double sqrt_k(double a, double& half_rinv) {
     half_rinv = h;
     return (a > 0.0) ? g : 0.0;
 }
+// The same without the refinement of h: with h fixed at the seed's 1/(2 sqrt a) (1 + d), |d| ~ 2^-20, one correction
+// g + (a - g^2) h leaves the error -e d - e^2 / (2 sqrt a): 2^-20 -> 2^-40 -> 2^-60, then the rounding of the last
+// fma.  Two FP64 instructions and 16 cycles of dependent latency less than the form above -- the sub-step's critical
+// path runs through two of these.  h20 receives the unrefined h (good to ~2^-20, enough for a correction term).
+__device__ __forceinline__ double sqrt_k20(double a, double& h20) {
+    const double r = rsqrt_seed(a);
+    const double h = 0.5 * r;
+    double g = a * r;
+    g = fma(fma(-g, g, a), h, g);
+    g = fma(fma(-g, g, a), h, g);
+    h20 = h;
+    return (a > 0.0) ? g : 0.0;
+}
 __device__ __forceinline__ double sqrt_k(double a) {
     double h;
-    return sqrt_k(a, h);
+    return sqrt_k20(a, h);
 }
 
 // 1/d for a normal, finite d bounded away from 0 (no special cases)
@@ -71,9 +84,12 @@ __device__ __forceinline__ double rcp_k(double d) {
     e = fma(-d, r, 1.0);
     return fma(r, e, r);
 }
-// n/d with one residual correction (<= 1 ulp)
+// n/d (<= 1 ulp): one Newton step takes the seed to ~2^-40, q = n r is then corrected with its exact residual
+// (n - d q) r, which leaves 2^-80 plus the rounding of the last fma.  (The reciprocal itself is never refined
+// further: three FP64 instructions and 32 cycles of dependent latency less than refining r first.)
 __device__ __forceinline__ double div_k(double n, double d) {
-    const double r = rcp_k(d);
+    double r = rcp_seed(d);
+    r = fma(r, fma(-d, r, 1.0), r);
     const double q = n * r;
     return fma(fma(-d, q, n), r, q);
 }
@@ -87,14 +103,19 @@ __device__ __forceinline__ double asin_k(double x) {
     if (big) {
         z = fma(-0.5, a, 0.5);  // exact for a in [0.5, 1]
         double h;
-        s = sqrt_k(z, h);
+        s = sqrt_k20(z, h);
         corr = fma(-s, s, z) * h;  // sqrt(z) - s, so that s + corr carries the rounding error of s
         if (!(z > 0.0)) corr = 0.0;
     }
+    // degree-12 polynomial by Estrin's scheme: 4 dependent fma levels instead of Horner's 12 (the sub-step's critical
+    // path runs through it); z <= 0.25, so the regrouping costs nothing in accuracy (probe: <= 2 ulp as before)
     const double* c = MATHK.asin_c;
-    double p = c[12];
-#pragma unroll
-    for (int k = 11; k >= 0; --k) p = fma(p, z, c[k]);
+    const double z2 = z * z, z4 = z2 * z2, z8 = z4 * z4;
+    const double a0 = fma(c[1], z, c[0]), a1 = fma(c[3], z, c[2]), a2 = fma(c[5], z, c[4]);
+    const double a3 = fma(c[7], z, c[6]), a4 = fma(c[9], z, c[8]), a5 = fma(c[11], z, c[10]);
+    const double b0 = fma(a1, z2, a0), b1 = fma(a3, z2, a2), b2 = fma(a5, z2, a4);
+    const double d0 = fma(b1, z4, b0), d1 = fma(c[12], z4, b2);
+    const double p = fma(d1, z8, d0);
     const double t = fma(s * z, p, corr);  // asin(s) - s
     double r = s + t;
     if (big) r = (MATHK.pio2_hi - 2.0 * s) - (fma(2.0, t, -MATHK.pio2_lo));

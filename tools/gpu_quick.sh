@@ -1,2 +1,3 @@
-python -m pytest tests/test_video.py tests/test_replay.py -x -q 2>&1 | tail -8
-python -m pytest tests -m gpu -x -q -k "collect" 2>&1 | tail -3
+python tools/time_step.py usv-asmc-simple 65536
+for k in 0 10 40; do USVGPU_LIB=build_variants/libusvgpu_s$k.so python tools/time_step.py usv-asmc-simple 65536 | sed "s/^/SUBSTEPS=$k /"; done
+python tools/time_step.py usv-asmc-simple 262144
