@@ -140,16 +140,19 @@ __device__ __forceinline__ bool rnd_touches_tile(const RenderPrim& p, int tx0, i
     return true;
 }
 
-// grid (tiles_x * tiles_y, K); frames [K][size][size][3] uint8
+// grid (tiles_y * ceil(tiles_x / tpc), K): a CTA builds the frame's draw list once and paints tpc consecutive tiles of
+// one tile row (the host picks tpc: whole rows when there are many frames, single tiles when there are few, so that
+// the grid still fills the machine); frames [K][size][size][3] uint8
 __global__ void __launch_bounds__(RND_THREADS)
 render_kernel(StatePtrs s, const long long* __restrict__ index, const float* __restrict__ obs, int obs_stride,
-              int obstacles_f32, int size, uint8_t* __restrict__ frames) {
+              int obstacles_f32, int size, int tpc, uint8_t* __restrict__ frames) {
     __shared__ PixelPrim prims[RND_MAX_PRIMS];
     __shared__ unsigned binmask[(RND_MAX_PRIMS + 31) / 32];  // bit id set: primitive id touches this tile
     __shared__ unsigned tile[RND_TILE][RND_TILE * 3 / 4];  // 32 rows x 96 bytes
     const int tid = threadIdx.x;
-    const int tiles_x = (size + RND_TILE - 1) / RND_TILE;
-    const int tx0 = (blockIdx.x % tiles_x) * RND_TILE, ty0 = (blockIdx.x / tiles_x) * RND_TILE;
+    const int tiles_x = (size + RND_TILE - 1) / RND_TILE, groups = (tiles_x + tpc - 1) / tpc;
+    const int ty0 = (blockIdx.x / groups) * RND_TILE;
+    const int tx_begin = (blockIdx.x % groups) * tpc * RND_TILE, tx_end = min(size, tx_begin + tpc * RND_TILE);
     const long long f = blockIdx.y;
     const long long i = index ? index[f] : f;
     const long long n = s.n;
@@ -158,12 +161,10 @@ render_kernel(StatePtrs s, const long long* __restrict__ index, const float* __r
     const double psx = s.epi[(long long)E_PSX * n + i], psy = s.epi[(long long)E_PSY * n + i];
     const double pex = s.epi[(long long)E_PEX * n + i], pey = s.epi[(long long)E_PEY * n + i];
     const int nob = *nobs_of(s, i);
-    if (tid < (RND_MAX_PRIMS + 31) / 32) binmask[tid] = 0u;
-    __syncthreads();
     // ---- the draw list, one primitive per thread -------------------------------------------------------------
+    RenderPrim p = {0, 0, 0, -1, 0, 1, 0u, 0};
+    bool valid = tid < RND_MAX_PRIMS;
     if (tid < RND_MAX_PRIMS) {
-        RenderPrim p = {0, 0, 0, -1, 0, 1, 0u, 0};
-        bool valid = true;
         if (tid == 0) {  // target: simple_env.py:139-148 keeps it at path_start + progress (path_end - path_start);
                          // a freshly reset env still has the random target of :245 (kept by the reset in the row's pad)
             double tx, ty;
@@ -217,8 +218,14 @@ render_kernel(StatePtrs s, const long long* __restrict__ index, const float* __r
             p.rgb = 100u;
         }
         prims[tid] = rnd_pixel_form(p);
-        if (valid && rnd_touches_tile(p, tx0, ty0)) atomicOr(&binmask[tid >> 5], 1u << (tid & 31));
     }
+    uint8_t* frame = frames + f * (long long)size * size * 3;
+  for (int tx0 = tx_begin; tx0 < tx_end; tx0 += RND_TILE) {
+    // ---- which primitives touch this tile ---------------------------------------------------------------------
+    __syncthreads();  // the previous tile's mask and staged pixels have been consumed (first round: prims are written)
+    if (tid < (RND_MAX_PRIMS + 31) / 32) binmask[tid] = 0u;
+    __syncthreads();
+    if (valid && rnd_touches_tile(p, tx0, ty0)) atomicOr(&binmask[tid >> 5], 1u << (tid & 31));
     __syncthreads();
     // ---- per pixel: the covering primitive drawn last wins ---------------------------------------------------
     // walk the tile's primitives from the last drawn to the first: the first one that covers the pixel is its colour
@@ -250,7 +257,6 @@ render_kernel(StatePtrs s, const long long* __restrict__ index, const float* __r
     }
     __syncthreads();
     // ---- tile rows out: 96 bytes = 24 words per row, 4-byte aligned whenever the frame row is -------------------
-    uint8_t* frame = frames + f * (long long)size * size * 3;
     const bool words = (size % 4) == 0 && tx0 + RND_TILE <= size;
     if (words) {
         for (int q = tid; q < RND_TILE * 24; q += RND_THREADS) {
@@ -264,6 +270,7 @@ render_kernel(StatePtrs s, const long long* __restrict__ index, const float* __r
             if (ty0 + ly < size && tx0 + bx / 3 < size) frame[((long long)(ty0 + ly) * size + tx0) * 3 + bx] = tb[q];
         }
     }
+  }
 }
 
 }  // namespace usv

@@ -692,8 +692,14 @@ int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const
     if (((uintptr_t)frames & 3) || ((uintptr_t)obs & 3)) return fail(h, USV_ERR_INVALID, "render: frames / obs misaligned");
     CU_TRY(h, cudaSetDevice(h->device));
     const int tiles = (size + RND_TILE - 1) / RND_TILE;
-    render_kernel<<<dim3((unsigned)(tiles * tiles), (unsigned)n_frames), RND_THREADS, 0, (cudaStream_t)stream>>>(
-        h->sp, reinterpret_cast<const long long*>(index), obs, OBS_DIM, h->cfg.obstacles_f32, size, frames);
+    // tiles per CTA: the draw list is built once per CTA, so whole tile rows when the frames alone fill the machine,
+    // shorter runs (down to single tiles) for a handful of frames
+    const long long cta_target = 32LL * h->sm_count;  // tiles differ a lot in cost (all 128 rays meet near the boat): many CTAs per SM even out the tail
+    int tpc = tiles;
+    while (tpc > 1 && n_frames * tiles * ((tiles + tpc - 1) / tpc) < cta_target) tpc = (tpc + 1) / 2;
+    const int groups = (tiles + tpc - 1) / tpc;
+    render_kernel<<<dim3((unsigned)(tiles * groups), (unsigned)n_frames), RND_THREADS, 0, (cudaStream_t)stream>>>(
+        h->sp, reinterpret_cast<const long long*>(index), obs, OBS_DIM, h->cfg.obstacles_f32, size, tpc, frames);
     CU_TRY(h, cudaGetLastError());
     h->launches += 1;
     return USV_OK;

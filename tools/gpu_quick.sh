@@ -1,3 +1,5 @@
-python tools/time_step.py usv-asmc-simple 65536
-for k in 0 10 40; do USVGPU_LIB=build_variants/libusvgpu_s$k.so python tools/time_step.py usv-asmc-simple 65536 | sed "s/^/SUBSTEPS=$k /"; done
-python tools/time_step.py usv-asmc-simple 262144
+mkdir -p gpurun_out
+python -m pytest tests/test_render.py tests/test_video.py -x -q 2>&1 | tail -4
+python tools/bench_render.py 2>&1 | tail -1 | tee gpurun_out/bench_render.json
+python tools/bench_render.py --frames 64 2>&1 | tail -1 | tee -a gpurun_out/bench_render.json
+python tools/bench_render.py --frames 16 --iters 50 2>&1 | tail -1 | tee -a gpurun_out/bench_render.json
