@@ -53,12 +53,14 @@ def algorithmic_bytes(obstacles: bool, obstacles_f32: bool) -> int:
 HANDOVER = 16 + 8 + 36 + 1
 
 
-def kernel_bytes(obstacles: bool, obstacles_f32: bool) -> dict:
+def kernel_bytes(obstacles: bool, obstacles_f32: bool, kinematic: bool = False) -> dict:
     dyn = (23 * 8 + 7 * 8 + 4 + 2 * 4) + (23 * 8 + 4) + HANDOVER
+    if kinematic:  # 'usv-simple': pose, velocity, last_action (8 columns) + progress move; no controller memory
+        dyn = (9 * 8 + 7 * 8 + 4 + 2 * 4) + (9 * 8 + 4) + HANDOVER
     sens = (2 * 8 + 4 + 8 + HANDOVER) + (143 * 4 + 4 + 2 + 8)
     if obstacles:
         sens += 32 * 3 * (4 if obstacles_f32 else 8)
-    return {"usv::dynamics_kernel": dyn, "usv::sensor_kernel": sens}
+    return {("usv::kinematic_kernel" if kinematic else "usv::dynamics_kernel"): dyn, "usv::sensor_kernel": sens}
 
 
 # 'usv-asmc-v0' (UsvAsmcEnv, one sub-step per env-step): float32 SoA state [19], float64 target (4 of 6 rows read)
@@ -191,7 +193,9 @@ def cpu_oracle_rate(n_envs: int, budget_s: float, threads: int, ignore_obstacles
         ov = uo.OracleLegacyVecEnv(n_envs, seed=seed, n_threads=threads, env_id=env_id)
         acts = rng.uniform(-np.pi / 2, np.pi / 2, (8, n_envs)).astype(np.float32)
     else:
-        ov = uo.OracleVecEnv(n_envs, seed=seed, ignore_obstacles=ignore_obstacles, n_threads=threads)
+        kin = env_id == "usv-simple"
+        ov = uo.OracleVecEnv(n_envs, seed=seed, ignore_obstacles=ignore_obstacles, n_threads=threads, kinematic=kin,
+                             max_episode_steps=500 if kin else 1000)
         acts = rng.uniform([0.2, -1], [1, 1], (8, n_envs, 2)).astype(np.float32)
     ov.reset()
     for k in range(2):
@@ -229,7 +233,9 @@ def run_reference(args, rank, world):
         ov = uo.OracleLegacyVecEnv(n, seed=args.seed, n_threads=threads, env_id=args.env)
         acts = rng.uniform(-np.pi / 2, np.pi / 2, (8, n)).astype(np.float32)
     else:
-        ov = uo.OracleVecEnv(n, seed=args.seed, ignore_obstacles=bool(args.no_obstacles), n_threads=threads)
+        kin = args.env == "usv-simple"
+        ov = uo.OracleVecEnv(n, seed=args.seed, ignore_obstacles=bool(args.no_obstacles), n_threads=threads,
+                             kinematic=kin, max_episode_steps=500 if kin else 1000)
         acts = rng.uniform([0.2, -1], [1, 1], (8, n, 2)).astype(np.float32)
     ov.reset()
     for k in range(args.warmup):
@@ -274,12 +280,15 @@ def workload_config(args, world, reference_sample=None):
         if reference_sample is not None:
             cfg["reference_sample_envs"] = reference_sample
         return cfg
+    kin = args.env == "usv-simple"
     cfg = {
-        "workload": ("usv-asmc-simple (ASMC path following" + (", obstacles ignored" if args.no_obstacles else
-                     " with randomised obstacles + 128-ray range sensors") + f"), {args.envs_per_gpu} envs per GPU, "
-                     "BASELINE.json configs[2]" + ("" if args.envs_per_gpu == 65536 else " (resized)")),
+        "workload": (("usv-simple (kinematic UsvSimpleEnv" if kin else "usv-asmc-simple (ASMC path following") +
+                     (", obstacles ignored" if args.no_obstacles else
+                     " with randomised obstacles + 128-ray range sensors") + f"), {args.envs_per_gpu} envs per GPU, " +
+                     ("the env train_test/sb3_train_vec.py:55 trains on" if kin else "BASELINE.json configs[2]") +
+                     ("" if args.envs_per_gpu == 65536 else " (resized)")),
         "envs_per_gpu": args.envs_per_gpu, "envs_total": args.envs_per_gpu * world,
-        "sub_steps_per_env_step": 20, "max_episode_steps": 1000, "auto_reset": True,
+        "sub_steps_per_env_step": 1 if kin else 20, "max_episode_steps": 500 if kin else 1000, "auto_reset": True,
         "precision": args.precision, "obstacle_table": "f32" if args.obstacles_f32 else "f64",
         "sharding": f"contiguous env-index ranges over {world} GPU(s), no data-path collective",
         "actions": "uniform in the action box, pre-staged on device",
@@ -410,7 +419,9 @@ def run_ours(args, rank, local_rank, world):
         peak, peak_src = measured_peaks()
         abytes = algorithmic_bytes(not args.no_obstacles, bool(args.obstacles_f32))
         step_s = (ms * 1e-3) / args.steps  # rank-0 device time per step (two kernels)
-        kb = kernel_bytes(not args.no_obstacles, bool(args.obstacles_f32))
+        kb = kernel_bytes(not args.no_obstacles, bool(args.obstacles_f32), args.env == "usv-simple")
+        if args.env == "usv-simple":
+            abytes -= 2 * 14 * 8
         if legacy:
             abytes = legacy_bytes(args.env)
             kb = {legacy_kernel(args.env): abytes, "-": 0}
@@ -423,7 +434,7 @@ def run_ours(args, rank, local_rank, world):
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": dtype_of(args),
             "data": "synthetic", "config": workload_config(args, world),
-            "sub_steps_per_sec": value * (1 if legacy else 20),
+            "sub_steps_per_sec": value * (1 if (legacy or args.env == "usv-simple") else 20),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "variants": e2e_variants,
                     "api": "UsvGpuVecEnv.step(np.ndarray) -> np.ndarray obs/rew/dones + infos of done envs "
@@ -466,7 +477,7 @@ def main():
     ap.add_argument("--steps", type=int, default=600)
     ap.add_argument("--warmup", type=int, default=30)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--env", default="usv-asmc-simple", choices=["usv-asmc-simple", "usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0"])
+    ap.add_argument("--env", default="usv-asmc-simple", choices=["usv-asmc-simple", "usv-simple", "usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0"])
     ap.add_argument("--envs-per-gpu", type=int, default=65536)
     ap.add_argument("--batches", type=int, default=3)
     ap.add_argument("--preroll", type=int, default=40, help="untimed steps per batch before warm-up (episode mixing)")

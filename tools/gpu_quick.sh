@@ -1,5 +1,7 @@
 mkdir -p gpurun_out
-python -m pytest tests/test_render.py tests/test_video.py -x -q 2>&1 | tail -4
-python tools/bench_render.py 2>&1 | tail -1 | tee gpurun_out/bench_render.json
-python tools/bench_render.py --frames 64 2>&1 | tail -1 | tee -a gpurun_out/bench_render.json
-python tools/bench_render.py --frames 16 --iters 50 2>&1 | tail -1 | tee -a gpurun_out/bench_render.json
+python bench.py --env usv-simple --steps 300 --warmup 20 --cpu-budget-s 6 > gpurun_out/bench_usv-simple.json 2> gpurun_out/bench_usv-simple.err; tail -c 600 gpurun_out/bench_usv-simple.err; python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench_usv-simple.json').read().strip().splitlines()[-1]); r=d['roofline']
+print('%.4g'%d['value'], 'e2e %.4g'%d['e2e']['value'], r['kernels_us'], 'frac %.3f'%r['frac'], 'cpu %.4g'%d['cpu_baseline']['value'])
+PY
+python bench.py --env usv-simple --impl reference --steps 20 --warmup 3 | cut -c1-200
