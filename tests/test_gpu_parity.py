@@ -743,6 +743,54 @@ def test_legacy_sibling_lockstep_vs_oracle_with_autoreset(usv, env_id):
     env.close()
 
 
+@pytest.mark.parametrize("env_id", ["usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0", "usv-simple"])
+def test_sharding_invariance_other_env_kinds_full_size(usv, env_id):
+    """The size-independent properties of the headline env for the other kinds, at 262 144 envs: a run is
+    bit-reproducible, a ragged shard [off, off + n) with global_env_offset reproduces exactly its rows of the whole job
+    (in-kernel Philox resets included: TimeLimit 20 forces them), observations stay finite and inside the box."""
+    N, T = 262144, 45
+    dev = torch.device("cuda", 0)
+    gen = torch.Generator(device=dev).manual_seed(2)
+    proto = usv.UsvGpuVecEnv(8, device=0, env_id=env_id)
+    lo_a = torch.as_tensor(proto.action_space.low, device=dev, dtype=torch.float32)
+    hi_a = torch.as_tensor(proto.action_space.high, device=dev, dtype=torch.float32)
+    box_hi = torch.as_tensor(proto.observation_space.high, device=dev, dtype=torch.float32)
+    act_dim = proto.act_dim
+    proto.close()
+    acts = lo_a + (hi_a - lo_a) * torch.rand((T, N, act_dim), generator=gen, device=dev)
+
+    def run(n, off, a):
+        env = usv.UsvGpuVecEnv(n, device=0, seed=11, env_id=env_id, global_env_offset=off, max_episode_steps=20)
+        env.reset_tensor()
+        digest = []
+        for t in range(T):
+            o, r, te, tr = env.step_tensor(a[t].contiguous())
+            if t in (0, 19, 20, T - 1):
+                digest.append((o.clone(), r.clone(), te.clone(), tr.clone()))
+        s = env.episode_stats()
+        env.close()
+        return digest, s
+
+    full, s_full = run(N, 0, acts)
+    again, _ = run(N, 0, acts)
+    for a, b in zip(full, again):
+        for x, y in zip(a, b):
+            assert torch.equal(x, y)
+    lo, n = 100003, 50000 + 7
+    part, _ = run(n, lo, acts[:, lo:lo + n])
+    for a, b in zip(full, part):
+        for x, y in zip(a, b):
+            assert torch.equal(x[lo:lo + n], y)
+    assert full[1][3].all() or full[1][2].any()     # step 20: every env is truncated by the limit (or had terminated)
+    o = full[-1][0]
+    assert torch.isfinite(o).all() and torch.isfinite(full[-1][1]).all()
+    if env_id == "usv-simple":
+        assert float(o[:, 15:].max()) <= 1.0
+    else:
+        assert bool((o.abs() <= box_hi * 1.5 + 1e-6).all())  # the legacy boxes are nominal; a safety margin only
+    assert s_full["env_steps"] == N * T and s_full["episodes"] >= 2 * N and s_full["nonfinite"] == 0
+
+
 def test_legacy_sibling_host_face(usv):
     for env_id in ("usv-asmc-ye-int-v0", "usv-pid-v0"):
         env = usv.UsvGpuVecEnv(130, device=0, seed=4, env_id=env_id, max_episode_steps=7)
