@@ -128,7 +128,7 @@ _SIGNATURES = {
     "usvgpu_render": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "usvgpu_replay_add": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_int64,
                                     C.c_void_p, C.c_int64, C.c_void_p, C.c_int64] + [C.c_void_p] * 11),
-    "usvgpu_replay_sample": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64] + [C.c_void_p] * 14),
+    "usvgpu_replay_sample": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64] + [C.c_void_p] * 14),
     "usvgpu_gae": (C.c_int, [C.c_int, C.c_int32, C.c_int64] + [C.c_void_p] * 5 + [C.c_float, C.c_float] + [C.c_void_p] * 3),
     "usvgpu_math_probe": (C.c_int, [C.c_int, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_fp64_peak": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.c_void_p]),

@@ -553,14 +553,21 @@ replay_add_kernel(ReplayPtrs b, long long n, int obs_dim, int act_dim, long long
 
 // ReplayBuffer._get_samples: sample k is (batch_inds[k], env_inds[k]); dones come out as dones * (1 - timeouts)
 __global__ void __launch_bounds__(256)
-replay_sample_kernel(ReplayPtrs b, long long n, int obs_dim, int act_dim, long long batch,
+replay_sample_kernel(ReplayPtrs b, long long n, long long capacity, int obs_dim, int act_dim, long long batch,
                      const long long* __restrict__ batch_inds, const long long* __restrict__ env_inds,
                      float* __restrict__ out_obs, float* __restrict__ out_next_obs, float* __restrict__ out_actions,
                      float* __restrict__ out_rewards, float* __restrict__ out_dones) {
     const int lane = threadIdx.x & 31;
     const long long k = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (k >= batch) return;
-    const long long slot = batch_inds[k] * n + env_inds[k];
+    const long long bi = batch_inds[k], ei = env_inds[k];
+    if (bi < 0 || bi >= capacity || ei < 0 || ei >= n) {  // an index outside the buffer: the sample comes out as zeros
+        for (int c = lane; c < obs_dim; c += 32) out_obs[k * obs_dim + c] = out_next_obs[k * obs_dim + c] = 0.0f;
+        if (lane < act_dim) out_actions[k * act_dim + lane] = 0.0f;
+        if (lane == 0) out_rewards[k] = out_dones[k] = 0.0f;
+        return;
+    }
+    const long long slot = bi * n + ei;
     warp_copy_row(out_obs + k * obs_dim, b.obs + slot * obs_dim, obs_dim, lane);
     warp_copy_row(out_next_obs + k * obs_dim, b.next_obs + slot * obs_dim, obs_dim, lane);
     if (lane < act_dim) out_actions[k * act_dim + lane] = b.actions[slot * act_dim + lane];

@@ -156,6 +156,7 @@ render_kernel(StatePtrs s, const long long* __restrict__ index, const float* __r
     const long long f = blockIdx.y;
     const long long i = index ? index[f] : f;
     const long long n = s.n;
+    if (i < 0 || i >= n) return;  // an index outside the shard: its frame is left untouched (CTA-uniform exit)
     const double scale = (double)size / ENV_HI;  // simple_env_visualizer.py:37
     const double x = s.dyn[(long long)D_X * n + i], y = s.dyn[(long long)D_Y * n + i], psi = s.dyn[(long long)D_PSI * n + i];
     const double psx = s.epi[(long long)E_PSX * n + i], psy = s.epi[(long long)E_PSY * n + i];

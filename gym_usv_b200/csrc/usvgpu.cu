@@ -728,7 +728,7 @@ int usvgpu_replay_add(int device, int64_t n, int32_t obs_dim, int32_t act_dim, i
     return USV_OK;
 }
 
-int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim, int64_t batch,
+int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim, int64_t capacity, int64_t batch,
                          const int64_t* batch_inds, const int64_t* env_inds, const float* buf_obs,
                          const float* buf_next_obs, const float* buf_actions, const float* buf_rewards,
                          const uint8_t* buf_dones, const uint8_t* buf_timeouts, float* out_obs, float* out_next_obs,
@@ -736,7 +736,7 @@ int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim
     if (!batch_inds || !env_inds || !buf_obs || !buf_next_obs || !buf_actions || !buf_rewards || !buf_dones ||
         !buf_timeouts || !out_obs || !out_next_obs || !out_actions || !out_rewards || !out_dones)
         return fail(nullptr, USV_ERR_INVALID, "replay_sample: NULL argument");
-    if (n <= 0 || obs_dim <= 0 || act_dim <= 0 || act_dim > 32 || batch <= 0)
+    if (n <= 0 || obs_dim <= 0 || act_dim <= 0 || act_dim > 32 || batch <= 0 || capacity <= 0)
         return fail(nullptr, USV_ERR_INVALID, "replay_sample: bad sizes");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
@@ -745,7 +745,7 @@ int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim
                           const_cast<float*>(buf_rewards), const_cast<uint8_t*>(buf_dones),
                           const_cast<uint8_t*>(buf_timeouts)};
     replay_sample_kernel<<<(unsigned)((batch * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        b, n, obs_dim, act_dim, batch, reinterpret_cast<const long long*>(batch_inds),
+        b, n, capacity, obs_dim, act_dim, batch, reinterpret_cast<const long long*>(batch_inds),
         reinterpret_cast<const long long*>(env_inds), out_obs, out_next_obs, out_actions, out_rewards, out_dones);
     CU_TRY(nullptr, cudaGetLastError());
     return USV_OK;

@@ -100,7 +100,8 @@ class DeviceReplayBuffer:
         out = ReplaySamples(e(b, self.obs_dim), e(b, self.act_dim), e(b, self.obs_dim), e(b, 1), e(b, 1))
         p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
         nat.check(nat.lib().usvgpu_replay_sample(
-            self.device.index or 0, self.n_envs, self.obs_dim, self.act_dim, b, p(batch_inds), p(env_inds),
+            self.device.index or 0, self.n_envs, self.obs_dim, self.act_dim, self.buffer_size, b, p(batch_inds),
+            p(env_inds),
             p(self.observations), p(self.next_observations), p(self.actions), p(self.rewards), p(self.dones),
             p(self.timeouts), p(out.observations), p(out.next_observations), p(out.actions), p(out.rewards),
             p(out.dones), self._stream()))

@@ -242,7 +242,8 @@ int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_st
  * index int64 [n_frames] DEVICE (env indices of this shard, each in [0, N)) or NULL for envs 0 .. n_frames - 1;
  * obs float32 [N][143] DEVICE: the observation the last step / reset returned (the ray lengths are read from its
  * columns 15..142, like self.sensor_data).  size: the reference's window_size (512).
- * USV_ENV_ASMC_SIMPLE and USV_ENV_SIMPLE only.  Coverage rules: gym_usv_b200/csrc/usv_render.cuh. */
+ * USV_ENV_ASMC_SIMPLE and USV_ENV_SIMPLE only.  Coverage rules: gym_usv_b200/csrc/usv_render.cuh.  The frame of an
+ * index outside [0, N) is left untouched. */
 int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const float* obs, int32_t size,
                   uint8_t* frames, void* stream);
 
@@ -273,8 +274,9 @@ int usvgpu_replay_add(int device, int64_t n, int32_t obs_dim, int32_t act_dim, i
 /* Replaces ReplayBuffer._get_samples (what SAC.train draws gradient_steps = 8 times per train_freq = 8 steps,
  * batch_size 256: train_test/config.py:21-25): sample k = (batch_inds[k], env_inds[k]), int64 DEVICE arrays drawn by
  * the caller (SB3: np.random.randint); out_obs / out_next_obs float32 [batch][obs_dim], out_actions [batch][act_dim],
- * out_rewards [batch], out_dones [batch] = dones * (1 - timeouts). */
-int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim, int64_t batch,
+ * out_rewards [batch], out_dones [batch] = dones * (1 - timeouts).  capacity: slots per env of the buffers; a sample whose
+ * indices fall outside [0, capacity) x [0, N) comes out as zeros. */
+int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim, int64_t capacity, int64_t batch,
                          const int64_t* batch_inds, const int64_t* env_inds, const float* buf_obs,
                          const float* buf_next_obs, const float* buf_actions, const float* buf_rewards,
                          const uint8_t* buf_dones, const uint8_t* buf_timeouts, float* out_obs, float* out_next_obs,

@@ -178,4 +178,13 @@ def test_gpu_render_errors_are_loud():
         env.render_tensor([8])
     with pytest.raises(RuntimeError):
         env.render_tensor([0], size=-1)
+    # through the C ABI an index outside the shard leaves its frame untouched instead of reading out of bounds
+    import ctypes as C
+    from gym_usv_b200 import _native as nat
+    idx = torch.tensor([0, 99, -5], dtype=torch.int64, device=env.device)
+    out = torch.full((3, 64, 64, 3), 7, dtype=torch.uint8, device=env.device)
+    nat.check(nat.lib().usvgpu_render(env._h, C.c_void_p(idx.data_ptr()), 3, C.c_void_p(env.obs.data_ptr()), 64,
+                                      C.c_void_p(out.data_ptr()), None))
+    torch.cuda.synchronize()
+    assert (out[1:] == 7).all() and (out[0] != 7).any()
     env.close()

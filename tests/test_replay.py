@@ -78,6 +78,8 @@ def test_device_replay_buffer_equals_sb3_restatement(env_id, n_stack, limit):
     want = ref.get_samples(bi, ei)
     for name in ("observations", "actions", "next_observations", "dones", "rewards"):
         assert np.array_equal(getattr(got, name).cpu().numpy(), want[name]), name
+    bad = buf.sample(3, batch_inds=[0, 13, -1], env_inds=[N, 0, 0])  # outside the buffer: zeros, no fault
+    assert not bad.observations.any() and not bad.rewards.any() and not bad.dones.any()
     g = torch.Generator(device=venv.device).manual_seed(5)
     s = buf.sample(256, generator=g)
     assert s.observations.shape == (256, obs_dim) and s.dones.shape == (256, 1) and s.actions.shape == (256, venv.act_dim)

@@ -1,1 +1,1 @@
-python -m pytest tests -m gpu -x -q -k "other_env_kinds" 2>&1 | tail -12
+python -m pytest tests/test_render.py tests/test_replay.py tests/test_video.py -x -q 2>&1 | tail -6
