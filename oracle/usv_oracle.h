@@ -144,6 +144,35 @@ void usv_oracle_legacy_vec_step(UsvOracleLegacy* envs, int64_t n, const float* a
                                 uint8_t* done, float* terminal_obs, int auto_reset, uint64_t seed,
                                 int64_t global_offset, int n_threads);
 
+/* ---- collision-avoidance env 'usv-asmc-ca-v0' (gym_usv/envs/usv_asmc_ca_env.py) with the in-repo UsvAsmc substituted
+ * for the absent usv_libs_py, usv_oracle_ca.c ---- */
+#define USV_ORACLE_CA_SENSORS 16   /* usv_asmc_ca_env.py:44 */
+#define USV_ORACLE_CA_OBS_DIM 23   /* :99  7 + sensor_num */
+#define USV_ORACLE_CA_MAX_OBS 9    /* :349 int(uniform(2, 10)) -> 2..9 */
+typedef struct UsvOracleCa {
+    UsvOracleAsmc asmc;                        /* model pose / velocity + controller memory */
+    double target[2];                          /* target_point[:2] (:343-347)               */
+    double prev_action[2];                     /* action_history (maxlen 1), denormalised   */
+    double obs_x[USV_ORACLE_CA_MAX_OBS];
+    double obs_y[USV_ORACLE_CA_MAX_OBS];
+    double obs_r[USV_ORACLE_CA_MAX_OBS];
+    double ep_return;
+    int32_t n_obs;
+    int32_t steps;
+    int32_t episode;
+    int32_t pad_;
+} UsvOracleCa;
+int  usv_oracle_sizeof_ca(void);
+void usv_oracle_ca_init(UsvOracleCa* e);
+void usv_oracle_ca_reset(UsvOracleCa* e, uint64_t seed, uint64_t global_id, float obs[USV_ORACLE_CA_OBS_DIM]);
+void usv_oracle_ca_step(UsvOracleCa* e, const float action_in[2], float obs[USV_ORACLE_CA_OBS_DIM], double* reward,
+                        uint8_t* done, uint8_t* trunc, int max_episode_steps);
+void usv_oracle_ca_vec_reset(UsvOracleCa* envs, int64_t n, uint64_t seed, int64_t global_offset, float* obs,
+                             int n_threads);
+void usv_oracle_ca_vec_step(UsvOracleCa* envs, int64_t n, const float* actions, float* obs, double* reward,
+                            uint8_t* done, uint8_t* trunc, float* terminal_obs, int auto_reset, int max_episode_steps,
+                            uint64_t seed, int64_t global_offset, int n_threads);
+
 /* ---- rgb_array frame of SimpleEnvVisualizer.render_frame (simple_env_visualizer.py:17-114), usv_oracle_render.c;
  * PARITY UNPINNED against pygame's pixels (pygame absent): draw list from the reference, coverage rules ours ---- */
 void usv_oracle_render_frame(const double position[3], const double target[2], const double* sensor_distance,

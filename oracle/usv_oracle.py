@@ -73,6 +73,23 @@ LEGACY_DTYPE = np.dtype(
     ],
     align=True,
 )
+CA_OBS_DIM, CA_MAX_OBS = 23, 9
+CA_DTYPE = np.dtype(
+    [
+        ("asmc", ASMC_DTYPE),
+        ("target", "<f8", (2,)),
+        ("prev_action", "<f8", (2,)),
+        ("obs_x", "<f8", (CA_MAX_OBS,)),
+        ("obs_y", "<f8", (CA_MAX_OBS,)),
+        ("obs_r", "<f8", (CA_MAX_OBS,)),
+        ("ep_return", "<f8"),
+        ("n_obs", "<i4"),
+        ("steps", "<i4"),
+        ("episode", "<i4"),
+        ("pad_", "<i4"),
+    ],
+    align=True,
+)
 # gym_usv/__init__.py:3-16: the three registered ids that share UsvAsmcEnv's step()
 LEGACY_VARIANTS = {"usv-asmc-v0": 0, "usv-asmc-ye-int-v0": 1, "usv-pid-v0": 2}
 
@@ -92,7 +109,7 @@ class Config(C.Structure):
 
 def build(force: bool = False) -> str:
     """Compile the oracle with gcc (make -C oracle).  Returns the .so path."""
-    srcs = [os.path.join(_HERE, f) for f in ("usv_oracle.c", "usv_oracle_legacy.c", "usv_oracle_legacy_step.inc", "usv_oracle_render.c",
+    srcs = [os.path.join(_HERE, f) for f in ("usv_oracle.c", "usv_oracle_legacy.c", "usv_oracle_legacy_step.inc", "usv_oracle_render.c", "usv_oracle_ca.c",
                                              "usv_oracle.h")]
     stale = (not os.path.exists(_LIB_PATH)) or any(
         os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in srcs if os.path.exists(s)
@@ -140,6 +157,11 @@ def lib():
         for name in ("usv_oracle_legacy_init", "usv_oracle_legacy_reset_from_draws", "usv_oracle_legacy_reset",
                      "usv_oracle_legacy_step", "usv_oracle_legacy_vec_reset", "usv_oracle_legacy_vec_step"):
             getattr(L, name).restype = None
+        L.usv_oracle_sizeof_ca.restype = C.c_int
+        L.usv_oracle_ca_vec_reset.argtypes = [vp, i64, u64, i64, vp, i32]
+        L.usv_oracle_ca_vec_step.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, i32, i32, u64, i64, i32]
+        L.usv_oracle_ca_vec_reset.restype = L.usv_oracle_ca_vec_step.restype = None
+        assert L.usv_oracle_sizeof_ca() == CA_DTYPE.itemsize, (L.usv_oracle_sizeof_ca(), CA_DTYPE.itemsize)
         L.usv_oracle_render_frame.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, dbl, i32, vp]
         L.usv_oracle_render_frame.restype = None
         assert L.usv_oracle_sizeof_legacy() == LEGACY_DTYPE.itemsize
@@ -263,6 +285,34 @@ class OracleLegacyVecEnv:
                                          _p(self.terminal_obs), int(self.auto_reset), self.seed, self.global_offset,
                                          self.n_threads)
         return self.obs, self.reward, self.done
+
+
+class OracleCaVecEnv:
+    """N UsvAsmcCaEnv instances ('usv-asmc-ca-v0', in-repo UsvAsmc substituted for usv_libs_py) in lock-step,
+    SB3 auto-reset semantics; TimeLimit 5000 (gym_usv/__init__.py:18-22)."""
+
+    def __init__(self, n, seed=0, global_offset=0, auto_reset=True, max_episode_steps=5000, n_threads=1):
+        self.n, self.seed, self.global_offset = int(n), int(seed), int(global_offset)
+        self.auto_reset, self.max_episode_steps, self.n_threads = bool(auto_reset), int(max_episode_steps), int(n_threads)
+        self.envs = np.zeros(self.n, dtype=CA_DTYPE)
+        lib()
+        self.envs["episode"] = -1
+        self.obs = np.zeros((self.n, CA_OBS_DIM), dtype=np.float32)
+        self.terminal_obs = np.zeros((self.n, CA_OBS_DIM), dtype=np.float32)
+        self.reward = np.zeros(self.n)
+        self.done = np.zeros(self.n, dtype=np.uint8)
+        self.trunc = np.zeros(self.n, dtype=np.uint8)
+
+    def reset(self):
+        lib().usv_oracle_ca_vec_reset(_p(self.envs), self.n, self.seed, self.global_offset, _p(self.obs), self.n_threads)
+        return self.obs
+
+    def step(self, actions):
+        a = np.ascontiguousarray(actions, dtype=np.float32).reshape(self.n, 2)
+        lib().usv_oracle_ca_vec_step(_p(self.envs), self.n, _p(a), _p(self.obs), _p(self.reward), _p(self.done),
+                                     _p(self.trunc), _p(self.terminal_obs), int(self.auto_reset),
+                                     self.max_episode_steps, self.seed, self.global_offset, self.n_threads)
+        return self.obs, self.reward, self.done, self.trunc
 
 
 def render_frame(position, target, sensor_distance, obs_x, obs_y, obs_r, path_start, path_end, env_hi=20.0, size=512):

@@ -382,3 +382,76 @@ def test_legacy_sibling_reset_from_reference_draws(env_id, gname, xy, seed):
     p, tg = ov.envs["position"], ov.envs["target"]
     assert np.all(np.abs(p[:, :2]) <= xy) and np.abs(p[:, :2]).max() > 0.95 * xy
     assert np.all((tg[:, 2] >= 0.4) & (tg[:, 2] <= 1.4)) and abs(tg[:, 2].mean() - 0.9) < 0.03
+
+
+# ------------------------------------------------------------------------------------------
+# 'usv-asmc-ca-v0' (usv_asmc_ca_env.py) with the in-repo UsvAsmc substituted for usv_libs_py, SURVEY 8f rank 3
+# ------------------------------------------------------------------------------------------
+def ca_inject(e, g, prefix, k):
+    """Installs the k-th reset snapshot of a golden CA rollout (taken after reset()'s internal step([-1, 0]))."""
+    e["asmc"]["eta"], e["asmc"]["nu"] = g[prefix + "reset_position"][k], g[prefix + "reset_velocity"][k]
+    e["asmc"]["last"], e["asmc"]["aux"] = g[prefix + "reset_last"][k], g[prefix + "reset_aux"][k]
+    e["asmc"]["so"] = g[prefix + "reset_so_filter"][k][:4]
+    e["asmc"]["perturb_step"] = 0
+    e["target"], e["prev_action"] = g[prefix + "reset_target"][k], g[prefix + "reset_prev_action"][k]
+    e["obs_x"], e["obs_y"], e["obs_r"] = g[prefix + "reset_ox"][k], g[prefix + "reset_oy"][k], g[prefix + "reset_orad"][k]
+    e["n_obs"], e["steps"], e["ep_return"] = g[prefix + "reset_n_obs"][k], 0, 0.0
+
+
+def ca_replay(g, prefix, step_fn, inject_fn):
+    """step_fn(action[2]) -> (obs[23], reward, done, trunc, position[3], velocity[3]); flags exact."""
+    g = {k: g[k] for k in g.keys() if k.startswith(prefix)}
+    acts, reset_step = g[prefix + "actions"], list(g[prefix + "reset_step"])
+    worst = dict(obs=0.0, rew=0.0, pos=0.0, vel=0.0)
+    for t in range(len(acts)):
+        if t in reset_step:
+            inject_fn(reset_step.index(t))
+        obs, rew, done, trunc, pos, vel = step_fn(acts[t])
+        assert (bool(done), bool(trunc)) == (bool(g[prefix + "done"][t]), bool(g[prefix + "trunc"][t])), f"flags differ at step {t}"
+        worst["obs"] = max(worst["obs"], float(np.abs(obs.astype(np.float64) - g[prefix + "obs"][t]).max()))
+        worst["rew"] = max(worst["rew"], abs(float(rew) - float(g[prefix + "reward"][t])))
+        worst["pos"] = max(worst["pos"], float(np.abs(pos - g[prefix + "pos"][t]).max()))
+        worst["vel"] = max(worst["vel"], float(np.abs(vel - g[prefix + "vel"][t]).max()))
+    return worst
+
+
+@pytest.mark.parametrize("prefix", ["R0_", "R1_", "R2_"])
+def test_ca_env_oracle_vs_reference_rollout(prefix):
+    g = load_golden("ca_env.npz")
+    ov = uo.OracleCaVecEnv(1, auto_reset=False, max_episode_steps=0)
+
+    def step(a):
+        obs, rew, done, trunc = ov.step(a[None])
+        e = ov.envs[0]["asmc"]
+        return obs[0].copy(), rew[0], done[0], trunc[0], e["eta"].copy(), e["nu"].copy()
+
+    w = ca_replay(g, prefix, step, lambda k: ca_inject(ov.envs[0], g, prefix, k))
+    # float64 on both sides; the controller sits on its sliding surface, so libm-vs-numpy ulps are carried by the closed
+    # loop over up to 30 000 sub-steps.  Measured: pose 8.2e-9, velocity 7.0e-9, reward 3.2e-10, observation 6e-8.
+    print(prefix, w)
+    assert w["pos"] < 1e-7 and w["vel"] < 1e-7 and w["rew"] < 1e-8 and w["obs"] < 1e-6, w
+    if prefix == "R2_":
+        assert int(g["R2_done"].sum()) >= 5 and int(g["R0_trunc"].sum()) >= 1  # arrivals and collisions are replayed
+
+
+def test_ca_reset_restatement_matches_reference_reset_observation():
+    """The reset observation is that of the internal step([-1, 0]) (usv_asmc_ca_env.py:402): from a golden snapshot
+    taken BEFORE that step cannot be had, so the check runs the other way -- the Philox reset leaves a state whose
+    own reset observation obeys the reference's formulae (previous action [-1, 0] -> columns 5, 6; 16 readings in
+    (0, 1]; obstacles outside the 0.75 m margins of boat and target) and whose ranges are the reference's."""
+    ov = uo.OracleCaVecEnv(3000, seed=7)
+    obs = ov.reset().copy()
+    e = ov.envs
+    assert np.all(e["prev_action"] == [-1.0, 0.0]) and np.all(e["steps"] == 0)
+    assert np.all((obs[:, 7:] > 0) & (obs[:, 7:] <= 1.0))
+    assert np.all((e["target"][:, 0] >= -10) & (e["target"][:, 0] <= 20) & (e["target"][:, 1] >= 5) & (e["target"][:, 1] <= 9))
+    assert np.all((e["n_obs"] >= 0) & (e["n_obs"] <= 9)) and e["n_obs"].max() == 9 and 4.5 < e["n_obs"].mean() < 5.6
+    assert np.all(np.abs(e["asmc"]["eta"][:, 2]) < np.pi / 4 + 0.02) and np.all(e["asmc"]["eta"][:, 1] < -4.9)
+    for i in range(200):
+        n = e["n_obs"][i]
+        d_t = np.hypot(e["obs_x"][i, :n] - e["target"][i, 0], e["obs_y"][i, :n] - e["target"][i, 1]) - e["obs_r"][i, :n]
+        assert np.all(d_t >= 0.75 - 1e-12) and np.all((e["obs_r"][i, :n] >= 1) & (e["obs_r"][i, :n] <= 2))
+    # the next step reports the reset step's action in columns 5, 6: -1 / pi and 0
+    obs2, *_ = ov.step(np.zeros((3000, 2), np.float32))
+    live = ~(ov.done | ov.trunc).astype(bool)
+    assert np.allclose(obs2[live, 5], -1 / np.pi, atol=1e-7) and np.all(obs2[live, 6] == 0)
