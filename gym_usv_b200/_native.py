@@ -15,7 +15,7 @@ _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
-HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_render.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
+HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_ca.cuh", "usv_render.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
                                              "usv_sensor.cuh", "usv_kernels.cuh", "usv_math.cuh")] + \
           [os.path.join(_ROOT, "include", "usvgpu.h")]
 
@@ -33,14 +33,19 @@ ENV_ASMC_SIMPLE = 0
 ENV_ASMC_V0 = 1
 ENV_SIMPLE = 2
 ENV_ASMC_YE_INT_V0, ENV_PID_V0 = 3, 4
+ENV_ASMC_CA_V0 = 5
 PREC_F64 = 0
 PREC_MIXED = 1
 
 FIELD_DYN, FIELD_EPI, FIELD_OBSTACLES, FIELD_N_OBS, FIELD_STEPS, FIELD_EPISODE, FIELD_EP_RETURN = range(7)
 FIELD_LEGACY, FIELD_LEGACY_TARGET, FIELD_LEGACY_POS0, FIELD_LEGACY64 = 7, 8, 9, 10
+FIELD_CA, FIELD_CA_N_OBS = 11, 12
 LEGACY_ROWS = 19
 LEGACY64_ROWS = 21
 LEGACY_OBS_DIM = 6
+CA_ROWS = 31
+CA_OBS_DIM = 23
+CA_MAX_OBSTACLES = 9
 LEGACY_NAMES = ("action_last", "u", "v", "r", "x", "y", "psi", "e_u_int", "ka_u", "ka_psi", "x_dot_last", "y_dot_last",
                 "psi_dot_last", "u_dot_last", "v_dot_last", "r_dot_last", "e_u_last", "ka_dot_u_last", "ka_dot_psi_last")
 

@@ -88,7 +88,8 @@ __device__ __forceinline__ double np_clip(double x, double lo, double hi) { retu
 // usv_asmc.py:120  np.where(|e| > pi, sign(e)*(|e| - 2 pi), e)
 __device__ __forceinline__ double wrap_once(double e) {
     const double a = fabs(e);
-    return (a > MK.pi) ? copysign(a - MK.two_pi, e) : e;
+    // sign(e) (|e| - 2 pi) == e - sign(e) 2 pi bit for bit: the sign flips for pi < |e| < 2 pi and stays beyond 2 pi
+    return (a > MK.pi) ? e - copysign(MK.two_pi, e) : e;
 }
 // angle reduced to [-pi, pi]  (simple_env.py:64-65 computes atan2(sin a, cos a))
 __device__ __forceinline__ double wrap_pi(double a) {

@@ -19,6 +19,7 @@
 #include "../../include/usvgpu.h"
 #include "usv_kernels.cuh"
 #include "usv_legacy.cuh"
+#include "usv_ca.cuh"
 #include "usv_render.cuh"
 
 // =================================================================================================
@@ -33,6 +34,8 @@ struct UsvGpu {
     int device;
     int obs_dim, act_dim;  // 143 / 2 ('usv-asmc-simple') or 6 / 1 ('usv-asmc-v0')
     bool legacy;
+    bool ca;               // env_kind == USV_ENV_ASMC_CA_V0: sp.dyn + cp.ca + cp.n_obs, the rest of sp as for legacy
+    CaPtrs cp;
     StatePtrs sp;
     LegacyPtrs lp;         // env_kind == USV_ENV_ASMC_V0: sp holds only n, stats, ep_return, steps, episode, ep_done
     size_t obst_elem;
@@ -106,6 +109,16 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
                      float* tobs, cudaStream_t st, cudaEvent_t mid = nullptr, long long lo = 0, long long hi = -1) {
     if (hi < 0) hi = h->sp.n;
     const StepFlags fl = {h->cfg.do_perturb, h->cfg.skip_kinematic, h->cfg.max_episode_steps, h->cfg.auto_reset, lo, hi};
+    if (h->ca) {  // 'usv-asmc-ca-v0': one kernel, thread per env
+        ca_kernel<false><<<(unsigned)((hi - lo + CA_B - 1) / CA_B), CA_B, 0, st>>>(h->cp, fl, nullptr, actions, obs, reward, term,
+                                                                                  trunc, tobs);
+        cudaError_t ce = cudaGetLastError();
+        if (ce != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("ca step launch: ") + cudaGetErrorString(ce));
+        if (mid) cudaEventRecord(mid, st);
+        h->host_env_steps += (unsigned long long)(hi - lo);
+        h->launches += 1;
+        return USV_OK;
+    }
     if (h->legacy) {  // 'usv-asmc-v0' and its float64 siblings: one kernel, thread per env
         const unsigned lblocks = (unsigned)((hi - lo + LEG_B - 1) / LEG_B);
         if (h->lp.variant == LEG_YE_INT)
@@ -155,11 +168,13 @@ static int field_ptr(UsvGpu* h, int32_t field, void** p, int64_t* bytes) {
         case USV_FIELD_LEGACY_TARGET: if (!h->legacy) return -1; *p = h->lp.target; *bytes = n * 6 * 8; return 0;
         case USV_FIELD_LEGACY_POS0: if (!h->lp.pos0) return -1; *p = h->lp.pos0; *bytes = n * 3 * 8; return 0;
         case USV_FIELD_LEGACY64: if (!h->lp.st64) return -1; *p = h->lp.st64; *bytes = n * LEG64_ROWS * 8; return 0;
+        case USV_FIELD_CA: if (!h->ca) return -1; *p = h->cp.ca; *bytes = n * CA_ROWS * 8; return 0;
+        case USV_FIELD_CA_N_OBS: if (!h->ca) return -1; *p = h->cp.n_obs; *bytes = n * 4; return 0;
         case USV_FIELD_DYN: if (h->legacy) return -1; *p = h->sp.dyn; *bytes = n * N_DYN * 8; return 0;
-        case USV_FIELD_EPI: if (h->legacy) return -1; *p = h->sp.epi; *bytes = n * N_EPI * 8; return 0;
+        case USV_FIELD_EPI: if (h->legacy || h->ca) return -1; *p = h->sp.epi; *bytes = n * N_EPI * 8; return 0;
         // these two live inside the interleaved sensor-input rows: *p is the first element, copies are pitched
-        case USV_FIELD_OBSTACLES: if (h->legacy) return -1; *p = h->sp.sin; *bytes = n * MAX_OBST * 3 * (int64_t)h->obst_elem; return 0;
-        case USV_FIELD_N_OBS: if (h->legacy) return -1; *p = h->sp.sin + h->sp.sin_tail + sizeof(Hand) + HDR_PAD * sizeof(float); *bytes = n * 4; return 0;
+        case USV_FIELD_OBSTACLES: if (h->legacy || h->ca) return -1; *p = h->sp.sin; *bytes = n * MAX_OBST * 3 * (int64_t)h->obst_elem; return 0;
+        case USV_FIELD_N_OBS: if (h->legacy || h->ca) return -1; *p = h->sp.sin + h->sp.sin_tail + sizeof(Hand) + HDR_PAD * sizeof(float); *bytes = n * 4; return 0;
         case USV_FIELD_STEPS: *p = h->sp.steps; *bytes = n * 4; return 0;
         case USV_FIELD_EPISODE: *p = h->sp.episode; *bytes = n * 4; return 0;
         case USV_FIELD_EP_RETURN: *p = h->sp.ep_return; *bytes = n * 8; return 0;
@@ -178,7 +193,7 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     if (!cfg || !out) return fail(nullptr, USV_ERR_INVALID, "cfg/out is NULL");
     *out = nullptr;
     if (n_envs <= 0) return fail(nullptr, USV_ERR_INVALID, "n_envs must be positive");
-    if (cfg->env_kind < USV_ENV_ASMC_SIMPLE || cfg->env_kind > USV_ENV_PID_V0)
+    if (cfg->env_kind < USV_ENV_ASMC_SIMPLE || cfg->env_kind > USV_ENV_ASMC_CA_V0)
         return fail(nullptr, USV_ERR_INVALID, "unknown env_kind");
     if (cfg->precision != USV_PREC_F64) return fail(nullptr, USV_ERR_INVALID, "precision not supported by this build");
     int rc = check_device(nullptr, device);
@@ -189,9 +204,11 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->device = device;
     const int variant = cfg->env_kind == USV_ENV_ASMC_YE_INT_V0 ? LEG_YE_INT : cfg->env_kind == USV_ENV_PID_V0 ? LEG_PID : LEG_ASMC_V0;
     h->legacy = cfg->env_kind == USV_ENV_ASMC_V0 || variant != LEG_ASMC_V0;
-    h->obs_dim = h->legacy ? LEG_OBS : OBS_DIM;
+    h->ca = cfg->env_kind == USV_ENV_ASMC_CA_V0;
+    h->obs_dim = h->legacy ? LEG_OBS : h->ca ? CA_OBS : OBS_DIM;
     h->act_dim = h->legacy ? 1 : 2;
     memset(&h->lp, 0, sizeof(h->lp));
+    memset(&h->cp, 0, sizeof(h->cp));
     h->host_env_steps = 0;
     h->launches = 0;
     h->obst_elem = cfg->obstacles_f32 ? sizeof(float) : sizeof(double);
@@ -228,6 +245,16 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
             alloc((void**)&h->lp.st64, n * LEG64_ROWS * sizeof(double));
         }
         alloc((void**)&h->lp.target, n * 6 * sizeof(double));
+    } else if (h->ca) {
+        alloc((void**)&h->sp.dyn, n * N_DYN * sizeof(double));
+        alloc((void**)&h->cp.ca, n * CA_ROWS * sizeof(double));
+        alloc((void**)&h->cp.n_obs, n * sizeof(int));
+        double2 t[CA_SENS];
+        for (int k = 0; k < CA_SENS; ++k) {  // usv_asmc_ca_env.py:47-49, 420-421
+            const double phi = -PI * 2 / 3 + (double)k * (((2.0 / 3) * (2 * PI)) / CA_SENS);
+            t[k] = make_double2(cos(phi), sin(phi));
+        }
+        if (e == cudaSuccess) e = cudaMemcpyToSymbol(CA_RAYTAB, t, sizeof(t));
     } else {
         alloc((void**)&h->sp.dyn, n * N_DYN * sizeof(double));
         alloc((void**)&h->sp.epi, n * N_EPI * sizeof(double));
@@ -263,6 +290,15 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->lp.global_offset = global_env_offset;
     h->lp.seed = seed;
     h->lp.variant = variant;
+    h->cp.dyn = h->sp.dyn;
+    h->cp.steps = h->sp.steps;
+    h->cp.episode = h->sp.episode;
+    h->cp.ep_return = h->sp.ep_return;
+    h->cp.ep_done = h->sp.ep_done;
+    h->cp.stats = h->sp.stats;
+    h->cp.n = n_envs;
+    h->cp.global_offset = global_env_offset;
+    h->cp.seed = seed;
     *out = h;
     return USV_OK;
 }
@@ -277,6 +313,8 @@ int usvgpu_destroy(usvgpu_handle h) {
     cudaFree(h->lp.pos0);
     cudaFree(h->lp.st64);
     cudaFree(h->lp.target);
+    cudaFree(h->cp.ca);
+    cudaFree(h->cp.n_obs);
     cudaFree(h->sp.dyn);
     cudaFree(h->sp.epi);
     cudaFree(h->sp.sin);
@@ -312,7 +350,11 @@ int usvgpu_reset(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream)
     const int threads = 128;
     const unsigned blocks = (unsigned)((h->sp.n + threads - 1) / threads);
     cudaStream_t st = (cudaStream_t)stream;
-    if (h->legacy) legacy_reset_kernel<<<blocks, threads, 0, st>>>(h->lp, mask, obs);
+    if (h->ca) {
+        const StepFlags fl = {0, 0, h->cfg.max_episode_steps, h->cfg.auto_reset, 0, h->sp.n};
+        ca_kernel<true><<<(unsigned)((h->sp.n + CA_B - 1) / CA_B), CA_B, 0, st>>>(h->cp, fl, mask, nullptr, obs, nullptr, nullptr,
+                                                                                 nullptr, nullptr);
+    } else if (h->legacy) legacy_reset_kernel<<<blocks, threads, 0, st>>>(h->lp, mask, obs);
     else if (h->cfg.obstacles_f32) reset_kernel<float><<<blocks, threads, 0, st>>>(h->sp, mask, obs);
     else reset_kernel<double><<<blocks, threads, 0, st>>>(h->sp, mask, obs);
     CU_TRY(h, cudaGetLastError());
@@ -685,7 +727,7 @@ int usvgpu_gae(int device, int32_t n_steps, int64_t n, const float* rewards, con
 int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const float* obs, int32_t size,
                   uint8_t* frames, void* stream) {
     if (!h) return fail(nullptr, USV_ERR_INVALID, "handle is NULL");
-    if (h->legacy) return fail(h, USV_ERR_INVALID, "render: the path-following envs have no SimpleEnvVisualizer");
+    if (h->legacy || h->ca) return fail(h, USV_ERR_INVALID, "render: only the simple envs draw with SimpleEnvVisualizer");
     if (!obs || !frames || n_frames <= 0 || n_frames > 65535 || size < 1 || size > 8192)
         return fail(h, USV_ERR_INVALID, "bad render arguments (obs / frames NULL, n_frames not in 1..65535, size not in 1..8192)");
     if (!index && n_frames > h->sp.n) return fail(h, USV_ERR_INVALID, "render: more frames than envs");

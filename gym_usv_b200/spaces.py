@@ -67,3 +67,13 @@ def legacy_observation_space():
 def legacy_action_space():
     """usv_asmc_env.py:92."""
     return make_box(-np.pi / 2, np.pi / 2, shape=(1,), dtype=np.float32)
+
+
+def ca_observation_space():
+    """usv_asmc_ca_env.py:99-113  Box(-1, 1, (7 + 16,), float32)."""
+    return make_box(-1.0, 1.0, shape=(23,), dtype=np.float32)
+
+
+def ca_action_space():
+    """usv_asmc_ca_env.py:106-110  Box([-1, -1], [1, 1], float32)."""
+    return make_box(-1.0, 1.0, shape=(2,), dtype=np.float32)

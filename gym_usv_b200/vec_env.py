@@ -28,9 +28,10 @@ ENV_ID = "usv-asmc-simple"
 # gym_usv/__init__.py:30-34 registers a 1000-step TimeLimit for 'usv-asmc-simple' and none for 'usv-asmc-v0' (:3-6)
 # 'usv-pid-v0' (:8-11) and 'usv-asmc-ye-int-v0' (:13-16) are registered without a limit as well
 MAX_EPISODE_STEPS = {"usv-asmc-simple": 1000, "usv-asmc-v0": 0, "usv-simple": 500,  # usv-simple: __init__.py:24-28
-                     "usv-asmc-ye-int-v0": 0, "usv-pid-v0": 0}
+                     "usv-asmc-ye-int-v0": 0, "usv-pid-v0": 0, "usv-asmc-ca-v0": 5000}  # ca: __init__.py:18-22
 ENV_KINDS = {"usv-asmc-simple": nat.ENV_ASMC_SIMPLE, "usv-asmc-v0": nat.ENV_ASMC_V0, "usv-simple": nat.ENV_SIMPLE,
-             "usv-asmc-ye-int-v0": nat.ENV_ASMC_YE_INT_V0, "usv-pid-v0": nat.ENV_PID_V0}
+             "usv-asmc-ye-int-v0": nat.ENV_ASMC_YE_INT_V0, "usv-pid-v0": nat.ENV_PID_V0,
+             "usv-asmc-ca-v0": nat.ENV_ASMC_CA_V0}
 LEGACY_IDS = ("usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0")  # UsvAsmcEnv's step() and its two float64 siblings
 
 
@@ -73,10 +74,13 @@ class UsvGpuVecEnv:
         self.env_id = env_id
         self.legacy = env_id in LEGACY_IDS  # UsvAsmcEnv, gym_usv/envs/usv_asmc_env.py, UsvAsmcYeIntEnv, UsvPidEnv
         self.legacy64 = self.legacy and env_id != "usv-asmc-v0"  # float64 state (USV_FIELD_LEGACY64)
-        self.obs_dim = nat.LEGACY_OBS_DIM if self.legacy else nat.OBS_DIM
+        self.ca = env_id == "usv-asmc-ca-v0"  # UsvAsmcCaEnv, gym_usv/envs/usv_asmc_ca_env.py (in-repo UsvAsmc substituted)
+        self.obs_dim = nat.LEGACY_OBS_DIM if self.legacy else nat.CA_OBS_DIM if self.ca else nat.OBS_DIM
         self.act_dim = 1 if self.legacy else nat.ACT_DIM
-        self.observation_space = spaces.legacy_observation_space() if self.legacy else spaces.simple_observation_space()
-        self.action_space = spaces.legacy_action_space() if self.legacy else spaces.simple_action_space()
+        self.observation_space = (spaces.legacy_observation_space() if self.legacy else spaces.ca_observation_space()
+                                  if self.ca else spaces.simple_observation_space())
+        self.action_space = (spaces.legacy_action_space() if self.legacy else spaces.ca_action_space() if self.ca
+                             else spaces.simple_action_space())
         self.render_mode = render_mode
         self.render_envs = 16   # how many envs get_images() / render() draw
         self.render_size = 512  # SimpleEnvVisualizer(window_size=512), simple_env_visualizer.py:9
@@ -315,8 +319,8 @@ class UsvGpuVecEnv:
         """UsvSimpleEnv.render() with render_mode "rgb_array" (simple_env.py:117-131 -> simple_env_visualizer.py:17-114)
         for the envs in `indices` (default: the first ``render_envs``): uint8 CUDA tensor [K, size, size, 3] drawn by
         usvgpu_render from the device state and the last observation.  No window system involved."""
-        if self.legacy:
-            raise NotImplementedError(f"{self.env_id} has no SimpleEnvVisualizer; its pyglet viewer is unavailable on this box")
+        if self.legacy or self.ca:
+            raise NotImplementedError(f"{self.env_id} has no SimpleEnvVisualizer; its own viewer is unavailable on this box")
         size = int(size or self.render_size)
         if indices is None:
             idx, k = None, min(self.num_envs, self.render_envs)
@@ -365,7 +369,13 @@ class UsvGpuVecEnv:
     _LEGACY64_FIELDS = {"legacy64": (nat.FIELD_LEGACY64, np.float64, (nat.LEGACY64_ROWS,), ()),
                         **{k: v for k, v in _LEGACY_FIELDS.items() if k not in ("legacy", "pos0")}}
 
+    _CA_FIELDS = {"dyn": _FIELDS["dyn"], "ca": (nat.FIELD_CA, np.float64, (nat.CA_ROWS,), ()),
+                  "n_obs": (nat.FIELD_CA_N_OBS, np.int32, (), ()),
+                  "steps": _FIELDS["steps"], "episode": _FIELDS["episode"], "ep_return": _FIELDS["ep_return"]}
+
     def _field_table(self):
+        if self.ca:
+            return self._CA_FIELDS
         return self._LEGACY64_FIELDS if self.legacy64 else self._LEGACY_FIELDS if self.legacy else self._FIELDS
 
     def _field_array(self, name):

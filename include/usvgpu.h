@@ -25,6 +25,7 @@ extern "C" {
 #define USVGPU_ACT_DIM 2           /* gym_usv/envs/simple_env.py:30                           */
 #define USVGPU_SENSORS 128         /* gym_usv/envs/simple_env.py:11                           */
 #define USVGPU_MAX_OBSTACLES 32    /* reset draws 15..29 (simple_env.py:257); padded to 32    */
+#define USVGPU_CA_OBS_DIM 23       /* gym_usv/envs/usv_asmc_ca_env.py:99 (7 + 16 sensors)     */
 #define USVGPU_LEGACY_OBS_DIM 6    /* gym_usv/envs/usv_asmc_env.py:89-96                      */
 
 typedef struct UsvGpu* usvgpu_handle;
@@ -47,7 +48,14 @@ typedef enum UsvEnvKind {
     /* the two float64 siblings of 'usv-asmc-v0': same spaces (obs [N][6], actions [N][1]) and entry points; their
      * state is USV_FIELD_LEGACY64 (+ USV_FIELD_LEGACY_TARGET), USV_FIELD_LEGACY / _POS0 do not exist for them */
     USV_ENV_ASMC_YE_INT_V0 = 3, /* 'usv-asmc-ye-int-v0' gym_usv/__init__.py:13-16 -> envs/usv_asmc_ye_int_env.py */
-    USV_ENV_PID_V0 = 4          /* 'usv-pid-v0'         gym_usv/__init__.py:8-11  -> envs/usv_pid_env.py         */
+    USV_ENV_PID_V0 = 4,         /* 'usv-pid-v0'         gym_usv/__init__.py:8-11  -> envs/usv_pid_env.py         */
+    /* 'usv-asmc-ca-v0' gym_usv/__init__.py:18-22 -> envs/usv_asmc_ca_env.py: point target, <= 9 obstacles, 16-ray lidar,
+     * observation float32[23], action float32[2] in [-1, 1]^2, TimeLimit 5000.  usv_libs_py (its model / controller)
+     * is not part of the reference tree: the env runs the in-repo UsvAsmc (one compute() of 10 sub-steps per step),
+     * the substitution usv_asmc_ca_env.py:210 keeps as a comment.  State: USV_FIELD_DYN (row 22 unused) + USV_FIELD_CA
+     * + USV_FIELD_CA_N_OBS.  terminated = arrived | tracking error > 40 | out of range; truncated = collision |
+     * out of range | TimeLimit.  No render, no perturbation, no info rows. */
+    USV_ENV_ASMC_CA_V0 = 5
 } UsvEnvKind;
 
 typedef enum UsvPrecision {
@@ -110,11 +118,16 @@ typedef enum UsvField {
     /* USV_ENV_ASMC_YE_INT_V0 / USV_ENV_PID_V0, float64 [21][N]: the 19 rows of USV_FIELD_LEGACY in float64 (these
      * envs never round to float32) | ye_int (aux_vars[3]) | ye_last (last[9]) of usv_asmc_ye_int_env.py:247-251;
      * the last two rows stay 0 for the pid env */
-    USV_FIELD_LEGACY64 = 10
+    USV_FIELD_LEGACY64 = 10,
+    /* USV_ENV_ASMC_CA_V0, float64 [31][N]: target x y | previous action (2, denormalised) | obstacle x[9] | y[9] |
+     * radius[9] (usv_asmc_ca_env.py:341-356) */
+    USV_FIELD_CA = 11,
+    USV_FIELD_CA_N_OBS = 12 /* int32 [N] obstacles left after the reset's deletions (:379-399) */
 } UsvField;
 
 #define USV_LEGACY_ROWS 19
 #define USV_LEGACY64_ROWS 21
+#define USV_CA_ROWS 31
 #define USV_DYN_ROWS 23
 #define USV_EPI_ROWS 7
 

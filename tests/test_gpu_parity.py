@@ -743,7 +743,7 @@ def test_legacy_sibling_lockstep_vs_oracle_with_autoreset(usv, env_id):
     env.close()
 
 
-@pytest.mark.parametrize("env_id", ["usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0", "usv-simple"])
+@pytest.mark.parametrize("env_id", ["usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0", "usv-simple", "usv-asmc-ca-v0"])
 def test_sharding_invariance_other_env_kinds_full_size(usv, env_id):
     """The size-independent properties of the headline env for the other kinds, at 262 144 envs: a run is
     bit-reproducible, a ragged shard [off, off + n) with global_env_offset reproduces exactly its rows of the whole job
