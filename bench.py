@@ -471,6 +471,15 @@ def run_ours(args, rank, local_rank, world):
         dist.destroy_process_group()
 
 
+def _json_only_stdout():
+    """The contract is ONE JSON line on stdout: native libraries that write to file descriptor 1 (NCCL prints its
+    version banner there) are sent to stderr, Python's sys.stdout keeps the real stdout."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -497,6 +506,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
+        _json_only_stdout()
         run_reference(args, rank, world)
         return
     if world == 1 and args.gpus > 1:
@@ -504,6 +514,7 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", str(29400 + os.getpid() % 500), os.path.abspath(__file__)]
         raise SystemExit(subprocess.call(cmd + sys.argv[1:]))
+    _json_only_stdout()
     run_ours(args, rank, local_rank, world)
 
 
