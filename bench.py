@@ -66,6 +66,8 @@ def kernel_bytes(obstacles: bool, obstacles_f32: bool, kinematic: bool = False) 
 # 'usv-asmc-v0' (UsvAsmcEnv, one sub-step per env-step): float32 SoA state [19], float64 target (4 of 6 rows read)
 #   read : 19 f32 state + 4 f64 target + f32 action + i32 steps + f64 episode return            = 124 B
 #   write: 19 f32 state + 6 f32 observation + f32 reward + 2 flag bytes + i32 steps + f64 return = 118 B
+# SURVEY.md 8d "Algorithmic bytes per env-step" with float64 dynamic state (the storage this build uses)
+SURVEY_BYTES_F64_STATE = {"obstacles": 1390, "no_obstacles": 1002}
 LEGACY_BYTES = (19 * 4 + 4 * 8 + 4 + 4 + 8) + (19 * 4 + 6 * 4 + 4 + 2 + 4 + 8)
 # the float64 siblings keep float64 state columns: 21 (ye-int) / 19 (pid) rows read and written
 LEGACY_IDS = ("usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0")
@@ -263,7 +265,7 @@ def dtype_of(args):
         return "f32 state / f64 control terms (the reference's own mix)"
     if args.env in LEGACY_IDS:
         return "f64"
-    return "f64" if args.precision == "f64" else "f64 state / f32 force terms"
+    return "f64"
 
 
 def workload_config(args, world, reference_sample=None):
@@ -289,7 +291,7 @@ def workload_config(args, world, reference_sample=None):
                      ("" if args.envs_per_gpu == 65536 else " (resized)")),
         "envs_per_gpu": args.envs_per_gpu, "envs_total": args.envs_per_gpu * world,
         "sub_steps_per_env_step": 1 if kin else 20, "max_episode_steps": 500 if kin else 1000, "auto_reset": True,
-        "precision": args.precision, "obstacle_table": "f32" if args.obstacles_f32 else "f64",
+        "precision": "f64", "obstacle_table": "f32" if args.obstacles_f32 else "f64",
         "sharding": f"contiguous env-index ranges over {world} GPU(s), no data-path collective",
         "actions": "uniform in the action box, pre-staged on device",
         "l2": f"{args.batches} rotating env batches per GPU (consecutive steps touch different state; working set > 126 MB L2)",
@@ -300,12 +302,112 @@ def workload_config(args, world, reference_sample=None):
 
 
 # ------------------------------------------------------------------------------------------------
+class Workload:
+    """`batches` independent env shards of n envs on one GPU (rotated so that consecutive steps touch different state:
+    working set > L2), pre-staged actions, and the K-step block in three forms: a Python loop of VecEnv.step_tensor()
+    calls, the same loop captured once into a CUDA graph, and a timed replay of either."""
+
+    def __init__(self, usv, torch, dev, local_rank, n, lo, args, env_id, no_obstacles, obstacles_f32, batches, seed):
+        self.torch, self.dev, self.n = torch, dev, n
+        self.envs = []
+        for b in range(batches):
+            e = usv.UsvGpuVecEnv(n, device=local_rank, seed=seed + b, global_env_offset=lo,
+                                 ignore_obstacles=bool(no_obstacles), obstacles_f32=bool(obstacles_f32),
+                                 info_mode="lazy", env_id=env_id)
+            e.reset_tensor()
+            self.envs.append(e)
+        self.A = 8
+        gen = torch.Generator(device=dev).manual_seed(1234 + lo)
+        if env_id in LEGACY_IDS:
+            self.acts = ((torch.rand((self.A, n, 1), generator=gen, device=dev) - 0.5) * 3.141592653589793).contiguous()
+        else:
+            a = torch.rand((self.A, n, 2), generator=gen, device=dev)
+            self.acts = (a * torch.tensor([0.8, 2.0], device=dev) + torch.tensor([0.2, -1.0], device=dev)).contiguous()
+        self.graph, self.graph_steps = None, 0
+
+    def step(self, k):
+        self.envs[k % len(self.envs)].step_tensor(self.acts[k % self.A])
+
+    def loop(self, steps):
+        for k in range(steps):
+            self.step(k)
+
+    def capture(self, steps):
+        """The K-step block as ONE CUDA graph: the host enqueues it with a single call, so the timed region cannot be
+        bound by the Python / ctypes launch loop.  Every step is still its own kernel launch(es) and the
+        state round-trips HBM between steps -- nothing is fused across steps."""
+        torch = self.torch
+        torch.cuda.synchronize(self.dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            self.loop(steps)
+        self.graph, self.graph_steps = g, steps
+        return g
+
+    def preroll(self, steps_per_batch):
+        """untimed steps so that episodes are spread over their whole life (steady-state mix of resets, collisions,
+        out-of-bounds exits); replayed through a graph of one rotation to keep it short"""
+        for k in range(len(self.envs)):  # one eager step per shard: nothing is loaded lazily inside a capture
+            self.step(k)
+        if steps_per_batch <= 0:
+            return
+        per = len(self.envs) * self.A  # one full rotation of shards x action slabs
+        g = self.capture(per)
+        for _ in range(max(1, (steps_per_batch * len(self.envs) + per - 1) // per)):
+            g.replay()
+        self.torch.cuda.synchronize(self.dev)
+
+    def close(self):
+        self.graph = None
+        for e in self.envs:
+            e.close()
+
+
+def timed_blocks(torch, dist, dev, world, launch, repeats):
+    """`repeats` times: barrier + synchronize, CUDA events around launch(), synchronize + barrier.  Returns per repeat the
+    device ms (max over ranks) and this rank's host seconds spent inside launch() (enqueue time)."""
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    ms_max, ms_own, host_s = [], [], []
+    for _ in range(repeats):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync_all()
+        ev0.record()
+        t0 = time.perf_counter()
+        launch()
+        host_s.append(time.perf_counter() - t0)
+        ev1.record()
+        sync_all()
+        ms = ev0.elapsed_time(ev1)
+        ms_own.append(ms)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_max.append(float(t.item()))
+    return ms_max, ms_own, host_s
+
+
+def ncu_metrics():
+    """What the committed ncu capture of the step kernel(s) says (profiles/ncu_metrics.json, written by
+    tools/ncu_summary.py from the .ncu-rep of the same bench command): FP64 / issue-slot figures for the bench line."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_metrics.json")) as f:
+            return json.load(f)
+    except Exception:  # noqa: BLE001
+        return {}
+
+
 def run_ours(args, rank, local_rank, world):
     import numpy as np
     import torch
     import torch.distributed as dist
 
     import gym_usv_b200 as usv
+    from gym_usv_b200 import _native as nat
     from gym_usv_b200.sharding import reduce_episode_stats, shard_range
 
     if not torch.cuda.is_available():
@@ -315,66 +417,48 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    n = args.envs_per_gpu
-    lo, hi = shard_range(n * world, rank, world)
-    envs = []
-    for b in range(args.batches):
-        e = usv.UsvGpuVecEnv(hi - lo, device=local_rank, seed=args.seed + b, global_env_offset=lo,
-                             ignore_obstacles=bool(args.no_obstacles), obstacles_f32=bool(args.obstacles_f32),
-                             precision=args.precision, info_mode="lazy", env_id=args.env)
-        e.reset_tensor()
-        envs.append(e)
-    A = 8
-    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    legacy = args.env in LEGACY_IDS
-    if legacy:
-        acts = ((torch.rand((A, n, 1), generator=gen, device=dev) - 0.5) * float(np.pi)).contiguous()
-    else:
-        acts = torch.rand((A, n, 2), generator=gen, device=dev)
-        acts = (acts * torch.tensor([0.8, 2.0], device=dev) + torch.tensor([0.2, -1.0], device=dev)).contiguous()
-
-    def sync_all():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize(dev)
-
-    def do_step(k):
-        envs[k % len(envs)].step_tensor(acts[k % A])
-
-    # pre-roll so that episodes are spread over their whole life (steady-state mix of resets and obstacle hits)
-    for k in range(args.preroll * len(envs)):
-        do_step(k)
-    for k in range(args.warmup):
-        do_step(k)
-    sync_all()
+    # clocks are sampled from before the warm-up to after the last timed block (not started inside the timed window)
     try:
         uuid = "GPU-" + str(torch.cuda.get_device_properties(dev).uuid)
     except Exception:  # noqa: BLE001
         uuid = None
     sampler = ClockSampler(local_rank, uuid)
     sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_wall0 = time.perf_counter()
-    ev0.record()
-    for k in range(args.steps):
-        do_step(k)
-    ev1.record()
-    sync_all()
-    t_wall = time.perf_counter() - t_wall0
-    ms = ev0.elapsed_time(ev1)
-    clocks = sampler.stop()
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = n * world * args.steps / (ms_max * 1e-3)
+
+    n = args.envs_per_gpu
+    lo, hi = shard_range(n * world, rank, world)
+    legacy = args.env in LEGACY_IDS
+    wl = Workload(usv, torch, dev, local_rank, hi - lo, lo, args, args.env, args.no_obstacles, args.obstacles_f32,
+                  args.batches, args.seed)
+    envs, acts, A = wl.envs, wl.acts, wl.A
+    fused = (not legacy) and args.env == "usv-asmc-simple" and os.environ.get("USVGPU_STEP", "fused") != "split"
+    launches_per_step = 1 if (legacy or fused) else 2
+
+    wl.preroll(args.preroll)
+    wl.loop(args.warmup)  # W untimed warm-up steps through the public per-step call
+    torch.cuda.synchronize(dev)
+
+    # ---- value: K steps, device-resident actions, CUDA events, max over ranks, median of R blocks -----------------
+    K, R = args.steps, max(1, args.repeats)
+    graph = wl.capture(K)
+    graph.replay()  # one untimed replay (graph upload)
+    ms_graph, ms_graph_own, host_graph = timed_blocks(torch, dist, dev, world, graph.replay, R)
+    ms_loop, ms_loop_own, host_loop = timed_blocks(torch, dist, dev, world, lambda: wl.loop(K), R)
+    ms_block = statistics.median(ms_graph)
+    value = n * world * K / (ms_block * 1e-3)
+    value_loop = n * world * K / (statistics.median(ms_loop) * 1e-3)
 
     # ---- e2e: host numpy in / host numpy out through VecEnv.step() -----------------------------------
-    # usvgpu_step_host: pinned H2D of the actions, the two kernels, D2H of observations / rewards / flags into
+    # usvgpu_step_host: pinned H2D of the actions, the kernels, D2H of observations / rewards / flags into
     # page-locked host buffers, stream sync, terminal observations of the finished envs -- all inside the timed region.
     e2e_steps = max(3, min(args.steps, args.e2e_steps))
     h_acts = np.ascontiguousarray(acts.cpu().numpy())
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
 
     def e2e_run(mapped):
         for e in envs:
@@ -394,7 +478,9 @@ def run_ours(args, rank, local_rank, world):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         return n * world * e2e_steps / float(tt.item())
 
-    e2e_variants = {"staged_d2h": e2e_run(False), "mapped_obs_stores": e2e_run(True)}
+    e2e_variants = {"staged_d2h": e2e_run(False)}
+    if args.mapped_obs or args.e2e_all:
+        e2e_variants["mapped_obs_stores"] = e2e_run(True)
     for e in envs:
         e.mapped_obs = bool(args.mapped_obs)
     e2e_value = e2e_variants["mapped_obs_stores" if args.mapped_obs else "staged_d2h"]
@@ -414,46 +500,115 @@ def run_ours(args, rank, local_rank, world):
         s = e.episode_stats()
         stats = {k: stats[k] + s[k] for k in stats}
     stats = reduce_episode_stats(stats, device=dev)
+    wl.close()
 
+    # ---- measured FP64 issue rate of this GPU (the binding resource of the float64 path) ----------------
+    dfma = C_double = None
+    if rank == 0:
+        import ctypes as C
+        C_double = C.c_double()
+        nat.check(nat.lib().usvgpu_fp64_peak(local_rank, 148 * 8, 20000, C.byref(C_double), None))
+        dfma = float(C_double.value)
+
+    # ---- driver-visible evidence for the other BASELINE.json configs (CUDA-event timed, not the headline) ---------
+    extra = {}
+    if not args.no_extra and args.env == "usv-asmc-simple" and not args.no_obstacles:
+        def side_run(tag, env_id, n_envs, no_obst, f32, batches, steps, label):
+            slo, shi = shard_range(n_envs * world if tag != "configs3" else n_envs, rank, world)
+            w2 = Workload(usv, torch, dev, local_rank, shi - slo, slo, args, env_id, no_obst, f32, batches, args.seed + 100)
+            w2.preroll(8)
+            g2 = w2.capture(steps)
+            g2.replay()
+            msx, _, _ = timed_blocks(torch, dist, dev, world, g2.replay, 3)
+            tt = torch.tensor([float(shi - slo)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tt)
+            total = float(tt.item())
+            m = statistics.median(msx)
+            w2.close()
+            extra[tag] = {"workload": label, "envs_total": int(total), "steps": steps, "ms_per_step": m / steps,
+                          "value": total * steps / (m * 1e-3), "unit": UNIT}
+
+        side_run("configs1", "usv-asmc-simple", 4096, True, args.obstacles_f32, 1, 200,
+                 "BASELINE.json configs[1]: 4096 lock-step envs per GPU, path following without obstacles (ignore_obstacles), ASMC")
+        side_run("configs1_legacy", "usv-asmc-v0", 4096, True, args.obstacles_f32, 1, 200,
+                 "configs[1] secondary reading: usv-asmc-v0 (UsvAsmcEnv, one sub-step per step), 4096 envs per GPU")
+        side_run("configs3", "usv-asmc-simple", 1048576, False, args.obstacles_f32, 1, 12,
+                 f"BASELINE.json configs[3]: 1 048 576 envs with obstacles in total, sharded over {world} GPU(s) by env index range")
+        side_run("f64_obstacle_table", "usv-asmc-simple", args.envs_per_gpu, False, 0, args.batches, K,
+                 "the headline workload with the API's default float64 obstacle table (896-byte sensor-input rows)")
+
+    clocks = sampler.stop()
     if rank == 0:
         peak, peak_src = measured_peaks()
         abytes = algorithmic_bytes(not args.no_obstacles, bool(args.obstacles_f32))
-        step_s = (ms * 1e-3) / args.steps  # rank-0 device time per step (two kernels)
+        survey_bytes = SURVEY_BYTES_F64_STATE["obstacles" if not args.no_obstacles else "no_obstacles"]
+        step_s = (ms_block * 1e-3) / K
         kb = kernel_bytes(not args.no_obstacles, bool(args.obstacles_f32), args.env == "usv-simple")
         if args.env == "usv-simple":
             abytes -= 2 * 14 * 8
         if legacy:
-            abytes = legacy_bytes(args.env)
+            abytes = survey_bytes = legacy_bytes(args.env)
             kb = {legacy_kernel(args.env): abytes, "-": 0}
+        elif fused:
+            kb = {"usv::step_fused_kernel": survey_bytes, "-": 0}
         knames = list(kb)
         dom = 0 if kms[0] >= kms[1] else 1
         dom_s = kms[dom] * 1e-3
         achieved = kb[knames[dom]] * n / dom_s / 1e9
+        nm = ncu_metrics()
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": args.warmup, "ms_per_step": ms_block / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": dtype_of(args),
             "data": "synthetic", "config": workload_config(args, world),
+            "timing": {"mode": "the K-step block replayed as one CUDA graph (one host call per block; one kernel launch per "
+                               "step inside it); CUDA events around the block, barrier + synchronize on both sides, max "
+                               "over ranks, median of `repeats` blocks",
+                       "repeats": R, "block_ms_max_over_ranks": ms_graph, "block_ms_rank0": ms_graph_own,
+                       "host_enqueue_us_per_step": 1e6 * statistics.median(host_graph) / K,
+                       "python_loop": {"value": value_loop, "block_ms_max_over_ranks": ms_loop,
+                                       "host_enqueue_us_per_step": 1e6 * statistics.median(host_loop) / K,
+                                       "what": "the same K steps as K VecEnv.step_tensor() calls (Python -> ctypes -> launch)"}},
             "sub_steps_per_sec": value * (1 if (legacy or args.env == "usv-simple") else 20),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "variants": e2e_variants,
                     "api": "UsvGpuVecEnv.step(np.ndarray) -> np.ndarray obs/rew/dones + infos of done envs "
                            "(usvgpu_step_host: page-locked host buffers, H2D + kernels + D2H + sync per step)"},
-            "gpu_launches": (1 if legacy else 2) * args.steps,
+            "gpu_launches": launches_per_step * K,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(knames[dom], n), "peak_source": peak_src, "kernel": knames[dom],
-                         "algorithmic_bytes_per_env_step": kb[knames[dom]], "launch_us": dom_s * 1e6,
+                         "algorithmic_bytes_per_env_step": kb[knames[dom]],
+                         "bytes_source": "SURVEY.md 8d, float64 state" if (fused or legacy) else "per-kernel share, DESIGN.md 6",
+                         "launch_us": dom_s * 1e6,
                          "kernels_us": {knames[0]: kms[0] * 1e3, knames[1]: kms[1] * 1e3},
                          "kernels_bytes_per_env_step": kb,
-                         "whole_step": {"algorithmic_bytes_per_env_step": abytes, "us": step_s * 1e6,
-                                        "achieved": abytes * n / step_s / 1e9, "frac": abytes * n / step_s / 1e9 / peak},
-                         "note": (("one kernel per step; float32 SoA state" if args.env == "usv-asmc-v0" else
-                                   "one kernel per step; float64 SoA state") if legacy else
-                                  "both kernels are float64-issue bound, not HBM bound: see DESIGN.md and profiles/")},
+                         "whole_step": {"algorithmic_bytes_per_env_step": survey_bytes, "own_count_bytes": abytes,
+                                        "us": step_s * 1e6, "achieved": survey_bytes * n / step_s / 1e9,
+                                        "frac": survey_bytes * n / step_s / 1e9 / peak},
+                         "binding_resource": "issue slots + FP64 pipe, not HBM: see roofline_fp64 (float64 is the "
+                                             "reference's precision and parity needs it, DESIGN.md 5)"},
+            "targets": {"north_star_env_steps_per_s_8gpu": 1e10, "north_star_hbm_frac": 0.60,
+                        "per_gpu_needed": 1.25e9, "per_gpu_measured": value / world,
+                        "met_throughput_per_gpu": bool(value / world >= 1.25e9),
+                        "met_hbm_frac": bool(survey_bytes * n / step_s / 1e9 / peak >= 0.60)},
             "clocks": clocks,
-            "host_wall_s": t_wall,
             "episode_stats": stats,
+            "episode_mix": {k: (stats[k] / max(stats["episodes"], 1)) for k in ("terminated", "out_of_bounds", "time_limit")},
         }
+        if dfma:
+            # FP64 roofline: warp-level FP64 instructions per env-step (ncu, profiles/ncu_metrics.json) x envs / step time
+            # against the measured DFMA issue rate of this GPU (usvgpu_fp64_peak, timed in this run)
+            wi = nm.get("fp64_warp_inst_per_env_step")
+            rf = {"bound": "fp64_pipe", "peak_dfma_per_s": dfma, "peak_warp_inst_per_s": dfma / 32,
+                  "fp64_warp_inst_per_env_step": wi, "source": nm.get("source")}
+            if wi:
+                rf["achieved_warp_inst_per_s"] = wi * n / step_s
+                rf["frac"] = wi * n / step_s / (dfma / 32)
+            line["roofline_fp64"] = rf
+            line["issue_slot_util"] = nm.get("issue_slot_util")
+        if extra:
+            line["extra"] = extra
         if world == 1 and not args.no_cpu_baseline:
             threads = host_threads()
             v, st, el = cpu_oracle_rate(args.ref_envs, args.cpu_budget_s, threads, bool(args.no_obstacles), args.seed,
@@ -464,8 +619,6 @@ def run_ours(args, rank, local_rank, world):
                                     "sample": f"{args.ref_envs} lock-step envs x {st} steps ({el:.1f} s), C oracle, OpenMP",
                                     "single_core_value": v1}
         print(json.dumps(line), flush=True)
-    for e in envs:
-        e.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -483,16 +636,18 @@ def _json_only_stdout():
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=600)
-    ap.add_argument("--warmup", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--repeats", type=int, default=5, help="timed K-step blocks; the median block is reported")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--env", default="usv-asmc-simple", choices=["usv-asmc-simple", "usv-simple", "usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0"])
     ap.add_argument("--envs-per-gpu", type=int, default=65536)
     ap.add_argument("--batches", type=int, default=3)
-    ap.add_argument("--preroll", type=int, default=40, help="untimed steps per batch before warm-up (episode mixing)")
+    ap.add_argument("--preroll", type=int, default=480, help="untimed steps per batch before warm-up (episode mixing)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the configs[1] / configs[3] / f64-table side measurements")
+    ap.add_argument("--e2e-all", action="store_true", help="also time the mapped-observation variant of the host face")
     ap.add_argument("--no-obstacles", action="store_true", help="configs[1] semantics (ignore_obstacles=True)")
     ap.add_argument("--obstacles-f32", type=int, default=1)
-    ap.add_argument("--precision", default="f64", choices=["f64", "mixed"])
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--e2e-steps", type=int, default=60)
     ap.add_argument("--mapped-obs", type=int, default=0, help="e2e: sensor kernel stores obs rows straight to mapped host memory")

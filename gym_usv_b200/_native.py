@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
 HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_ca.cuh", "usv_render.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
-                                             "usv_sensor.cuh", "usv_kernels.cuh", "usv_math.cuh")] + \
+                                             "usv_sensor.cuh", "usv_kernels.cuh", "usv_fused.cuh", "usv_math.cuh")] + \
           [os.path.join(_ROOT, "include", "usvgpu.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",

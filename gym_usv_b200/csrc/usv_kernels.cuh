@@ -40,10 +40,12 @@ constexpr int SENS_MIN_CTAS = USV_SENS_MIN_CTAS; // resident CTAs per SM the per
 // observation header, the reward terms that do not need the sensors, hand-over record.  Shared by 'usv-asmc-simple'
 // (KIN = false: called with a zero action after the 20 ASMC sub-steps) and 'usv-simple' (KIN = true).
 // ---------------------------------------------------------------------------------------------
+// The hand-over (Hand record + the 16 padded header columns) comes back in registers: the split kernels store it to the
+// env's sensor-input row, the fused kernel to its shared-memory ring.
 template <bool KIN>
 __device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags& fl, const long long i, const long long n,
                                              Pose& p, double& cs, double& sn, double& progress, int& steps,
-                                             const double a0, const double a1) {
+                                             const double a0, const double a1, Hand& hd, float4 (&hrow)[4]) {
     // episode constants are only needed from here on: loaded late to keep them out of the sub-step loop's registers
     double* dyn = s.dyn + i;
     progress = dyn[(long long)D_PROGRESS * n];
@@ -105,7 +107,6 @@ __device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags
     // the reference divides (x / 10, angle / pi, ...): multiplying by the rounded reciprocal differs by at
     // most one float64 ulp before the float32 rounding.  Columns 7, 8 (last_action), 10 (max_action[1]) and
     // 13 (max_acceleration[1]) are 0 for the whole life of this env.
-    float4* hrow = reinterpret_cast<float4*>(hdr_of(s, i));
     hrow[0] = make_float4((float)(p.u * 0.1), (float)(p.v * 0.1), (float)(p.r * 0.1), (float)(ang * (1.0 / PI)));
     // columns 7, 8: the PREVIOUS last_action[[0, 2]] / max_action[[0, 2]] (:338 runs before :343)
     hrow[1] = make_float4((float)(tdist * (1.0 / DIST_NORM)), (float)(ye * 0.1), (float)(vref * 0.1),
@@ -119,7 +120,6 @@ __device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags
     const double ye_reward = exp(-fmin(at, t * t));  // max(exp(-|t|), exp(-t^2)): exp is monotone
     const double angle_reward = exp(-fabs(ang));
     const double vel_reward = exp(-fabs(sqrt_k(fma(p.u, p.u, p.v * p.v)) - vref)) * 0.05;
-    Hand hd;
     hd.x = p.x;
     hd.y = p.y;
     hd.cs = cs;
@@ -128,17 +128,23 @@ __device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags
     if (KIN) hd.rew_part += -((fabs(la0 - c0) + fabs(la2 - c2)) / 2) * 0.15;  // delta_action_reward, :176
     hd.flags = (oob ? FLG_OOB : 0u) | (tlimit ? FLG_TLIMIT : 0u);
     hd.pad = 0u;
+}
+
+__device__ __forceinline__ void store_handover(const StatePtrs& s, const long long i, const Hand& hd, const float4 (&hrow)[4]) {
     *hand_of(s, i) = hd;
+    float4* dst = reinterpret_cast<float4*>(hdr_of(s, i));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) dst[k] = hrow[k];
 }
 
 // ---------------------------------------------------------------------------------------------
+// One env's share of dynamics_kernel / of the fused kernel's dynamics role: load the SoA columns, 2 x UsvAsmc.compute
+// = 20 sub-steps (simple_env_asmc.py:19-25), wrapper_tail, store the columns.  The hand-over comes back in registers.
+// ---------------------------------------------------------------------------------------------
 template <bool PERTURB>
-__global__ void __launch_bounds__(DYN_B, DYN_MIN_CTAS)
-dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
+__device__ __forceinline__ void dyn_env(const StatePtrs& s, const StepFlags& fl, const float* __restrict__ actions,
+                                        const long long i, Hand& hd, float4 (&hrow)[4]) {
     const long long n = s.n;
-    const long long i = fl.lo + (long long)blockIdx.x * DYN_B + threadIdx.x;
-    if (i >= fl.hi) return;
-
     // ---- load state (coalesced SoA columns) -------------------------------------------------
     double* dyn = s.dyn + i;
     Pose p;
@@ -177,7 +183,7 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     for (int k = 0; k < USV_DYN_SUBSTEPS; ++k) asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
 
     double progress;
-    wrapper_tail<false>(s, fl, i, n, p, cs, sn, progress, steps, 0.0, 0.0);
+    wrapper_tail<false>(s, fl, i, n, p, cs, sn, progress, steps, 0.0, 0.0, hd, hrow);
     if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.psi))) atomicAdd(&s.stats->nonfinite, 1ull);
 
     // ---- store state ---------------------------------------------------------------------------
@@ -207,6 +213,17 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     s.steps[i] = steps;
 }
 
+template <bool PERTURB>
+__global__ void __launch_bounds__(DYN_B, DYN_MIN_CTAS)
+dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
+    const long long i = fl.lo + (long long)blockIdx.x * DYN_B + threadIdx.x;
+    if (i >= fl.hi) return;
+    Hand hd;
+    float4 hrow[4];
+    dyn_env<PERTURB>(s, fl, actions, i, hd, hrow);
+    store_handover(s, i, hd, hrow);
+}
+
 // ---------------------------------------------------------------------------------------------
 // 'usv-simple' (UsvSimpleEnv.step, simple_env.py:310-346; the env train_test/sb3_train_vec.py:55 trains on): the
 // action drives the kinematic update directly, no controller.  Thread per env, 9 float64 columns in, 9 out, then the
@@ -234,7 +251,10 @@ kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     double sn, cs;
     sincos(p.psi, &sn, &cs);  // theta = position[2] before the update, simple_env.py:321
     double progress;
-    wrapper_tail<true>(s, fl, i, n, p, cs, sn, progress, steps, (double)af.x, (double)af.y);
+    Hand hd;
+    float4 hrow[4];
+    wrapper_tail<true>(s, fl, i, n, p, cs, sn, progress, steps, (double)af.x, (double)af.y, hd, hrow);
+    store_handover(s, i, hd, hrow);
     if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.psi))) atomicAdd(&s.stats->nonfinite, 1ull);
     dyn[(long long)D_X * n] = p.x;
     dyn[(long long)D_Y * n] = p.y;
@@ -244,6 +264,57 @@ kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     dyn[(long long)D_R * n] = p.r;
     dyn[(long long)D_PROGRESS * n] = progress;
     s.steps[i] = steps;
+}
+
+// ---------------------------------------------------------------------------------------------
+// What a warp does with one env once the sensors are known: flags (simple_env.py:334-336 + TimeLimit), reward
+// (:150-201), episode statistics, the observation row(s) -- 15 header columns + 128 sensor columns, contiguous in
+// obs[N][143] -- and the SB3 auto-reset (usv_reset.cuh).  head: observation column `lane` (lane < 15); sens[p]: column
+// 15 + lane + 32 p.  Shared by sensor_kernel and step_fused_kernel.
+// ---------------------------------------------------------------------------------------------
+template <typename ObT>
+__device__ __forceinline__ void finish_env(const StatePtrs& s, const StepFlags& fl, const long long i, const int lane,
+                                           float head, const float (&sens)[4], const bool term, const bool collided,
+                                           const double rew_part, const unsigned flags, float* __restrict__ obs,
+                                           float* __restrict__ reward, uint8_t* __restrict__ terminated,
+                                           uint8_t* __restrict__ truncated, float* __restrict__ terminal_obs) {
+    const bool oob = flags & FLG_OOB, tlimit = flags & FLG_TLIMIT;
+    const bool trunc = oob || tlimit;
+    const bool done = term || trunc;
+    const double rew = (collided ? -20.0 : 0.0) + rew_part;
+    if (lane == 0) {
+        reward[i] = (float)rew;
+        terminated[i] = term ? 1 : 0;
+        truncated[i] = trunc ? 1 : 0;
+        if (done) {
+            const double ep_ret = s.ep_return[i] + rew;
+            DeviceStats* ds = s.stats;
+            const double ep_len = (double)s.steps[i];
+            s.ep_done[i] = make_double2(ep_ret, ep_len);
+            atomicAdd(&ds->return_sum, ep_ret);
+            atomicAdd(&ds->length_sum, ep_len);
+            atomicAdd(&ds->episodes, 1ull);
+            if (term) atomicAdd(&ds->terminated, 1ull);
+            if (oob) atomicAdd(&ds->out_of_bounds, 1ull);
+            if (tlimit && !term && !oob) atomicAdd(&ds->time_limit, 1ull);
+            if (!fl.auto_reset) s.ep_return[i] = ep_ret;  // the reset below zeroes it otherwise
+        } else {
+            atomicAdd(&s.ep_return[i], rew);  // result unused: a fire-and-forget reduction, no load to wait for
+        }
+    }
+    float* orow = obs + i * OBS_DIM;
+    if (done && fl.auto_reset) {
+        if (terminal_obs) {
+            float* trow = terminal_obs + i * OBS_DIM;
+            if (lane < HDR) trow[lane] = head;
+#pragma unroll
+            for (int p = 0; p < 4; ++p) trow[HDR + lane + 32 * p] = sens[p];
+        }
+        head = reset_env_warp<ObT>(s, i, lane);  // header <- reset obs; sensor columns stay (simple_env.py:302)
+    }
+    if (lane < HDR) orow[lane] = head;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) orow[HDR + lane + 32 * p] = sens[p];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -287,7 +358,7 @@ __global__ void __launch_bounds__(SENS_WARPS * 32, SENS_MIN_CTAS)
 sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restrict__ reward,
               uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated, float* __restrict__ terminal_obs) {
     __shared__ double2 raytab[N_SENS];
-    __shared__ SensorScratch scratch[OBST ? SENS_WARPS : 1];
+    __shared__ SensorScratch<float> scratch[OBST ? SENS_WARPS : 1];
     __shared__ SensorStage<ObT> stage[SENS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long n = fl.hi;
@@ -297,7 +368,7 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
     if (i < n) sensor_prefetch<OBST, ObT>(st, s, i, lane);
     if (OBST) {
         if (tid < N_SENS) raytab[tid] = s.raytab[tid];
-        if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = SENSOR_MAX_RANGE;  // the "no hit" slot
+        if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<float>::no_hit();  // the "no hit" slot
         __syncthreads();
     }
     if (i >= n) return;
@@ -307,7 +378,7 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
         __pipeline_wait_prior(0);
         __syncwarp();
         const Hand hd = st.hd;
-        float head = st.head[lane & (HDR_PAD - 1)];
+        const float head = st.head[lane & (HDR_PAD - 1)];
         const int nob = OBST ? st.nob : 0;
         const double ox = (double)st.obst[lane], oy = (double)st.obst[MAX_OBST + lane];
         const double rr = (double)st.obst[2 * MAX_OBST + lane];
@@ -318,55 +389,9 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
         // ---- sensors, simple_env.py:203-226 ----------------------------------------------------
         float sens[4] = {1.0f, 1.0f, 1.0f, 1.0f};  // max range / 100 (simple_env.py:83); ignore_obstacles: all rays (:222-224)
         bool term = false, collided = false;
-        if (OBST) {
-            double out[4];
-            sensor_warp(scratch[warp], raytab, lane, nob, hd.x, hd.y, hd.cs, hd.sn, ox, oy, rr, out, 0.05, term, 0.2,
-                        collided);
-#pragma unroll
-            for (int p = 0; p < 4; ++p) sens[p] = (float)(out[p] * 0.01);  // SENSOR_MAX_RANGE * 0.01 rounds to 1.0f
-        }
-
-        // ---- flags (simple_env.py:334-336 + TimeLimit), reward (:150-201) -----------------------
-        const bool oob = hd.flags & FLG_OOB, tlimit = hd.flags & FLG_TLIMIT;
-        const bool trunc = oob || tlimit;
-        const bool done = term || trunc;
-        const double rew = (collided ? -20.0 : 0.0) + hd.rew_part;
-        if (lane == 0) {
-            reward[i] = (float)rew;
-            terminated[i] = term ? 1 : 0;
-            truncated[i] = trunc ? 1 : 0;
-            if (done) {
-                const double ep_ret = s.ep_return[i] + rew;
-                DeviceStats* ds = s.stats;
-                const double ep_len = (double)s.steps[i];
-                s.ep_done[i] = make_double2(ep_ret, ep_len);
-                atomicAdd(&ds->return_sum, ep_ret);
-                atomicAdd(&ds->length_sum, ep_len);
-                atomicAdd(&ds->episodes, 1ull);
-                if (term) atomicAdd(&ds->terminated, 1ull);
-                if (oob) atomicAdd(&ds->out_of_bounds, 1ull);
-                if (tlimit && !term && !oob) atomicAdd(&ds->time_limit, 1ull);
-                if (!fl.auto_reset) s.ep_return[i] = ep_ret;  // the reset below zeroes it otherwise
-            } else {
-                atomicAdd(&s.ep_return[i], rew);  // result unused: a fire-and-forget reduction, no load to wait for
-            }
-        }
-
-        // ---- observation row(s): 15 header columns + 128 sensor columns, contiguous in obs[N][143] ----
-        float* orow = obs + i * OBS_DIM;
-        if (done && fl.auto_reset) {
-            if (terminal_obs) {
-                float* trow = terminal_obs + i * OBS_DIM;
-                if (lane < HDR) trow[lane] = head;
-#pragma unroll
-                for (int p = 0; p < 4; ++p) trow[HDR + lane + 32 * p] = sens[p];
-            }
-            head = reset_env_warp<ObT>(s, i, lane);  // header <- reset obs; sensor columns stay (simple_env.py:302)
-        }
-        if (lane < HDR) orow[lane] = head;
-#pragma unroll
-        for (int p = 0; p < 4; ++p) orow[HDR + lane + 32 * p] = sens[p];
-
+        if (OBST) sensor_warp<float>(scratch[warp], raytab, lane, nob, hd.x, hd.y, hd.cs, hd.sn, ox, oy, rr, sens, 0.05, term, collided);
+        finish_env<ObT>(s, fl, i, lane, head, sens, term, collided, hd.rew_part, hd.flags, obs, reward, terminated, truncated,
+                        terminal_obs);
         if (i_next >= n) break;
         i = i_next;
     }
@@ -619,10 +644,10 @@ __global__ void __launch_bounds__(SENS_WARPS * 32)
 sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const double* __restrict__ pose,
                     const double* __restrict__ obstacles, const int* __restrict__ n_obs, double* __restrict__ out) {
     __shared__ double2 raytab[N_SENS];
-    __shared__ SensorScratch scratch[SENS_WARPS];
+    __shared__ SensorScratch<double> scratch[SENS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid < N_SENS) raytab[tid] = g_raytab[tid];
-    if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = SENSOR_MAX_RANGE;
+    if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<double>::no_hit();
     __syncthreads();
     const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
     if (i >= n) return;
@@ -638,7 +663,7 @@ sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const dou
     }
     double o[4];
     bool a, b;
-    sensor_warp(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, o, 0.05, a, 0.2, b);
+    sensor_warp<double>(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, o, 0.05, a, b);
 #pragma unroll
     for (int p = 0; p < 4; ++p) out[(long long)(lane + 32 * p) * n + i] = o[p];
 }

@@ -23,6 +23,8 @@ struct MathK {
     double sin_c[3];    // -1/3!, 1/5!, -1/7!
     double cos_c[3];    // 1/4!, -1/6!, 1/8!   (-1/2! is an immediate)
     double pio2_hi, pio2_lo;
+    double ksin[6];     // fdlibm __kernel_sin S1..S6: sin r = r + r^3 (S1 + z (S2 + ...)), |r| <= pi/4
+    double kcos[6];     // fdlibm __kernel_cos C1..C6: cos r = 1 - z/2 + z^2 (C1 + z (C2 + ...))
 };
 
 __constant__ MathK MATHK = {
@@ -31,7 +33,11 @@ __constant__ MathK MATHK = {
      0.01740087944269402, -0.014851887071247204, 0.028757851367421566},
     {-1.0 / 6, 1.0 / 120, -1.0 / 5040},
     {1.0 / 24, -1.0 / 720, 1.0 / 40320},
-    1.5707963267948966, 6.123233995736766e-17};
+    1.5707963267948966, 6.123233995736766e-17,
+    {-1.66666666666666324348e-01, 8.33333333332248946124e-03, -1.98412698298579493134e-04, 2.75573137070700676789e-06,
+     -2.50507602534068634195e-08, 1.58969099521155010221e-10},
+    {4.16666666666666019037e-02, -1.38888888888741095749e-03, 2.48015872894767294178e-05, -2.75573143513906633035e-07,
+     2.08757232129817482790e-09, -1.13596475577881948265e-11}};
 
 // MUFU.RSQ64H / MUFU.RCP64H: ~20-bit seeds computed from the high word
 __device__ __forceinline__ double rsqrt_seed(double a) {
@@ -120,6 +126,35 @@ __device__ __forceinline__ double asin_k(double x) {
     double r = s + t;
     if (big) r = (MATHK.pio2_hi - 2.0 * s) - (fma(2.0, t, -MATHK.pio2_lo));
     return copysign(r, x);
+}
+
+// sin / cos of a BOUNDED argument, |x| <= 64 (the reset's angles lie in [-pi, 2 pi]): quadrant by rint(x 2/pi), two-word
+// pi/2 with fma, fdlibm kernel polynomials; <= 1 ulp of 1.0 absolute.  No range-reduction slow path, hence no call into
+// the CUDA math library: the fused step kernel runs sincos() in its register-rich dynamics role, and ptxas 12.9 crashes
+// on a library routine that is reachable from both sides of a setmaxnreg split (usv_fused.cuh).
+__device__ __forceinline__ void sincos_bounded(double x, double* sn, double* cs) {
+    const double kf = rint(x * 0.63661977236758134308);  // 2/pi
+    const int k = (int)kf;
+    double r = fma(-kf, MATHK.pio2_hi, x);
+    r = fma(-kf, MATHK.pio2_lo, r);
+    const double z = r * r;
+    const double* S = MATHK.ksin;
+    const double* C = MATHK.kcos;
+    double ps = fma(S[5], z, S[4]);
+    ps = fma(ps, z, S[3]);
+    ps = fma(ps, z, S[2]);
+    ps = fma(ps, z, S[1]);
+    ps = fma(ps, z, S[0]);
+    const double sr = fma(r * z, ps, r);
+    double pc = fma(C[5], z, C[4]);
+    pc = fma(pc, z, C[3]);
+    pc = fma(pc, z, C[2]);
+    pc = fma(pc, z, C[1]);
+    pc = fma(pc, z, C[0]);
+    const double cr = fma(z * z, pc, fma(-0.5, z, 1.0));
+    const double s1 = (k & 1) ? cr : sr, c1 = (k & 1) ? sr : cr;
+    *sn = (k & 2) ? -s1 : s1;
+    *cs = ((k + 1) & 2) ? -c1 : c1;
 }
 
 // (cs, sn) <- rotation of (cs, sn) by d, |d| <= 1/32 (Taylor to d^7 / d^8: truncation < 1e-19 relative)

@@ -24,7 +24,7 @@ __device__ __forceinline__ ResetScalars reset_scalars(const double (&un)[16]) {
     ResetScalars q;
     const double rad = sqrt(-2.0 * log(1.0 - un[0]));  // Box-Muller pair
     double sn, cs;
-    sincos(6.283185307179586 * un[1], &sn, &cs);
+    sincos_bounded(6.283185307179586 * un[1], &sn, &cs);
     q.psx = 0.5 * (rad * cs) + ENV_HI / 2;  // :234-235
     q.psy = 0.5 * (rad * sn) + ENV_HI / 2;
     // :236-237 draws a position that :238 overwrites; not drawn
@@ -32,7 +32,7 @@ __device__ __forceinline__ ResetScalars reset_scalars(const double (&un)[16]) {
     const double angle = lerp_u(-PI, PI, un[3]);       // :241
     const double dist = lerp_u(100.0, 110.0, un[4]);   // :242
     double sa, ca;
-    sincos(angle, &sa, &ca);
+    sincos_bounded(angle, &sa, &ca);
     q.pex = q.psx + ca * dist;                         // :243
     q.pey = q.psy + sa * dist;
     q.tx = lerp_u(0.0, ENV_HI, un[5]);                 // :245

@@ -10,7 +10,7 @@
 //            can touch (+-asin(r/d) around its bearing; cheap float32 approximations widened by a margin
 //            -- a few extra candidates cost a test, a missing one would be an error), clipped to the
 //            4 pi / 3 fan; a warp scan turns the wedge sizes into offsets of a compacted list of
-//            (obstacle, ray) candidate pairs (~140 per env instead of 29 x 128);
+//            (obstacle, ray) candidate pairs (~100 per env instead of 29 x 128);
 //   phase B  lane = candidate pair, 32 per pass, all lanes busy: the reference's float64 hit test; a hit
 //            stores its reading in the pair's slot and enters the ray's winner word with a shared-memory
 //            atomicMin on (order-preserving float32 key bits, top 24 | pair slot, low 8);
@@ -19,9 +19,19 @@
 // rounded keys, which is exact unless two obstacles that hit the SAME ray have keys equal to within 2^-16
 // relative: phase B detects exactly that (the atomicMin returns a word with the same key bits) and the
 // env then re-does its rays on the exact path (float64 keys, ascending slot order breaks ties like the
-// reference's stable argsort); so does an env with more than 255 candidate pairs (boat inside circles).  In the body frame the ray directions are the constant table (cos phi_i, sin phi_i),
-// so along = cos phi bx + sin phi by and perp = sin phi bx - cos phi by equal the reference's
-// expressions (usv_asmc_ca_env.py:516-518) with cos / sin (psi + phi_i) expanded.
+// reference's stable argsort); so does an env with more than 255 candidate pairs (boat inside circles).
+// In the body frame the ray directions are the constant table (cos phi_i, sin phi_i), so
+// along = cos phi bx + sin phi by and perp = sin phi bx - cos phi by equal the reference's expressions
+// (usv_asmc_ca_env.py:516-518) with cos / sin (psi + phi_i) expanded.
+//
+// Two output forms (template HT):
+//   HT = double  raw readings in metres (the unit-parity entry point usvgpu_sensors);
+//   HT = float   what the observation row stores, float32(reading * 0.01) (simple_env.py:83), rounded ONCE from the
+//                float64 reading in phase B -- phase C is then four 4-byte look-ups per lane.  The collision test
+//                "min reading < 0.2" (simple_env.py:153-156) is decided on those float32 values: float32 rounding
+//                is monotone, so v < float32(0.002) implies reading < 0.2 and v > float32(0.002) implies
+//                reading > 0.2; only v == float32(0.002) (the reading within 2.3e-8 m of 0.2) is undecided and
+//                sends the env to the exact float64 path.
 #pragma once
 #include "usv_math.cuh"
 #include "usv_state.cuh"
@@ -31,12 +41,23 @@ namespace usv {
 constexpr int PAIR_SLOTS = 256;           // slot 255 is reserved: "no hit" -> SENSOR_MAX_RANGE
 constexpr uint32_t NO_HIT = 0xFFFFFFFFu;
 
-struct SensorScratch {  // per warp
+template <typename HT>
+struct SensorScratch {  // per warp: 3.1 KB (HT = float) / 4.1 KB (double)
     double4 geo[MAX_OBST];      // bx, by (offset in the body frame), radius^2, key
     int4 rec[MAX_OBST];         // split, rbase, rbase2, key bits: pair t of this obstacle is ray t + (t < split ? rbase : rbase2)
-    double hpair[PAIR_SLOTS];   // reading of candidate pair t (valid where the pair hit)
+    HT hpair[PAIR_SLOTS];       // reading of candidate pair t (valid where the pair hit)
     uint32_t best[N_SENS];      // min over hitting obstacles of (key bits & ~255 | pair slot)
     int ne[MAX_OBST];           // slots of the obstacles that have candidates, in order
+};
+
+template <typename HT> struct Reading;
+template <> struct Reading<double> {
+    static __device__ __forceinline__ double of(double h) { return h; }
+    static __device__ __forceinline__ double no_hit() { return SENSOR_MAX_RANGE; }
+};
+template <> struct Reading<float> {
+    static __device__ __forceinline__ float of(double h) { return (float)(h * 0.01); }  // SENSOR_MAX_RANGE * 0.01 rounds to 1.0f
+    static __device__ __forceinline__ float no_hit() { return 1.0f; }
 };
 
 // atan2(y, x) to 2.1e-4 rad (7th-order odd polynomial on the folded octant)
@@ -57,28 +78,29 @@ __device__ __forceinline__ float asin_coarse(float q) {
     return q * fmaf(s, fmaf(s, fmaf(s, 15.0f / 336, 3.0f / 40), 1.0f / 6), 1.0f);
 }
 
-// the reference's test of a ray (direction t in the body frame) against an obstacle g: hit iff along >= 0,
-// delta >= 0 and the reading is inside the range (usv_asmc_ca_env.py:448-458)
-__device__ __forceinline__ bool ray_test(const double2 t, const double4 g, double& h) {
-    const double along = fma(t.x, g.x, t.y * g.y);      // :516
-    const double perp = fma(t.y, g.x, -(t.x * g.y));    // :518
-    const double delta = fma(-perp, perp, g.z);         // :453
+// the reference's test of a ray (direction t in the body frame) against an obstacle at body-frame offset (bx, by) with
+// squared radius rr2: hit iff along >= 0, delta >= 0 and the reading is inside the range (usv_asmc_ca_env.py:448-458)
+__device__ __forceinline__ bool ray_test(const double2 t, const double bx, const double by, const double rr2, double& h) {
+    const double along = fma(t.x, bx, t.y * by);      // :516
+    const double perp = fma(t.y, bx, -(t.x * by));    // :518
+    const double delta = fma(-perp, perp, rr2);       // :453
     if (!(along >= 0.0 && delta >= 0.0)) return false;  // :448, :454
     h = along - sqrt_k(delta);                          // :457
     return h < SENSOR_MAX_RANGE;                        // :458
 }
 
 // ox, oy, rr: this lane's obstacle (ignored when lane >= nob).  cps/sps = cos/sin(psi).
-// The caller sets sc.hpair[PAIR_SLOTS - 1] = SENSOR_MAX_RANGE once (the "no hit" slot).
-// out[p]: reading of ray (lane + 32 p), SENSOR_MAX_RANGE when nothing is hit.
-// min_key_lt / min_hit_lt: warp-uniform "min over obstacles of key < key_thr" and "min over rays of
-// reading < hit_thr" (simple_env.py:334 and :153-156).
-__device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __restrict__ raytab, const int lane,
+// The caller sets sc.hpair[PAIR_SLOTS - 1] = Reading<HT>::no_hit() once (the "no hit" slot).
+// out[p]: reading of ray (lane + 32 p) in the form of Reading<HT>.
+// min_key_lt: warp-uniform "min over obstacles of key < key_thr" (simple_env.py:334); min_hit_lt: warp-uniform "min over
+// rays of reading < 0.2" (simple_env.py:153-156).
+template <typename HT>
+__device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2* __restrict__ raytab, const int lane,
                                             const int nob, const double x, const double y, const double cps,
                                             const double sps, const double ox, const double oy, const double rr,
-                                            double out[4], const double key_thr, bool& min_key_lt,
-                                            const double hit_thr, bool& min_hit_lt) {
+                                            HT out[4], const double key_thr, bool& min_key_lt, bool& min_hit_lt) {
     constexpr unsigned FULL = 0xFFFFFFFFu;
+    constexpr double HIT_THR = 0.2;
     reinterpret_cast<uint4*>(sc.best)[lane] = make_uint4(NO_HIT, NO_HIT, NO_HIT, NO_HIT);
 
     // ---- phase A: lane = obstacle ---------------------------------------------------------------
@@ -133,60 +155,67 @@ __device__ __forceinline__ void sensor_warp(SensorScratch& sc, const double2* __
     // Pair t belongs to the last obstacle (among those with candidates) whose offset is <= t.  Per pass of 32
     // pairs: bit k of `starts` marks an obstacle whose list starts at pair base + k, `before` counts those that
     // started earlier, so the owner of pair base + q is ne[before + popc(starts & bits 0..q) - 1].
-    bool ambiguous = false;
-    int before = 0;
-    for (int base = 0; base < total; base += 32) {
-        const unsigned rel = (unsigned)(off - base);
-        const unsigned starts = __reduce_or_sync(FULL, (has && rel < 32u) ? (1u << rel) : 0u);
-        const int t = base + lane;
-        if (t < total) {
-            const int j = sc.ne[before + __popc(starts & (0xFFFFFFFFu >> (31 - lane))) - 1];
-            const int4 rc = sc.rec[j];
-            const int ri = t + ((t < rc.x) ? rc.y : rc.z);
-            double h;
-            if (ray_test(raytab[ri], sc.geo[j], h)) {
-                if (t < PAIR_SLOTS - 1) {
+    bool ambiguous = total > PAIR_SLOTS - 1;  // out of pair slots (boat inside circles): exact path
+    if (!ambiguous) {
+        const unsigned le_mask = 0xFFFFFFFFu >> (31 - lane);
+        int before = -1;
+        for (int base = 0; base < total; base += 32) {
+            const unsigned rel = (unsigned)(off - base);
+            const unsigned starts = __reduce_or_sync(FULL, (has && rel < 32u) ? (1u << rel) : 0u);
+            const int t = base + lane;
+            if (t < total) {
+                const int j = sc.ne[before + __popc(starts & le_mask)];
+                const int4 rc = sc.rec[j];
+                const int ri = t + ((t < rc.x) ? rc.y : rc.z);
+                const double2 bxy = *reinterpret_cast<const double2*>(&sc.geo[j]);
+                const double rr2 = sc.geo[j].z;
+                double h;
+                if (ray_test(raytab[ri], bxy.x, bxy.y, rr2, h)) {
                     const uint32_t v = (uint32_t)rc.w | (uint32_t)t;
                     const uint32_t old = atomicMin(&sc.best[ri], v);
-                    ambiguous = ambiguous || ((old >> 8) == (v >> 8));  // same ray, equal key bits: order undecided
-                    sc.hpair[t] = h;
-                } else {
-                    ambiguous = true;  // out of pair slots
+                    ambiguous = ambiguous || ((old ^ v) < 256u);  // same ray, equal key bits: order undecided
+                    sc.hpair[t] = Reading<HT>::of(h);
                 }
             }
+            before += __popc(starts);
         }
-        before += __popc(starts);
     }
-    ambiguous = __any_sync(FULL, ambiguous);
     __syncwarp();
 
     // ---- phase C: lane = ray ---------------------------------------------------------------------
-    double hmin = SENSOR_MAX_RANGE;
-    if (!ambiguous) {
+    bool hit_lt = false;
+    if (!__any_sync(FULL, ambiguous)) {
+        HT vmin = Reading<HT>::no_hit();
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            out[p] = sc.hpair[sc.best[lane + 32 * p] & 0xFFu];  // NO_HIT -> slot 255 -> SENSOR_MAX_RANGE
-            hmin = (out[p] < hmin) ? out[p] : hmin;
+            out[p] = sc.hpair[sc.best[lane + 32 * p] & 0xFFu];  // NO_HIT -> slot 255 -> no_hit()
+            vmin = (out[p] < vmin) ? out[p] : vmin;
         }
-    } else {
+        const HT thr = Reading<HT>::of(HIT_THR);
+        hit_lt = vmin < thr;
+        // float32 form: a minimum that rounds onto the threshold itself is undecided (header of this file)
+        ambiguous = (sizeof(HT) == sizeof(float)) && (vmin == thr);
+    }
+    if (__any_sync(FULL, ambiguous)) {
         // exact path: every obstacle against this lane's rays, float64 keys, strict '<' in ascending slot order
         // (the lower slot wins a tie, as the reference's stable argsort does)
+        double hmin = SENSOR_MAX_RANGE;
         for (int p = 0; p < 4; ++p) {
             const double2 tb = raytab[lane + 32 * p];
             double bkey = INFINITY, bh = SENSOR_MAX_RANGE;
             for (int j = 0; j < nob; ++j) {
                 const double4 g = sc.geo[j];
                 double h;
-                if (ray_test(tb, g, h) && g.w < bkey) {
+                if (ray_test(tb, g.x, g.y, g.z, h) && g.w < bkey) {
                     bkey = g.w;
                     bh = h;
                 }
             }
-            out[p] = bh;
+            out[p] = Reading<HT>::of(bh);
             hmin = (bh < hmin) ? bh : hmin;
         }
+        hit_lt = hmin < HIT_THR;  // readings of rays without a hit are SENSOR_MAX_RANGE
     }
-    const bool hit_lt = hmin < hit_thr;  // readings of rays without a hit are SENSOR_MAX_RANGE
     min_hit_lt = __any_sync(FULL, hit_lt);
     __syncwarp();
 }

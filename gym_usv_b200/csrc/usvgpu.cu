@@ -11,6 +11,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -18,6 +19,7 @@
 
 #include "../../include/usvgpu.h"
 #include "usv_kernels.cuh"
+#include "usv_fused.cuh"
 #include "usv_legacy.cuh"
 #include "usv_ca.cuh"
 #include "usv_render.cuh"
@@ -43,6 +45,7 @@ struct UsvGpu {
     unsigned long long host_env_steps;
     unsigned long long launches;  // kernels launched by step / rollout so far
     int sm_count;
+    bool fused;            // usv-asmc-simple without do_perturb: one warp-specialised kernel per step (usv_fused.cuh)
     // device staging for the host-buffer face (usvgpu_step_host), allocated on first use
     float* d_actions;
     float* d_obs;
@@ -104,6 +107,30 @@ static void launch_sensor(UsvGpu* h, const StepFlags& fl, float* obs, float* rew
     sensor_kernel<OBST, ObT><<<blocks, SENS_WARPS * 32, 0, st>>>(h->sp, fl, obs, reward, term, trunc, tobs);
 }
 
+template <bool OBST, typename ObT>
+static cudaError_t launch_fused(UsvGpu* h, const StepFlags& fl, const float* actions, float* obs, float* reward, uint8_t* term,
+                                uint8_t* trunc, float* tobs, cudaStream_t st) {
+    const size_t smem = sizeof(FusedSmem<ObT>);  // > 48 KB: usvgpu_create opted in (fused_opt_in)
+    const long long batches = (fl.hi - fl.lo + 31) / 32;
+    const unsigned blocks = (unsigned)(batches < h->sm_count ? batches : h->sm_count);  // persistent: one CTA per SM
+    step_fused_kernel<OBST, ObT><<<blocks, FU_THREADS, smem, st>>>(h->sp, fl, actions, obs, reward, term, trunc, tobs);
+    return cudaGetLastError();
+}
+
+template <bool OBST, typename ObT>
+static cudaError_t fused_opt_in() {
+    // setmaxnreg.inc blocks until the CTA's register pool (threads x registers at launch, plus what setmaxnreg.dec
+    // released) covers the request: the split of usv_fused.cuh must fit the pool this build was compiled with,
+    // otherwise the dynamics warps would wait forever
+    cudaFuncAttributes fa;
+    cudaError_t e = cudaFuncGetAttributes(&fa, step_fused_kernel<OBST, ObT>);
+    if (e != cudaSuccess) return e;
+    if ((long long)fa.numRegs * FU_THREADS < 32LL * (FU_D * USV_FUSED_DYN_REGS + FU_S * USV_FUSED_SENS_REGS))
+        return cudaErrorLaunchOutOfResources;
+    return cudaFuncSetAttribute(step_fused_kernel<OBST, ObT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)sizeof(FusedSmem<ObT>));
+}
+
 // One VecEnv.step(): dynamics_kernel (thread per env) then sensor_kernel (warp per env), stream-ordered.
 static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
                      float* tobs, cudaStream_t st, cudaEvent_t mid = nullptr, long long lo = 0, long long hi = -1) {
@@ -129,6 +156,19 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
             legacy_step_kernel<<<lblocks, LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term, trunc, tobs);
         cudaError_t le = cudaGetLastError();
         if (le != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("legacy step launch: ") + cudaGetErrorString(le));
+        if (mid) cudaEventRecord(mid, st);
+        h->host_env_steps += (unsigned long long)(hi - lo);
+        h->launches += 1;
+        return USV_OK;
+    }
+    if (h->fused) {  // 'usv-asmc-simple': both halves of the step in one persistent kernel
+        const bool f32t = h->cfg.obstacles_f32 != 0;
+        cudaError_t fe;
+        if (h->cfg.ignore_obstacles) fe = f32t ? launch_fused<false, float>(h, fl, actions, obs, reward, term, trunc, tobs, st)
+                                               : launch_fused<false, double>(h, fl, actions, obs, reward, term, trunc, tobs, st);
+        else fe = f32t ? launch_fused<true, float>(h, fl, actions, obs, reward, term, trunc, tobs, st)
+                       : launch_fused<true, double>(h, fl, actions, obs, reward, term, trunc, tobs, st);
+        if (fe != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("fused step launch: ") + cudaGetErrorString(fe));
         if (mid) cudaEventRecord(mid, st);
         h->host_env_steps += (unsigned long long)(hi - lo);
         h->launches += 1;
@@ -213,6 +253,11 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->launches = 0;
     h->obst_elem = cfg->obstacles_f32 ? sizeof(float) : sizeof(double);
     h->sm_count = 148;
+    {   // USVGPU_STEP=split keeps the two-kernel step (dynamics_kernel + sensor_kernel) for A/B runs
+        const char* mode = getenv("USVGPU_STEP");
+        const bool want_fused = !(mode && strcmp(mode, "split") == 0);
+        h->fused = want_fused && cfg->env_kind == USV_ENV_ASMC_SIMPLE && !cfg->do_perturb;
+    }
     h->d_actions = h->d_obs = h->d_tobs = h->d_reward = h->h_rows = nullptr;
     h->d_flags = nullptr;
     h->h_idx = nullptr;
@@ -270,6 +315,11 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     double2* rt = nullptr;
     alloc((void**)&rt, N_SENS * sizeof(double2));
     h->sp.raytab = rt;
+    if (e == cudaSuccess && h->fused) {  // the fused kernel's shared-memory block is larger than the 48 KB default
+        const bool f32t = cfg->obstacles_f32 != 0;
+        e = cfg->ignore_obstacles ? (f32t ? fused_opt_in<false, float>() : fused_opt_in<false, double>())
+                                  : (f32t ? fused_opt_in<true, float>() : fused_opt_in<true, double>());
+    }
     if (e == cudaSuccess) e = cudaMemset(h->sp.episode, 0xFF, n * sizeof(int));  // episode = -1 before the first reset
     if (e == cudaSuccess) {
         double2 t[N_SENS];
