@@ -6,6 +6,7 @@ calls raise.  ``build()`` compiles the library in-tree with nvcc for sm_100a.
 from __future__ import annotations
 
 import ctypes as C
+import hashlib
 import os
 import shutil
 import subprocess
@@ -16,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
 HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_ca.cuh", "usv_render.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
-                                             "usv_sensor.cuh", "usv_kernels.cuh", "usv_fused.cuh", "usv_math.cuh")] + \
+                                             "usv_sensor.cuh", "usv_kernels.cuh", "usv_math.cuh")] + \
           [os.path.join(_ROOT, "include", "usvgpu.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
@@ -75,26 +76,53 @@ class UsvStats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+HASH_PATH = LIB_PATH + ".hash"   # sidecar: the source hash the binary was built from (also compiled into it)
+
+
+def source_hash() -> str:
+    """sha256 (first 16 hex digits) over the CUDA sources and headers of this tree: `usvgpu_source_hash()` of the
+    loaded library must return the same string, which makes "the tested binary is this tree" checkable."""
+    h = hashlib.sha256()
+    for path in sorted(SOURCES + HEADERS):
+        h.update(os.path.basename(path).encode())
+        with open(path, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def _nvcc():
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    return nvcc if os.path.exists(nvcc) else None
+
+
 def _stale() -> bool:
-    if not os.path.exists(LIB_PATH):
+    """True when libusvgpu.so is missing or was built from other sources than the ones in this tree."""
+    if not os.path.exists(LIB_PATH) or not os.path.exists(HASH_PATH):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    return any(os.path.exists(s) and os.path.getmtime(s) > t for s in SOURCES + HEADERS)
+    try:
+        with open(HASH_PATH) as f:
+            return f.read().strip() != source_hash()
+    except OSError:
+        return True
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     """nvcc -gencode arch=compute_100a,code=sm_100a ... -> gym_usv_b200/libusvgpu.so (in-tree)."""
     if not force and not _stale():
         return LIB_PATH
-    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    if not os.path.exists(nvcc):
+    nvcc = _nvcc()
+    if nvcc is None:
         raise UsvError("nvcc not found and libusvgpu.so is missing or stale: cannot build the CUDA library")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + SOURCES
+    digest = source_hash()
+    cmd = [nvcc] + NVCC_FLAGS + [f'-DUSVGPU_SOURCE_HASH="{digest}"'] + (["-Xptxas", "-v"] if verbose else []) + \
+          ["-o", LIB_PATH] + SOURCES
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise UsvError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stderr)
+    with open(HASH_PATH, "w") as f:
+        f.write(digest + "\n")
     return LIB_PATH
 
 
@@ -102,6 +130,7 @@ _lib = None
 
 _SIGNATURES = {
     "usvgpu_version": (C.c_int, []),
+    "usvgpu_source_hash": (C.c_char_p, []),
     "usvgpu_last_error": (C.c_char_p, [C.c_void_p]),
     "usvgpu_create": (C.c_int, [C.POINTER(UsvConfig), C.c_int, C.c_int64, C.c_int64, C.c_uint64, C.POINTER(C.c_void_p)]),
     "usvgpu_destroy": (C.c_int, [C.c_void_p]),
@@ -134,7 +163,7 @@ _SIGNATURES = {
     "usvgpu_replay_add": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_int64,
                                     C.c_void_p, C.c_int64, C.c_void_p, C.c_int64] + [C.c_void_p] * 11),
     "usvgpu_replay_sample": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64] + [C.c_void_p] * 14),
-    "usvgpu_gae": (C.c_int, [C.c_int, C.c_int32, C.c_int64] + [C.c_void_p] * 5 + [C.c_float, C.c_float] + [C.c_void_p] * 3),
+    "usvgpu_gae": (C.c_int, [C.c_int, C.c_int32, C.c_int64] + [C.c_void_p] * 5 + [C.c_double, C.c_double] + [C.c_void_p] * 3),
     "usvgpu_math_probe": (C.c_int, [C.c_int, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_fp64_peak": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.c_void_p]),
 }
@@ -143,18 +172,33 @@ EXPORTS = tuple(_SIGNATURES)
 
 
 def lib():
-    """Load libusvgpu.so (never builds implicitly on a box without the .so AND without nvcc)."""
+    """Load libusvgpu.so.  A binary that is missing or was built from other sources than this tree's is rebuilt when
+    nvcc is here; without nvcc a stale binary is an error, not a silent mismatch (USVGPU_LIB, an alternative build of
+    the same ABI for A/B experiments, is loaded as it is)."""
     global _lib
     if _lib is None:
-        path = os.environ.get("USVGPU_LIB", LIB_PATH)  # experiments: an alternative build of the same ABI
-        if path == LIB_PATH and not os.path.exists(LIB_PATH):
+        path = os.environ.get("USVGPU_LIB", LIB_PATH)
+        if path == LIB_PATH and _stale():
+            if _nvcc() is None:
+                raise UsvError("libusvgpu.so is missing or was not built from this tree's sources, and nvcc is not "
+                               "here to rebuild it (python -c 'import __graft_entry__ as g; g.build()')")
             build()
         L = C.CDLL(path)
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(L, name)
             fn.restype, fn.argtypes = res, args
+        if path == LIB_PATH and L.usvgpu_source_hash().decode() != source_hash():
+            raise UsvError("libusvgpu.so reports another source hash than this tree's: rebuild it")
         _lib = L
     return _lib
+
+
+def device_index(device) -> int:
+    """CUDA ordinal of a torch device; a bare "cuda" (index None) means the CURRENT device, not device 0."""
+    if device.index is not None:
+        return int(device.index)
+    import torch
+    return int(torch.cuda.current_device())
 
 
 def check(rc: int, handle=None) -> None:

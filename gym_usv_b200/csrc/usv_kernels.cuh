@@ -23,6 +23,13 @@ namespace usv {
 #ifndef USV_DYN_SUBSTEPS
 #define USV_DYN_SUBSTEPS 20  // 2 x UsvAsmc.compute; other values only for timing experiments (tools/time_step.py)
 #endif
+#ifndef USV_DYN_UNROLL
+#define USV_DYN_UNROLL 1
+#endif
+#ifndef USV_DYN_UNROLL
+#define USV_DYN_UNROLL 1
+#endif
+constexpr int DYN_UNROLL = USV_DYN_UNROLL;  // sub-steps per trip of the loop in dyn_env
 constexpr int DYN_B = 32;        // threads (= envs) per CTA of the dynamics kernel: one warp, so that the 2048 warps of a
                                  // 65 536-env shard spread evenly over the 148 SMs (13.8 per SM)
 constexpr int DYN_MIN_CTAS = 16; // all of them resident at once (<= 128 registers): no second, nearly empty wave
@@ -47,6 +54,8 @@ __device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags
                                              Pose& p, double& cs, double& sn, double& progress, int& steps,
                                              const double a0, const double a1, Hand& hd, float4 (&hrow)[4]) {
     // episode constants are only needed from here on: loaded late to keep them out of the sub-step loop's registers
+    // (the wait for them is hidden by the other warps of the sub-partition, which are still inside their loops:
+    // stashing them in shared memory with cp.async at kernel start, r02d, left the kernel's time unchanged)
     double* dyn = s.dyn + i;
     progress = dyn[(long long)D_PROGRESS * n];
     const double* epi = s.epi + i;
@@ -179,7 +188,7 @@ __device__ __forceinline__ void dyn_env(const StatePtrs& s, const StepFlags& fl,
     const long long pstep0 = (long long)steps * 20;
     double sn, cs;
     sincos(p.psi, &sn, &cs);  // carried through the sub-steps by small rotations (usv_math.cuh)
-#pragma unroll 1
+#pragma unroll DYN_UNROLL
     for (int k = 0; k < USV_DYN_SUBSTEPS; ++k) asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
 
     double progress;
@@ -270,10 +279,11 @@ kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
 // What a warp does with one env once the sensors are known: flags (simple_env.py:334-336 + TimeLimit), reward
 // (:150-201), episode statistics, the observation row(s) -- 15 header columns + 128 sensor columns, contiguous in
 // obs[N][143] -- and the SB3 auto-reset (usv_reset.cuh).  head: observation column `lane` (lane < 15); sens[p]: column
-// 15 + lane + 32 p.  Shared by sensor_kernel and step_fused_kernel.
+// 15 + lane + 32 p.  The env index is 32-bit (usvgpu_create refuses shards of 2^31 envs or more): every address below is
+// then one IMAD.WIDE off its base pointer instead of 64-bit multiply-add chains.
 // ---------------------------------------------------------------------------------------------
 template <typename ObT>
-__device__ __forceinline__ void finish_env(const StatePtrs& s, const StepFlags& fl, const long long i, const int lane,
+__device__ __forceinline__ void finish_env(const StatePtrs& s, const StepFlags& fl, const unsigned i, const int lane,
                                            float head, const float (&sens)[4], const bool term, const bool collided,
                                            const double rew_part, const unsigned flags, float* __restrict__ obs,
                                            float* __restrict__ reward, uint8_t* __restrict__ terminated,
@@ -302,10 +312,10 @@ __device__ __forceinline__ void finish_env(const StatePtrs& s, const StepFlags& 
             atomicAdd(&s.ep_return[i], rew);  // result unused: a fire-and-forget reduction, no load to wait for
         }
     }
-    float* orow = obs + i * OBS_DIM;
+    float* orow = obs + (size_t)i * OBS_DIM;
     if (done && fl.auto_reset) {
         if (terminal_obs) {
-            float* trow = terminal_obs + i * OBS_DIM;
+            float* trow = terminal_obs + (size_t)i * OBS_DIM;
             if (lane < HDR) trow[lane] = head;
 #pragma unroll
             for (int p = 0; p < 4; ++p) trow[HDR + lane + 32 * p] = sens[p];
@@ -335,20 +345,27 @@ static_assert(sizeof(SensorStage<double>) == sizeof(double) * OBST_ROW + SIN_TAI
 
 // The stage has the layout of the env's sensor-input row (usv_state.cuh): the prefetch is a straight 16-byte-chunk
 // copy, one cp.async per lane for a float32 table.  Without obstacles only the 128-byte tail is fetched.
+// cp.async as plain PTX: the cuda_pipeline wrappers expand to the same LDGSTS plus three dummy `@!PT LDS` per call
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 template <bool OBST, typename ObT>
-__device__ __forceinline__ void sensor_prefetch(SensorStage<ObT>& st, const StatePtrs& s, long long i, int lane) {
+__device__ __forceinline__ void sensor_prefetch(SensorStage<ObT>& st, const StatePtrs& s, unsigned i, int lane) {
     constexpr int TABLE_CHUNKS = (int)(sizeof(ObT) * OBST_ROW / 16);  // 24 (float32 table) or 48 (float64)
     constexpr int ROW_CHUNKS = TABLE_CHUNKS + SIN_TAIL_BYTES / 16;    // 32 or 56
     const char* row = reinterpret_cast<const char*>(obst_row<ObT>(s, i));
     char* dst = reinterpret_cast<char*>(&st);
     if (OBST) {
 #pragma unroll
-        for (int c = lane; c < ROW_CHUNKS; c += 32) __pipeline_memcpy_async(dst + 16 * c, row + 16 * c, 16);
+        for (int c = lane; c < ROW_CHUNKS; c += 32) cp_async16(dst + 16 * c, row + 16 * c);
     } else {
-        if (lane < SIN_TAIL_BYTES / 16)
-            __pipeline_memcpy_async(dst + 16 * (TABLE_CHUNKS + lane), row + 16 * (TABLE_CHUNKS + lane), 16);
+        if (lane < SIN_TAIL_BYTES / 16) cp_async16(dst + 16 * (TABLE_CHUNKS + lane), row + 16 * (TABLE_CHUNKS + lane));
     }
-    __pipeline_commit();
+    cp_async_commit();
 }
 
 // Persistent: the grid is sized to the machine (SENS_MIN_CTAS CTAs per SM) and every warp walks envs
@@ -361,9 +378,9 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
     __shared__ SensorScratch<float> scratch[OBST ? SENS_WARPS : 1];
     __shared__ SensorStage<ObT> stage[SENS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long n = fl.hi;
-    const long long stride = (long long)gridDim.x * SENS_WARPS;
-    long long i = fl.lo + (long long)blockIdx.x * SENS_WARPS + warp;
+    const unsigned n = (unsigned)fl.hi;
+    const unsigned stride = gridDim.x * SENS_WARPS;
+    unsigned i = (unsigned)fl.lo + blockIdx.x * SENS_WARPS + warp;
     SensorStage<ObT>& st = stage[warp];
     if (i < n) sensor_prefetch<OBST, ObT>(st, s, i, lane);
     if (OBST) {
@@ -375,7 +392,7 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
 
     for (;;) {
         // ---- this env's inputs: stage -> registers, then the stage is free for the next env -------
-        __pipeline_wait_prior(0);
+        cp_async_wait_all();
         __syncwarp();
         const Hand hd = st.hd;
         const float head = st.head[lane & (HDR_PAD - 1)];
@@ -383,7 +400,7 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
         const double ox = (double)st.obst[lane], oy = (double)st.obst[MAX_OBST + lane];
         const double rr = (double)st.obst[2 * MAX_OBST + lane];
         __syncwarp();
-        const long long i_next = i + stride;
+        const unsigned i_next = i + stride;
         if (i_next < n) sensor_prefetch<OBST, ObT>(st, s, i_next, lane);  // in flight during this env's pass
 
         // ---- sensors, simple_env.py:203-226 ----------------------------------------------------
@@ -511,12 +528,13 @@ frame_push_kernel(long long n, int obs_dim, int n_stack, int pos, float* __restr
 // ---------------------------------------------------------------------------------------------
 // stable_baselines3 RolloutBuffer.compute_returns_and_advantage (GAE(lambda)) for a device-resident rollout of
 // n_steps x N: one thread per env walks its column backwards; rows are coalesced.  float32, the operation order of
-// SB3's numpy code, no FMA contraction, so the result is bit-identical to the numpy restatement.
+// SB3's numpy code, no FMA contraction, so the result is bit-identical to the numpy restatement.  gamma_lambda is
+// float32(gamma * gae_lambda) with the product taken in float64 on the host, as numpy does with two Python floats.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 gae_kernel(int n_steps, long long n, const float* __restrict__ rewards, const float* __restrict__ values,
            const float* __restrict__ episode_starts, const float* __restrict__ last_values,
-           const uint8_t* __restrict__ last_dones, float gamma, float gae_lambda, float* __restrict__ advantages,
+           const uint8_t* __restrict__ last_dones, float gamma, float gamma_lambda, float* __restrict__ advantages,
            float* __restrict__ returns) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -529,7 +547,7 @@ gae_kernel(int n_steps, long long n, const float* __restrict__ rewards, const fl
         // delta = rewards + gamma * next_values * next_non_terminal - values
         const float delta = __fsub_rn(__fadd_rn(rewards[k], __fmul_rn(__fmul_rn(gamma, next_values), next_non_terminal)), v);
         // last_gae_lam = delta + gamma * gae_lambda * next_non_terminal * last_gae_lam
-        last_gae_lam = __fadd_rn(delta, __fmul_rn(__fmul_rn(__fmul_rn(gamma, gae_lambda), next_non_terminal), last_gae_lam));
+        last_gae_lam = __fadd_rn(delta, __fmul_rn(__fmul_rn(gamma_lambda, next_non_terminal), last_gae_lam));
         advantages[k] = last_gae_lam;
         returns[k] = __fadd_rn(last_gae_lam, v);
         next_non_terminal = 1.0f - episode_starts[k];

@@ -51,8 +51,11 @@ __device__ __forceinline__ double rcp_seed(double a) {
     return r;
 }
 
-// sqrt(a) for 0 <= a << DBL_MAX (sums of squares, |sigma|, discriminants); exactly 0 for a == 0.
-// half_rinv receives ~1/(2 sqrt a) (garbage when a == 0), which callers reuse as a free reciprocal.
+// sqrt(a) for 0 <= a << DBL_MAX (sums of squares, |sigma|, discriminants); exactly 0 for a == 0 and for subnormal a
+// (rsqrt.approx.ftz flushes a subnormal argument to zero and returns +inf: without the guard a |sigma| or a
+// discriminant that underflows would turn into NaN and poison the env's state; sqrt of a subnormal is < 1.5e-154).
+// half_rinv receives ~1/(2 sqrt a) (garbage when a is below DBL_MIN), which callers reuse as a free reciprocal.
+constexpr double SQRT_MIN_ARG = 2.2250738585072014e-308;  // DBL_MIN: its low word is zero, so it is a 32-bit immediate
 __device__ __forceinline__ double sqrt_k(double a, double& half_rinv) {
     const double r = rsqrt_seed(a);
     double h = 0.5 * r;
@@ -61,7 +64,7 @@ __device__ __forceinline__ double sqrt_k(double a, double& half_rinv) {
     h = fma(fma(-r, g, 1.0), h, h);        // refine h with the new g
     g = fma(fma(-g, g, a), h, g);          // final correction: <= 1 ulp
     half_rinv = h;
-    return (a > 0.0) ? g : 0.0;
+    return (a >= SQRT_MIN_ARG) ? g : 0.0;
 }
 // The same without the refinement of h: with h fixed at the seed's 1/(2 sqrt a) (1 + d), |d| ~ 2^-20, one correction
 // g + (a - g^2) h leaves the error -e d - e^2 / (2 sqrt a): 2^-20 -> 2^-40 -> 2^-60, then the rounding of the last
@@ -74,7 +77,7 @@ __device__ __forceinline__ double sqrt_k20(double a, double& h20) {
     g = fma(fma(-g, g, a), h, g);
     g = fma(fma(-g, g, a), h, g);
     h20 = h;
-    return (a > 0.0) ? g : 0.0;
+    return (a >= SQRT_MIN_ARG) ? g : 0.0;
 }
 __device__ __forceinline__ double sqrt_k(double a) {
     double h;

@@ -4,7 +4,7 @@
 // stream of uniforms for one (env, episode) therefore does not depend on which GPU owns the env
 // or on how many GPUs share the job.  The reference draws from numpy's PCG64 (simple_env.py:229);
 // matching that bit stream on a GPU is not a goal -- the DISTRIBUTIONS are matched
-// (tests/test_reset_distribution.py) and the CPU oracle uses this same generator so reset states
+// (tests/test_oracle_golden.py::test_reset_distributions_match_reference_samples) and the CPU oracle uses this same generator so reset states
 // can be compared value for value.
 #pragma once
 #include <cuda_runtime.h>

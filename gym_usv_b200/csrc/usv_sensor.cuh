@@ -42,12 +42,13 @@ constexpr int PAIR_SLOTS = 256;           // slot 255 is reserved: "no hit" -> S
 constexpr uint32_t NO_HIT = 0xFFFFFFFFu;
 
 template <typename HT>
-struct SensorScratch {  // per warp: 3.1 KB (HT = float) / 4.1 KB (double)
+struct SensorScratch {  // per warp: 3.0 KB (HT = float) / 4.0 KB (double)
+    // entry k of geo / rec belongs to the k-th obstacle THAT HAS CANDIDATE RAYS (table order kept): phase B finds the
+    // owner of a pair as a rank and reads both with it, without a slot look-up in between
     double4 geo[MAX_OBST];      // bx, by (offset in the body frame), radius^2, key
     int4 rec[MAX_OBST];         // split, rbase, rbase2, key bits: pair t of this obstacle is ray t + (t < split ? rbase : rbase2)
     HT hpair[PAIR_SLOTS];       // reading of candidate pair t (valid where the pair hit)
     uint32_t best[N_SENS];      // min over hitting obstacles of (key bits & ~255 | pair slot)
-    int ne[MAX_OBST];           // slots of the obstacles that have candidates, in order
 };
 
 template <typename HT> struct Reading;
@@ -60,11 +61,17 @@ template <> struct Reading<float> {
     static __device__ __forceinline__ float no_hit() { return 1.0f; }
 };
 
-// atan2(y, x) to 2.1e-4 rad (7th-order odd polynomial on the folded octant)
+// 1/x as one MUFU.RCP (__fdividef wraps the same instruction in range checks that cost six more)
+__device__ __forceinline__ float rcp_fast(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+// atan2(y, x) to 2.1e-4 rad (7th-order odd polynomial on the folded octant); (x, y) != (0, 0)
 __device__ __forceinline__ float atan2_coarse(float y, float x) {
     const float ax = fabsf(x), ay = fabsf(y);
     const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
-    const float a = __fdividef(mn, fmaxf(mx, 1e-30f));
+    const float a = mn * rcp_fast(fmaxf(mx, 1e-30f));
     const float s = a * a;
     float r = fmaf(fmaf(fmaf(-0.0464964749f, s, 0.15931422f), s, -0.327622764f), s * a, a);
     r = (ay > ax) ? 1.57079637f - r : r;
@@ -107,20 +114,21 @@ __device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2
     bool key_lt = false;
     int lo1 = 0, n1 = 0, lo2 = 0, n2 = 0;
     uint32_t kbits = 0u;
+    double bx = 0.0, by = 0.0, key = 0.0;
     if (lane < nob) {
         const double dx = ox - x, dy = oy - y;  // usv_asmc_ca_env.py:508
         const double d = sqrt_k(fma(dx, dx, dy * dy));
-        const double key = d - rr;              // simple_env.py:205-206
+        key = d - rr;                           // simple_env.py:205-206
         key_lt = key < key_thr;
-        const double bx = fma(cps, dx, sps * dy), by = fma(cps, dy, -(sps * dx));  // offset in the body frame
-        sc.geo[lane] = make_double4(bx, by, rr * rr, key);
+        bx = fma(cps, dx, sps * dy);            // offset in the body frame
+        by = fma(cps, dy, -(sps * dx));
         const uint32_t kb = __float_as_uint((float)key);  // float32 rounding is monotone: it can tie, never invert
         kbits = ((kb & 0x80000000u) ? ~kb : (kb | 0x80000000u)) & ~255u;
         if (d <= rr) {  // boat inside the circle (only on a terminal step): every ray may hit
             n1 = N_SENS;
         } else {
             const float cf = (atan2_coarse((float)by, (float)bx) + 2.0943951f) * INV_PITCH_F;  // ray index of the bearing, [-32, 160]
-            const float w = asin_coarse(__fdividef((float)rr, (float)d)) * INV_PITCH_F + 0.05f;  // approximations: < 0.01 ray
+            const float w = asin_coarse((float)rr * rcp_fast((float)d)) * INV_PITCH_F + 0.05f;  // approximations: < 0.01 ray
             const int klo = (int)ceilf(cf - w), khi = (int)floorf(cf + w);
             // rays klo..khi (mod 192) that fall inside the fan 0..127: one piece, plus a second one when the
             // wedge wraps around the stern (khi >= 192 or klo <= -65); the wedge is < 98 rays wide, so the
@@ -146,15 +154,19 @@ __device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2
     const int off = incl - cnt;
     const bool has = cnt > 0;
     const unsigned has_bal = __ballot_sync(FULL, has);
-    if (has) sc.ne[__popc(has_bal & ((1u << lane) - 1u))] = lane;
-    sc.rec[lane] = make_int4(off + n1, lo1 - off, lo2 - off - n1, (int)kbits);
+    if (has) {  // an obstacle whose (conservative) wedge misses the fan cannot be hit by any ray: it is not stored
+        const int k = __popc(has_bal & ((1u << lane) - 1u));
+        sc.geo[k] = make_double4(bx, by, rr * rr, key);
+        sc.rec[k] = make_int4(off + n1, lo1 - off, lo2 - off - n1, (int)kbits);
+    }
+    const int n_cand = __popc(has_bal);
     const int total = __shfl_sync(FULL, incl, 31);
     __syncwarp();
 
     // ---- phase B: lane = candidate pair ------------------------------------------------------------
     // Pair t belongs to the last obstacle (among those with candidates) whose offset is <= t.  Per pass of 32
     // pairs: bit k of `starts` marks an obstacle whose list starts at pair base + k, `before` counts those that
-    // started earlier, so the owner of pair base + q is ne[before + popc(starts & bits 0..q) - 1].
+    // started earlier, so the owner of pair base + q is entry before + popc(starts & bits 0..q) - 1.
     bool ambiguous = total > PAIR_SLOTS - 1;  // out of pair slots (boat inside circles): exact path
     if (!ambiguous) {
         const unsigned le_mask = 0xFFFFFFFFu >> (31 - lane);
@@ -164,7 +176,7 @@ __device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2
             const unsigned starts = __reduce_or_sync(FULL, (has && rel < 32u) ? (1u << rel) : 0u);
             const int t = base + lane;
             if (t < total) {
-                const int j = sc.ne[before + __popc(starts & le_mask)];
+                const int j = before + __popc(starts & le_mask);
                 const int4 rc = sc.rec[j];
                 const int ri = t + ((t < rc.x) ? rc.y : rc.z);
                 const double2 bxy = *reinterpret_cast<const double2*>(&sc.geo[j]);
@@ -203,7 +215,7 @@ __device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2
         for (int p = 0; p < 4; ++p) {
             const double2 tb = raytab[lane + 32 * p];
             double bkey = INFINITY, bh = SENSOR_MAX_RANGE;
-            for (int j = 0; j < nob; ++j) {
+            for (int j = 0; j < n_cand; ++j) {
                 const double4 g = sc.geo[j];
                 double h;
                 if (ray_test(tb, g.x, g.y, g.z, h) && g.w < bkey) {

@@ -97,6 +97,10 @@ template <typename ObT>
 __device__ __forceinline__ ObT* obst_row(const StatePtrs& s, long long i) {
     return reinterpret_cast<ObT*>(s.sin + i * (long long)(sizeof(ObT) * OBST_ROW + SIN_TAIL_BYTES));
 }
+template <typename ObT>
+__device__ __forceinline__ ObT* obst_row(const StatePtrs& s, unsigned i) {  // 32-bit env index: one IMAD.WIDE
+    return reinterpret_cast<ObT*>(s.sin + (size_t)i * (unsigned)(sizeof(ObT) * OBST_ROW + SIN_TAIL_BYTES));
+}
 __device__ __forceinline__ char* sin_tail(const StatePtrs& s, long long i) { return s.sin + i * s.sin_row + s.sin_tail; }
 __device__ __forceinline__ Hand* hand_of(const StatePtrs& s, long long i) { return reinterpret_cast<Hand*>(sin_tail(s, i)); }
 __device__ __forceinline__ float* hdr_of(const StatePtrs& s, long long i) {

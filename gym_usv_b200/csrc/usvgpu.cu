@@ -19,7 +19,6 @@
 
 #include "../../include/usvgpu.h"
 #include "usv_kernels.cuh"
-#include "usv_fused.cuh"
 #include "usv_legacy.cuh"
 #include "usv_ca.cuh"
 #include "usv_render.cuh"
@@ -45,7 +44,6 @@ struct UsvGpu {
     unsigned long long host_env_steps;
     unsigned long long launches;  // kernels launched by step / rollout so far
     int sm_count;
-    bool fused;            // usv-asmc-simple without do_perturb: one warp-specialised kernel per step (usv_fused.cuh)
     // device staging for the host-buffer face (usvgpu_step_host), allocated on first use
     float* d_actions;
     float* d_obs;
@@ -67,6 +65,27 @@ struct UsvGpu {
 
 static thread_local std::string g_create_err;
 static double2* g_raytab[64] = {nullptr};  // per device ray table for the stand-alone sensors entry point
+
+// Every ABI entry point makes the env's device current for its own duration and puts the caller's device back on
+// the way out: a process that drives several GPUs (or whose torch default device differs from the env's) keeps its
+// current device across calls into this library.
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int device) {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != device) {
+            err = cudaSetDevice(device);
+            switched = err == cudaSuccess;
+        }
+    }
+    ~DeviceGuard() {
+        if (switched) cudaSetDevice(prev);
+    }
+    DeviceGuard(const DeviceGuard&) = delete;
+    DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
 
 static int fail(UsvGpu* h, int code, const std::string& msg) {
     if (h) h->err = msg;
@@ -107,30 +126,6 @@ static void launch_sensor(UsvGpu* h, const StepFlags& fl, float* obs, float* rew
     sensor_kernel<OBST, ObT><<<blocks, SENS_WARPS * 32, 0, st>>>(h->sp, fl, obs, reward, term, trunc, tobs);
 }
 
-template <bool OBST, typename ObT>
-static cudaError_t launch_fused(UsvGpu* h, const StepFlags& fl, const float* actions, float* obs, float* reward, uint8_t* term,
-                                uint8_t* trunc, float* tobs, cudaStream_t st) {
-    const size_t smem = sizeof(FusedSmem<ObT>);  // > 48 KB: usvgpu_create opted in (fused_opt_in)
-    const long long batches = (fl.hi - fl.lo + 31) / 32;
-    const unsigned blocks = (unsigned)(batches < h->sm_count ? batches : h->sm_count);  // persistent: one CTA per SM
-    step_fused_kernel<OBST, ObT><<<blocks, FU_THREADS, smem, st>>>(h->sp, fl, actions, obs, reward, term, trunc, tobs);
-    return cudaGetLastError();
-}
-
-template <bool OBST, typename ObT>
-static cudaError_t fused_opt_in() {
-    // setmaxnreg.inc blocks until the CTA's register pool (threads x registers at launch, plus what setmaxnreg.dec
-    // released) covers the request: the split of usv_fused.cuh must fit the pool this build was compiled with,
-    // otherwise the dynamics warps would wait forever
-    cudaFuncAttributes fa;
-    cudaError_t e = cudaFuncGetAttributes(&fa, step_fused_kernel<OBST, ObT>);
-    if (e != cudaSuccess) return e;
-    if ((long long)fa.numRegs * FU_THREADS < 32LL * (FU_D * USV_FUSED_DYN_REGS + FU_S * USV_FUSED_SENS_REGS))
-        return cudaErrorLaunchOutOfResources;
-    return cudaFuncSetAttribute(step_fused_kernel<OBST, ObT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)sizeof(FusedSmem<ObT>));
-}
-
 // One VecEnv.step(): dynamics_kernel (thread per env) then sensor_kernel (warp per env), stream-ordered.
 static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
                      float* tobs, cudaStream_t st, cudaEvent_t mid = nullptr, long long lo = 0, long long hi = -1) {
@@ -156,19 +151,6 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
             legacy_step_kernel<<<lblocks, LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term, trunc, tobs);
         cudaError_t le = cudaGetLastError();
         if (le != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("legacy step launch: ") + cudaGetErrorString(le));
-        if (mid) cudaEventRecord(mid, st);
-        h->host_env_steps += (unsigned long long)(hi - lo);
-        h->launches += 1;
-        return USV_OK;
-    }
-    if (h->fused) {  // 'usv-asmc-simple': both halves of the step in one persistent kernel
-        const bool f32t = h->cfg.obstacles_f32 != 0;
-        cudaError_t fe;
-        if (h->cfg.ignore_obstacles) fe = f32t ? launch_fused<false, float>(h, fl, actions, obs, reward, term, trunc, tobs, st)
-                                               : launch_fused<false, double>(h, fl, actions, obs, reward, term, trunc, tobs, st);
-        else fe = f32t ? launch_fused<true, float>(h, fl, actions, obs, reward, term, trunc, tobs, st)
-                       : launch_fused<true, double>(h, fl, actions, obs, reward, term, trunc, tobs, st);
-        if (fe != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("fused step launch: ") + cudaGetErrorString(fe));
         if (mid) cudaEventRecord(mid, st);
         h->host_env_steps += (unsigned long long)(hi - lo);
         h->launches += 1;
@@ -226,6 +208,11 @@ extern "C" {
 
 int usvgpu_version(void) { return USVGPU_VERSION; }
 
+#ifndef USVGPU_SOURCE_HASH
+#define USVGPU_SOURCE_HASH "unknown"
+#endif
+const char* usvgpu_source_hash(void) { return USVGPU_SOURCE_HASH; }
+
 const char* usvgpu_last_error(usvgpu_handle h) { return h ? h->err.c_str() : g_create_err.c_str(); }
 
 int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t global_env_offset, uint64_t seed,
@@ -233,6 +220,7 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     if (!cfg || !out) return fail(nullptr, USV_ERR_INVALID, "cfg/out is NULL");
     *out = nullptr;
     if (n_envs <= 0) return fail(nullptr, USV_ERR_INVALID, "n_envs must be positive");
+    if (n_envs >= (1LL << 31)) return fail(nullptr, USV_ERR_INVALID, "n_envs must be below 2^31 (the kernels index envs with 32 bits)");
     if (cfg->env_kind < USV_ENV_ASMC_SIMPLE || cfg->env_kind > USV_ENV_ASMC_CA_V0)
         return fail(nullptr, USV_ERR_INVALID, "unknown env_kind");
     if (cfg->precision != USV_PREC_F64) return fail(nullptr, USV_ERR_INVALID, "precision not supported by this build");
@@ -253,11 +241,6 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->launches = 0;
     h->obst_elem = cfg->obstacles_f32 ? sizeof(float) : sizeof(double);
     h->sm_count = 148;
-    {   // USVGPU_STEP=split keeps the two-kernel step (dynamics_kernel + sensor_kernel) for A/B runs
-        const char* mode = getenv("USVGPU_STEP");
-        const bool want_fused = !(mode && strcmp(mode, "split") == 0);
-        h->fused = want_fused && cfg->env_kind == USV_ENV_ASMC_SIMPLE && !cfg->do_perturb;
-    }
     h->d_actions = h->d_obs = h->d_tobs = h->d_reward = h->h_rows = nullptr;
     h->d_flags = nullptr;
     h->h_idx = nullptr;
@@ -277,7 +260,8 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     h->sp.seed = seed;
     h->sp.kinematic = cfg->env_kind == USV_ENV_SIMPLE;
     const size_t n = (size_t)n_envs;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceGuard dev_guard(device);
+    cudaError_t e = dev_guard.err;
     auto alloc = [&](void** p, size_t bytes) {
         if (e == cudaSuccess) e = cudaMalloc(p, bytes);
         if (e == cudaSuccess) e = cudaMemset(*p, 0, bytes);
@@ -315,11 +299,6 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     double2* rt = nullptr;
     alloc((void**)&rt, N_SENS * sizeof(double2));
     h->sp.raytab = rt;
-    if (e == cudaSuccess && h->fused) {  // the fused kernel's shared-memory block is larger than the 48 KB default
-        const bool f32t = cfg->obstacles_f32 != 0;
-        e = cfg->ignore_obstacles ? (f32t ? fused_opt_in<false, float>() : fused_opt_in<false, double>())
-                                  : (f32t ? fused_opt_in<true, float>() : fused_opt_in<true, double>());
-    }
     if (e == cudaSuccess) e = cudaMemset(h->sp.episode, 0xFF, n * sizeof(int));  // episode = -1 before the first reset
     if (e == cudaSuccess) {
         double2 t[N_SENS];
@@ -358,7 +337,7 @@ int usvgpu_act_dim(usvgpu_handle h) { return h ? h->act_dim : USV_ERR_INVALID; }
 
 int usvgpu_destroy(usvgpu_handle h) {
     if (!h) return USV_OK;
-    cudaSetDevice(h->device);
+    DeviceGuard dev_guard(h->device);
     cudaFree(h->lp.st);
     cudaFree(h->lp.pos0);
     cudaFree(h->lp.st64);
@@ -396,7 +375,8 @@ int usvgpu_destroy(usvgpu_handle h) {
 
 int usvgpu_reset(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream) {
     if (!h) return USV_ERR_INVALID;
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     const int threads = 128;
     const unsigned blocks = (unsigned)((h->sp.n + threads - 1) / threads);
     cudaStream_t st = (cudaStream_t)stream;
@@ -416,7 +396,8 @@ int usvgpu_step(usvgpu_handle h, const float* actions, float* obs, float* reward
     if (!h) return USV_ERR_INVALID;
     if (!actions || !obs || !reward || !terminated || !truncated) return fail(h, USV_ERR_INVALID, "NULL buffer");
     if (bad_alignment(h, obs, actions)) return fail(h, USV_ERR_INVALID, "obs / actions misaligned (simple: 4 / 8 bytes, legacy: 8 / 4 bytes)");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     return step_impl(h, actions, obs, reward, terminated, truncated, terminal_obs, (cudaStream_t)stream);
 }
 
@@ -425,7 +406,8 @@ int usvgpu_step_timed(usvgpu_handle h, const float* actions, float* obs, float* 
     if (!h) return USV_ERR_INVALID;
     if (!actions || !obs || !reward || !terminated || !truncated || !kernel_ms) return fail(h, USV_ERR_INVALID, "NULL buffer");
     if (bad_alignment(h, obs, actions)) return fail(h, USV_ERR_INVALID, "obs / actions misaligned (simple: 4 / 8 bytes, legacy: 8 / 4 bytes)");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     cudaStream_t st = (cudaStream_t)stream;
     cudaEvent_t ev[3];
     for (int k = 0; k < 3; ++k) CU_TRY(h, cudaEventCreate(&ev[k]));
@@ -447,7 +429,8 @@ int usvgpu_rollout(usvgpu_handle h, const float* actions, int32_t n_steps, int32
     if (!actions || !obs || !reward || !terminated || !truncated || n_steps < 0)
         return fail(h, USV_ERR_INVALID, "bad rollout arguments");
     if (bad_alignment(h, obs, actions)) return fail(h, USV_ERR_INVALID, "obs / actions misaligned (simple: 4 / 8 bytes, legacy: 8 / 4 bytes)");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     for (int k = 0; k < n_steps; ++k) {
         const int slab = action_wrap > 0 ? (k % action_wrap) : k;
         int rc = step_impl(h, actions + (size_t)slab * h->sp.n * h->act_dim, obs, reward, terminated, truncated, nullptr,
@@ -481,7 +464,7 @@ int usvgpu_use_staging(usvgpu_handle h, float* actions, float* obs, float* rewar
     if (!h) return USV_ERR_INVALID;
     if (!actions || !obs || !reward || !flags || !terminal_obs) return fail(h, USV_ERR_INVALID, "NULL staging buffer");
     if (h->d_obs && h->own_staging) {
-        cudaSetDevice(h->device);
+        DeviceGuard dev_guard(h->device);
         cudaDeviceSynchronize();
         cudaFree(h->d_actions);
         cudaFree(h->d_obs);
@@ -511,7 +494,8 @@ int usvgpu_host_free(void* p) {
 
 int usvgpu_reset_host(usvgpu_handle h, const uint8_t* mask_host, float* obs_host, void* stream) {
     if (!h || !obs_host) return USV_ERR_INVALID;
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     int rc = ensure_staging(h);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
@@ -533,7 +517,8 @@ int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host
     if (!h) return USV_ERR_INVALID;
     if (!actions_host || !obs_host || !reward_host || !terminated_host || !truncated_host)
         return fail(h, USV_ERR_INVALID, "NULL buffer");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     int rc = ensure_staging(h);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
@@ -594,7 +579,8 @@ int usvgpu_set_host_chunks(usvgpu_handle h, int32_t chunks) {
 
 int usvgpu_stream_sync(usvgpu_handle h, void* stream) {
     if (!h) return USV_ERR_INVALID;
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     CU_TRY(h, cudaStreamSynchronize((cudaStream_t)stream));
     return USV_OK;
 }
@@ -602,7 +588,8 @@ int usvgpu_stream_sync(usvgpu_handle h, void* stream) {
 int usvgpu_flags_sync(usvgpu_handle h) {
     if (!h) return USV_ERR_INVALID;
     if (!h->ev_flags) return fail(h, USV_ERR_INVALID, "no usvgpu_step_host() has run on this handle");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     CU_TRY(h, cudaEventSynchronize(h->ev_flags));
     return USV_OK;
 }
@@ -613,7 +600,8 @@ int usvgpu_terminal_obs_host(usvgpu_handle h, const int32_t* index_host, int64_t
     if (n_index == 0) return USV_OK;
     if (!h->d_tobs || !h->ev_flags) return fail(h, USV_ERR_INVALID, "no usvgpu_step_host() has run on this handle");
     if (n_index > h->sp.n) return fail(h, USV_ERR_INVALID, "more indices than envs");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     if (n_index > h->gather_cap) {
         int64_t cap = h->gather_cap ? h->gather_cap : 1024;
         while (cap < n_index) cap *= 2;
@@ -663,7 +651,8 @@ int usvgpu_get_state(usvgpu_handle h, int32_t field, void* buf, int64_t bytes, v
     int64_t b;
     if (field_ptr(h, field, &p, &b)) return fail(h, USV_ERR_INVALID, "unknown field");
     if (bytes != b) return fail(h, USV_ERR_INVALID, "buffer size does not match usvgpu_field_bytes()");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     if (field == USV_FIELD_OBSTACLES || field == USV_FIELD_N_OBS) {  // rows of the interleaved sensor-input block
         const size_t w = (size_t)(b / h->sp.n);
         CU_TRY(h, cudaMemcpy2DAsync(buf, w, p, (size_t)h->sp.sin_row, w, (size_t)h->sp.n, cudaMemcpyDefault, (cudaStream_t)stream));
@@ -680,7 +669,8 @@ int usvgpu_set_state(usvgpu_handle h, int32_t field, const void* buf, int64_t by
     int64_t b;
     if (field_ptr(h, field, &p, &b)) return fail(h, USV_ERR_INVALID, "unknown field");
     if (bytes != b) return fail(h, USV_ERR_INVALID, "buffer size does not match usvgpu_field_bytes()");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     if (field == USV_FIELD_OBSTACLES || field == USV_FIELD_N_OBS) {
         const size_t w = (size_t)(b / h->sp.n);
         CU_TRY(h, cudaMemcpy2DAsync(p, (size_t)h->sp.sin_row, buf, w, w, (size_t)h->sp.n, cudaMemcpyDefault, (cudaStream_t)stream));
@@ -693,7 +683,8 @@ int usvgpu_set_state(usvgpu_handle h, int32_t field, const void* buf, int64_t by
 
 int usvgpu_episode_stats(usvgpu_handle h, UsvStats* out, int32_t reset, void* stream) {
     if (!h || !out) return USV_ERR_INVALID;
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     cudaStream_t st = (cudaStream_t)stream;
     CU_TRY(h, cudaMemcpyAsync(out, h->sp.stats, sizeof(UsvStats), cudaMemcpyDeviceToHost, st));
     if (reset) CU_TRY(h, cudaMemsetAsync(h->sp.stats, 0, sizeof(DeviceStats), st));
@@ -715,7 +706,8 @@ int usvgpu_asmc_compute(int device, int64_t n, double* state, const double* acti
     if (precision != USV_PREC_F64) return fail(nullptr, USV_ERR_INVALID, "precision not supported by this build");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
-    CU_TRY(nullptr, cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
     const int threads = 128;
     const unsigned blocks = (unsigned)((n + threads - 1) / threads);
     cudaStream_t st = (cudaStream_t)stream;
@@ -730,7 +722,8 @@ int usvgpu_sensors(int device, int64_t n, const double* pose, const double* obst
     if (!pose || !obstacles || !n_obs || !out || n <= 0) return fail(nullptr, USV_ERR_INVALID, "bad sensors arguments");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
-    CU_TRY(nullptr, cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
     if (!g_raytab[device & 63]) {
         double2 t[N_SENS];
         host_raytab(t);
@@ -751,7 +744,8 @@ int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_st
         return fail(nullptr, USV_ERR_INVALID, "bad frame_stack_push arguments");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
-    CU_TRY(nullptr, cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
     frame_push_kernel<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(n, obs_dim, n_stack, pos, ring, obs, terminated,
                                                                               truncated, terminal_obs, terminal_stack);
     CU_TRY(nullptr, cudaGetLastError());
@@ -759,17 +753,18 @@ int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_st
 }
 
 int usvgpu_gae(int device, int32_t n_steps, int64_t n, const float* rewards, const float* values,
-               const float* episode_starts, const float* last_values, const uint8_t* last_dones, float gamma,
-               float gae_lambda, float* advantages, float* returns, void* stream) {
+               const float* episode_starts, const float* last_values, const uint8_t* last_dones, double gamma,
+               double gae_lambda, float* advantages, float* returns, void* stream) {
     if (!rewards || !values || !episode_starts || !last_values || !last_dones || !advantages || !returns || n <= 0 ||
         n_steps <= 0)
         return fail(nullptr, USV_ERR_INVALID, "bad gae arguments");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
-    CU_TRY(nullptr, cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
     gae_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n_steps, n, rewards, values, episode_starts,
-                                                                           last_values, last_dones, gamma, gae_lambda,
-                                                                           advantages, returns);
+                                                                           last_values, last_dones, (float)gamma,
+                                                                           (float)(gamma * gae_lambda), advantages, returns);
     CU_TRY(nullptr, cudaGetLastError());
     return USV_OK;
 }
@@ -782,7 +777,8 @@ int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const
         return fail(h, USV_ERR_INVALID, "bad render arguments (obs / frames NULL, n_frames not in 1..65535, size not in 1..8192)");
     if (!index && n_frames > h->sp.n) return fail(h, USV_ERR_INVALID, "render: more frames than envs");
     if (((uintptr_t)frames & 3) || ((uintptr_t)obs & 3)) return fail(h, USV_ERR_INVALID, "render: frames / obs misaligned");
-    CU_TRY(h, cudaSetDevice(h->device));
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
     const int tiles = (size + RND_TILE - 1) / RND_TILE;
     // tiles per CTA: the draw list is built once per CTA, so whole tile rows when the frames alone fill the machine,
     // shorter runs (down to single tiles) for a handful of frames
@@ -811,7 +807,8 @@ int usvgpu_replay_add(int device, int64_t n, int32_t obs_dim, int32_t act_dim, i
         return fail(nullptr, USV_ERR_INVALID, "replay_add: bad sizes (act_dim <= 32, 0 <= pos < capacity, strides >= obs_dim)");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
-    CU_TRY(nullptr, cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
     const ReplayPtrs b = {buf_obs, buf_next_obs, buf_actions, buf_rewards, buf_dones, buf_timeouts};
     replay_add_kernel<<<(unsigned)((n * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         b, n, obs_dim, act_dim, pos, obs, obs_stride, next_obs, next_stride, terminal_obs, terminal_stride, actions,
@@ -832,7 +829,8 @@ int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim
         return fail(nullptr, USV_ERR_INVALID, "replay_sample: bad sizes");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
-    CU_TRY(nullptr, cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
     const ReplayPtrs b = {const_cast<float*>(buf_obs), const_cast<float*>(buf_next_obs), const_cast<float*>(buf_actions),
                           const_cast<float*>(buf_rewards), const_cast<uint8_t*>(buf_dones),
                           const_cast<uint8_t*>(buf_timeouts)};
@@ -847,7 +845,8 @@ int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, do
     if (!in || !out || n <= 0 || which < 0 || which > 3) return fail(nullptr, USV_ERR_INVALID, "bad math_probe arguments");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
-    CU_TRY(nullptr, cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
     const int threads = 128;
     math_probe_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(which, n, in, out);
     CU_TRY(nullptr, cudaGetLastError());
@@ -858,7 +857,8 @@ int usvgpu_fp64_peak(int device, int32_t blocks, int32_t iters, double* dfma_per
     if (!dfma_per_sec || blocks == 0 || iters <= 0) return fail(nullptr, USV_ERR_INVALID, "bad fp64_peak arguments");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
-    CU_TRY(nullptr, cudaSetDevice(device));
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
     cudaStream_t st = (cudaStream_t)stream;
     double* sink = nullptr;
     CU_TRY(nullptr, cudaMalloc((void**)&sink, sizeof(double)));

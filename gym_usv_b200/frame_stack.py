@@ -51,7 +51,7 @@ class UsvGpuVecFrameStack:
         pos = self._k % self.n_stack
         p = lambda t: None if t is None else C.c_void_p(t.data_ptr())  # noqa: E731
         nat.check(self._lib.usvgpu_frame_stack_push(
-            self.device.index or 0, self.num_envs, self.obs_dim, self.n_stack, pos, p(self.ring), p(obs), p(term),
+            nat.device_index(self.device), self.num_envs, self.obs_dim, self.n_stack, pos, p(self.ring), p(obs), p(term),
             p(trunc), p(tobs), p(self.terminal_stack) if tobs is not None else None,
             C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
         self._k += 1

@@ -27,7 +27,7 @@ def asmc_compute(state: torch.Tensor, actions: torch.Tensor, n_calls: int = 1, d
     n = state.shape[1]
     assert actions.dtype == torch.float64 and actions.is_contiguous() and tuple(actions.shape) == (n, 2)
     info = torch.zeros((4, n), dtype=torch.float64, device=state.device) if want_info else None
-    rc = nat.lib().usvgpu_asmc_compute(state.device.index or 0, n, C.c_void_p(state.data_ptr()),
+    rc = nat.lib().usvgpu_asmc_compute(nat.device_index(state.device), n, C.c_void_p(state.data_ptr()),
                                        C.c_void_p(actions.data_ptr()), int(n_calls), int(do_perturb),
                                        int(first_substep), {"f64": 0, "mixed": 1}[precision],
                                        C.c_void_p(info.data_ptr()) if want_info else None, _stream(state.device))
@@ -46,7 +46,7 @@ def sensor_distances(pose: torch.Tensor, obstacles: torch.Tensor, n_obs: torch.T
     assert obstacles.dtype == torch.float64 and obstacles.is_contiguous() and tuple(obstacles.shape) == (32, 3, n)
     assert n_obs.dtype == torch.int32 and n_obs.is_contiguous() and n_obs.shape[0] == n
     out = torch.empty((nat.SENSORS, n), dtype=torch.float64, device=pose.device)
-    rc = nat.lib().usvgpu_sensors(pose.device.index or 0, n, C.c_void_p(pose.data_ptr()),
+    rc = nat.lib().usvgpu_sensors(nat.device_index(pose.device), n, C.c_void_p(pose.data_ptr()),
                                   C.c_void_p(obstacles.data_ptr()), C.c_void_p(n_obs.data_ptr()),
                                   C.c_void_p(out.data_ptr()), _stream(pose.device))
     nat.check(rc)
@@ -62,7 +62,7 @@ def math_probe(which: str, x: torch.Tensor) -> torch.Tensor:
     assert x.dtype == torch.float64 and x.is_contiguous()
     n = x.shape[-1]
     out = torch.empty((2, n) if which == "rot" else (n,), dtype=torch.float64, device=x.device)
-    nat.check(nat.lib().usvgpu_math_probe(x.device.index or 0, code, n, C.c_void_p(x.data_ptr()),
+    nat.check(nat.lib().usvgpu_math_probe(nat.device_index(x.device), code, n, C.c_void_p(x.data_ptr()),
                                           C.c_void_p(out.data_ptr()), _stream(x.device)))
     return out
 

@@ -67,7 +67,7 @@ class DeviceReplayBuffer:
         rewards = rewards.to(torch.float32).contiguous()
         terminated, truncated = terminated.to(torch.uint8).contiguous(), truncated.to(torch.uint8).contiguous()
         nat.check(nat.lib().usvgpu_replay_add(
-            self.device.index or 0, self.n_envs, self.obs_dim, self.act_dim, self.buffer_size, self.pos, o, so, nx, sn,
+            nat.device_index(self.device), self.n_envs, self.obs_dim, self.act_dim, self.buffer_size, self.pos, o, so, nx, sn,
             tb, stb, p(actions), p(rewards), p(terminated), p(truncated), p(self.observations),
             p(self.next_observations), p(self.actions), p(self.rewards), p(self.dones), p(self.timeouts),
             self._stream()))
@@ -81,7 +81,7 @@ class DeviceReplayBuffer:
         o, so = self._rows(obs, self.obs_dim)
         p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
         nat.check(nat.lib().usvgpu_replay_add(
-            self.device.index or 0, self.n_envs, self.obs_dim, self.act_dim, self.buffer_size, self.pos, o, so, None, 0,
+            nat.device_index(self.device), self.n_envs, self.obs_dim, self.act_dim, self.buffer_size, self.pos, o, so, None, 0,
             None, 0, None, None, None, None, p(self.observations), p(self.next_observations), p(self.actions),
             p(self.rewards), p(self.dones), p(self.timeouts), self._stream()))
 
@@ -100,7 +100,7 @@ class DeviceReplayBuffer:
         out = ReplaySamples(e(b, self.obs_dim), e(b, self.act_dim), e(b, self.obs_dim), e(b, 1), e(b, 1))
         p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
         nat.check(nat.lib().usvgpu_replay_sample(
-            self.device.index or 0, self.n_envs, self.obs_dim, self.act_dim, self.buffer_size, b, p(batch_inds),
+            nat.device_index(self.device), self.n_envs, self.obs_dim, self.act_dim, self.buffer_size, b, p(batch_inds),
             p(env_inds),
             p(self.observations), p(self.next_observations), p(self.actions), p(self.rewards), p(self.dones),
             p(self.timeouts), p(out.observations), p(out.next_observations), p(out.actions), p(out.rewards),

@@ -80,7 +80,7 @@ class DeviceRolloutBuffer:
         last_values = last_values.to(torch.float32).contiguous()
         dones = dones.to(torch.uint8).contiguous()
         p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
-        nat.check(nat.lib().usvgpu_gae(dev.index or 0, n_steps, n, p(self.rewards), p(self.values),
+        nat.check(nat.lib().usvgpu_gae(nat.device_index(dev), n_steps, n, p(self.rewards), p(self.values),
                                        p(self.episode_starts), p(last_values), p(dones), float(gamma),
                                        float(gae_lambda), p(self.advantages), p(self.returns),
                                        C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))

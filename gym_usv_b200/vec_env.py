@@ -87,9 +87,12 @@ class UsvGpuVecEnv:
         self.info_mode = info_mode
         if max_episode_steps is None:
             max_episode_steps = MAX_EPISODE_STEPS[env_id]
+        if precision != "f64":
+            # USV_PREC_MIXED is a reserved value of the C ABI, not an implemented mode: the parity bar (exact done flags
+            # against the reference's float64 arithmetic) does not survive float32 force terms
+            raise nat.UsvError(f"precision '{precision}' is not implemented: this build computes in float64 ('f64') only")
         self.cfg = nat.UsvConfig(ENV_KINDS[env_id], int(ignore_obstacles), int(do_perturb), int(skip_kinematic),
-                                 int(max_episode_steps), int(auto_reset), {"f64": 0, "mixed": 1}[precision],
-                                 int(obstacles_f32))
+                                 int(max_episode_steps), int(auto_reset), nat.PREC_F64, int(obstacles_f32))
         self._seed = int(seed)
         self.global_env_offset = int(global_env_offset)
         self._lib = nat.lib()

@@ -132,6 +132,10 @@ typedef enum UsvField {
 #define USV_EPI_ROWS 7
 
 int usvgpu_version(void);
+/* sha256 (16 hex digits) over the CUDA sources this binary was compiled from, as gym_usv_b200/_native.py::source_hash()
+ * computes it for the tree; "unknown" for a build that did not pass -DUSVGPU_SOURCE_HASH.  No reference counterpart:
+ * it makes "the tested binary is this tree" checkable (the .so is git-ignored and travels to the GPU box prebuilt). */
+const char* usvgpu_source_hash(void);
 /* text of the last error on this handle (or of the last failed usvgpu_create when h == NULL) */
 const char* usvgpu_last_error(usvgpu_handle h);
 
@@ -262,10 +266,12 @@ int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const
 
 /* Replaces stable_baselines3 RolloutBuffer.compute_returns_and_advantage (what PPO.learn of
  * train_test/config.py:3-15 runs after every n_steps = 2048 rollout) on device-resident buffers: rewards, values,
- * episode_starts, advantages, returns float32 [n_steps][N]; last_values float32 [N]; last_dones uint8 [N]. */
+ * episode_starts, advantages, returns float32 [n_steps][N]; last_values float32 [N]; last_dones uint8 [N].
+ * gamma and gae_lambda are DOUBLES as SB3 holds them (Python floats): numpy rounds gamma to float32 against the
+ * arrays, and the product gamma * gae_lambda is taken in float64 first and rounded once. */
 int usvgpu_gae(int device, int32_t n_steps, int64_t n, const float* rewards, const float* values,
-               const float* episode_starts, const float* last_values, const uint8_t* last_dones, float gamma,
-               float gae_lambda, float* advantages, float* returns, void* stream);
+               const float* episode_starts, const float* last_values, const uint8_t* last_dones, double gamma,
+               double gae_lambda, float* advantages, float* returns, void* stream);
 
 /* Replaces stable_baselines3 OffPolicyAlgorithm._store_transition + ReplayBuffer.add for SAC
  * (train_test/sb3_train_vec.py:72 with config_sac, train_test/config.py:17-37: buffer_size 400 000) on device-resident
