@@ -16,13 +16,20 @@ _ROOT = os.path.dirname(_PKG)
 LIB_PATH = os.path.join(_PKG, "libusvgpu.so")
 CSRC = os.path.join(_PKG, "csrc")
 SOURCES = [os.path.join(CSRC, "usvgpu.cu")]
-HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_ca.cuh", "usv_render.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
+HEADERS = [os.path.join(CSRC, f) for f in ("usv_legacy.cuh", "usv_ca.cuh", "usv_render.cuh", "usv_info.cuh", "usv_model.cuh", "usv_philox.cuh", "usv_state.cuh", "usv_reset.cuh",
                                              "usv_sensor.cuh", "usv_kernels.cuh", "usv_math.cuh")] + \
           [os.path.join(_ROOT, "include", "usvgpu.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-shared",
               "-Xcompiler", "-fPIC"]
 
+INFO_DIM = 24
+# UsvInfoCol (include/usvgpu.h): key of the reference's info dict -> (first column, width)
+INFO_KEYS = {"position": (0, 3), "velocity": (3, 3), "path_start": (6, 2), "path_end": (8, 2), "action0": (10, 1),
+             "action1": (11, 1), "ye": (12, 1), "angle_to_target": (13, 1), "ye_reward": (14, 1),
+             "angle_to_target_reward": (15, 1), "angle_action_reward": (16, 1), "delta_action_reward": (17, 1),
+             "delta_action": (18, 1), "velocity_track_reward": (19, 1), "reference_velocity": (20, 1),
+             "reward_velocity": (21, 1), "reference_velocity_error": (22, 1)}
 OBS_DIM = 143
 ACT_DIM = 2
 SENSORS = 128
@@ -41,6 +48,7 @@ PREC_MIXED = 1
 FIELD_DYN, FIELD_EPI, FIELD_OBSTACLES, FIELD_N_OBS, FIELD_STEPS, FIELD_EPISODE, FIELD_EP_RETURN = range(7)
 FIELD_LEGACY, FIELD_LEGACY_TARGET, FIELD_LEGACY_POS0, FIELD_LEGACY64 = 7, 8, 9, 10
 FIELD_CA, FIELD_CA_N_OBS = 11, 12
+FIELD_TARGET0 = 13
 LEGACY_ROWS = 19
 LEGACY64_ROWS = 21
 LEGACY_OBS_DIM = 6
@@ -160,6 +168,8 @@ _SIGNATURES = {
     "usvgpu_sensors": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_frame_stack_push": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 7),
     "usvgpu_render": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
+    "usvgpu_step_info": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "usvgpu_reset_obs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_replay_add": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_int64,
                                     C.c_void_p, C.c_int64, C.c_void_p, C.c_int64] + [C.c_void_p] * 11),
     "usvgpu_replay_sample": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64] + [C.c_void_p] * 14),

@@ -76,6 +76,8 @@ __device__ __forceinline__ void wrapper_tail(const StatePtrs& s, const StepFlags
         c2 = 0.8 * la2 + 0.2 * (ma2 * a1);
         dyn[(long long)D_LA0 * n] = c0;  // :343 last_action = action
         dyn[(long long)D_LA2 * n] = c2;
+        dyn[(long long)D_DACT * n] = fabs(la0 - c0) + fabs(la2 - c2);  // for the info dict only (usv_info.cuh)
+        dyn[(long long)D_LA0_PREV * n] = la0;
     }
     if (KIN || !fl.skip_kinematic) {
         const double du = np_clip(c0 - p.u, -MAX_ACC_U, MAX_ACC_U);

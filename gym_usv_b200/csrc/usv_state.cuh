@@ -33,6 +33,9 @@ static_assert(N_DYN == USV_DYN_ROWS, "header/kernel row count mismatch");
 // 'usv-simple' (UsvSimpleEnv itself, no ASMC controller): the controller rows are unused and two of them hold
 // last_action[0] and last_action[2] (simple_env.py:41,343), which a reset does NOT clear
 constexpr int D_LA0 = D_XD_L, D_LA2 = D_YD_L;
+// ... and two more hold what only the info dict of 'usv-simple' needs (usv_info.cuh): sum |last_action - action| of the
+// last step (simple_env.py:158,196 'delta_action') and last_action[0] before it (:198 'reward_velocity')
+constexpr int D_DACT = D_PSID_L, D_LA0_PREV = D_UD_L;
 // rows of USV_FIELD_EPI
 enum EpiRow { E_PSX = 0, E_PSY, E_PEX, E_PEY, E_MA0, E_MA2, E_VREF, N_EPI };
 static_assert(N_EPI == USV_EPI_ROWS, "header/kernel row count mismatch");

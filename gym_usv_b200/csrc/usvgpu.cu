@@ -22,6 +22,7 @@
 #include "usv_legacy.cuh"
 #include "usv_ca.cuh"
 #include "usv_render.cuh"
+#include "usv_info.cuh"
 
 // =================================================================================================
 // Host side: handle + C ABI
@@ -197,6 +198,7 @@ static int field_ptr(UsvGpu* h, int32_t field, void** p, int64_t* bytes) {
         // these two live inside the interleaved sensor-input rows: *p is the first element, copies are pitched
         case USV_FIELD_OBSTACLES: if (h->legacy || h->ca) return -1; *p = h->sp.sin; *bytes = n * MAX_OBST * 3 * (int64_t)h->obst_elem; return 0;
         case USV_FIELD_N_OBS: if (h->legacy || h->ca) return -1; *p = h->sp.sin + h->sp.sin_tail + sizeof(Hand) + HDR_PAD * sizeof(float); *bytes = n * 4; return 0;
+        case USV_FIELD_TARGET0: if (h->legacy || h->ca) return -1; *p = h->sp.sin + h->sp.sin_tail + sizeof(Hand) + HDR_PAD * sizeof(float) + sizeof(int); *bytes = n * 8; return 0;
         case USV_FIELD_STEPS: *p = h->sp.steps; *bytes = n * 4; return 0;
         case USV_FIELD_EPISODE: *p = h->sp.episode; *bytes = n * 4; return 0;
         case USV_FIELD_EP_RETURN: *p = h->sp.ep_return; *bytes = n * 8; return 0;
@@ -653,7 +655,7 @@ int usvgpu_get_state(usvgpu_handle h, int32_t field, void* buf, int64_t bytes, v
     if (bytes != b) return fail(h, USV_ERR_INVALID, "buffer size does not match usvgpu_field_bytes()");
     DeviceGuard dev_guard(h->device);
     CU_TRY(h, dev_guard.err);
-    if (field == USV_FIELD_OBSTACLES || field == USV_FIELD_N_OBS) {  // rows of the interleaved sensor-input block
+    if (field == USV_FIELD_OBSTACLES || field == USV_FIELD_N_OBS || field == USV_FIELD_TARGET0) {  // rows of the interleaved sensor-input block
         const size_t w = (size_t)(b / h->sp.n);
         CU_TRY(h, cudaMemcpy2DAsync(buf, w, p, (size_t)h->sp.sin_row, w, (size_t)h->sp.n, cudaMemcpyDefault, (cudaStream_t)stream));
     } else {
@@ -671,7 +673,7 @@ int usvgpu_set_state(usvgpu_handle h, int32_t field, const void* buf, int64_t by
     if (bytes != b) return fail(h, USV_ERR_INVALID, "buffer size does not match usvgpu_field_bytes()");
     DeviceGuard dev_guard(h->device);
     CU_TRY(h, dev_guard.err);
-    if (field == USV_FIELD_OBSTACLES || field == USV_FIELD_N_OBS) {
+    if (field == USV_FIELD_OBSTACLES || field == USV_FIELD_N_OBS || field == USV_FIELD_TARGET0) {
         const size_t w = (size_t)(b / h->sp.n);
         CU_TRY(h, cudaMemcpy2DAsync(p, (size_t)h->sp.sin_row, buf, w, w, (size_t)h->sp.n, cudaMemcpyDefault, (cudaStream_t)stream));
     } else {
@@ -790,6 +792,29 @@ int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const
         h->sp, reinterpret_cast<const long long*>(index), obs, OBS_DIM, h->cfg.obstacles_f32, size, tpc, frames);
     CU_TRY(h, cudaGetLastError());
     h->launches += 1;
+    return USV_OK;
+}
+
+int usvgpu_step_info(usvgpu_handle h, const int64_t* index, int64_t n_index, double* out, void* stream) {
+    if (!h) return fail(nullptr, USV_ERR_INVALID, "handle is NULL");
+    if (h->legacy || h->ca) return fail(h, USV_ERR_INVALID, "step_info: only the simple envs return the info dict of simple_env.py");
+    if (!out || n_index <= 0 || (!index && n_index > h->sp.n)) return fail(h, USV_ERR_INVALID, "bad step_info arguments");
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
+    info_kernel<<<(unsigned)((n_index + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        h->sp, reinterpret_cast<const long long*>(index), n_index, out);
+    CU_TRY(h, cudaGetLastError());
+    return USV_OK;
+}
+
+int usvgpu_reset_obs(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream) {
+    if (!h) return fail(nullptr, USV_ERR_INVALID, "handle is NULL");
+    if (h->legacy || h->ca) return fail(h, USV_ERR_INVALID, "reset_obs: only the simple envs");
+    if (!obs) return fail(h, USV_ERR_INVALID, "reset_obs: obs is NULL");
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
+    reset_obs_kernel<<<(unsigned)((h->sp.n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(h->sp, mask, obs);
+    CU_TRY(h, cudaGetLastError());
     return USV_OK;
 }
 

@@ -62,7 +62,7 @@ class UsvGpuVecEnv:
                  max_episode_steps: Optional[int] = None, auto_reset: bool = True, precision: str = "f64",
                  obstacles_f32: bool = False, global_env_offset: int = 0, info_mode: str = "list",
                  render_mode: Optional[str] = None, copy_host_outputs: bool = False, mapped_obs: bool = False,
-                 host_chunks: int = 2, env_id: str = ENV_ID):
+                 host_chunks: int = 2, env_id: str = ENV_ID, options: Optional[dict] = None):
         if not torch.cuda.is_available():
             raise nat.UsvError("UsvGpuVecEnv needs a CUDA device: there is no CPU fallback")
         self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
@@ -85,6 +85,20 @@ class UsvGpuVecEnv:
         self.render_envs = 16   # how many envs get_images() / render() draw
         self.render_size = 512  # SimpleEnvVisualizer(window_size=512), simple_env_visualizer.py:9
         self.info_mode = info_mode
+        # UsvSimpleEnv.__init__(render_mode, options) (simple_env.py:10,15): 'run_custom_experiment' + 'experiment' make
+        # EVERY reset of that env install a fixed scene (:292-300).  Only 'usv-simple' takes constructor options
+        # (UsvSimpleASMCEnv.__init__ has no such argument, simple_env_asmc.py:10-11).  With an experiment installed the
+        # resets of finished envs run through the host (in-kernel auto-reset off), see step_wait().
+        self.options = dict(options or {})
+        self._experiment = None
+        if self.options.get("run_custom_experiment"):
+            if env_id != "usv-simple":
+                raise nat.UsvError("constructor options (run_custom_experiment) exist for 'usv-simple' only "
+                                   "(gym_usv/envs/simple_env.py:10; simple_env_asmc.py:10-11 takes none)")
+            self._experiment = self.options["experiment"]
+        self._host_auto_reset = bool(auto_reset) and self._experiment is not None
+        if self._host_auto_reset:
+            auto_reset = False
         if max_episode_steps is None:
             max_episode_steps = MAX_EPISODE_STEPS[env_id]
         if precision != "f64":
@@ -218,10 +232,118 @@ class UsvGpuVecEnv:
         return self.obs, self.reward, self.terminated, self.truncated
 
     # ------------------------------------------------------------------ SB3 VecEnv face (host numpy)
-    def reset(self) -> np.ndarray:
+    def reset(self, seed: Optional[int] = None, options: Optional[dict] = None) -> np.ndarray:
+        """VecEnv.reset().  ``options`` are the reset options of the reference env (UsvSimpleEnv.reset(seed, options),
+        simple_env.py:228,276-288: ``{'place_obstacles_on_path': n}``), applied to every env; 'usv-asmc-simple' drops
+        them like the reference does (simple_env_asmc.py:14-16 passes only the seed on)."""
+        if seed is not None:
+            self.seed(seed)
+        if options is None and getattr(self, "_next_reset_options", None):
+            options, self._next_reset_options = self._next_reset_options, None
         hb = self._host_buffers()[self._slot]
-        self._check(self._lib.usvgpu_reset_host(self._h, None, hb["obs"].ctypes.data_as(C.c_void_p), self._stream()))
+        if self.env_id != "usv-simple":
+            options = None
+        if options or self._experiment is not None:
+            self.reset_tensor()
+            self._apply_reset_edits(None, options)
+            hb["obs"][...] = self.obs.cpu().numpy()
+        else:
+            self._check(self._lib.usvgpu_reset_host(self._h, None, hb["obs"].ctypes.data_as(C.c_void_p), self._stream()))
         return hb["obs"].copy() if self.copy_host_outputs else hb["obs"]
+
+    def set_options(self, options=None) -> None:
+        """SB3 VecEnv.set_options(): options for the next reset() (one dict for all envs, or a list whose first entry is
+        used: the batched env resets all envs alike)."""
+        if isinstance(options, (list, tuple)):
+            options = options[0] if options else None
+        self._next_reset_options = dict(options) if options else None
+
+    # ------------------------------------------------------------------ reset options / custom experiment (host edits)
+    def _apply_reset_edits(self, idx, options: Optional[dict]) -> None:
+        """The reference's option-driven parts of reset(), as edits of a fresh in-kernel reset (simple_env.py:276-300):
+        obstacles placed along the path ('place_obstacles_on_path': n, drawn here with numpy keyed by (seed, global env
+        id, episode)) and the constructor's custom experiment (fixed obstacles, path, pose).  Then the reset observation
+        of the edited envs is recomputed on the device (usvgpu_reset_obs)."""
+        idx = np.arange(self.num_envs) if idx is None else np.asarray(idx, dtype=np.int64)
+        if idx.size == 0:
+            return
+        st = self.get_state(["dyn", "epi", "obstacles", "n_obs", "episode"])
+        if options and options.get("place_obstacles_on_path"):
+            n_add = int(options["place_obstacles_on_path"])
+            for i in idx:
+                k0 = int(st["n_obs"][i])
+                if k0 + n_add > nat.MAX_OBSTACLES:
+                    raise nat.UsvError(f"place_obstacles_on_path={n_add}: env {i} would hold {k0 + n_add} obstacles, "
+                                       f"the table has {nat.MAX_OBSTACLES} slots")
+                rng = np.random.default_rng([self._seed & 0xFFFFFFFF, self.global_env_offset + int(i),
+                                             int(st["episode"][i]) & 0xFFFFFFFF, 0x0B57])
+                ps, pe = st["epi"][0:2, i], st["epi"][2:4, i]
+                angle = np.arctan2(pe[1] - ps[1], pe[0] - ps[0])
+                mag = rng.uniform(0, np.hypot(0.0, 20.0), n_add)                       # :281
+                st["obstacles"][i, 0, k0:k0 + n_add] = rng.normal(np.cos(angle) * mag + ps[0], 1)   # :283
+                st["obstacles"][i, 1, k0:k0 + n_add] = rng.normal(np.sin(angle) * mag + ps[1], 1)   # :284
+                st["obstacles"][i, 2, k0:k0 + n_add] = rng.uniform(0.15, 0.5, n_add)                 # :290
+                st["n_obs"][i] = k0 + n_add
+        if self._experiment is not None:
+            exp = self._experiment
+            pos = np.asarray(exp["obstacle_positions"], dtype=np.float64).reshape(-1, 2)
+            rad = np.asarray(exp["obstacle_radius"], dtype=np.float64).reshape(-1)
+            if pos.shape[0] > nat.MAX_OBSTACLES or rad.shape[0] != pos.shape[0]:
+                raise nat.UsvError(f"custom experiment: {pos.shape[0]} obstacles / {rad.shape[0]} radii; the table has "
+                                   f"{nat.MAX_OBSTACLES} slots")
+            ps = np.asarray(exp["path_start"], dtype=np.float64).reshape(2)
+            pe = ps + np.array([np.cos(exp["angle"]), np.sin(exp["angle"])]) * 100                   # :297
+            p0 = np.asarray(exp["position"], dtype=np.float64).reshape(3)
+            k = pos.shape[0]
+            for i in idx:
+                st["obstacles"][i, 0, :k], st["obstacles"][i, 1, :k], st["obstacles"][i, 2, :k] = pos[:, 0], pos[:, 1], rad
+                st["n_obs"][i] = k
+                st["epi"][0:2, i], st["epi"][2:4, i] = ps, pe
+                st["dyn"][0:3, i] = p0
+        self.set_state({k: st[k] for k in ("dyn", "epi", "obstacles", "n_obs")})
+        mask = torch.zeros(self.num_envs, dtype=torch.uint8, device=self.device)
+        mask[torch.as_tensor(idx, device=self.device)] = 1
+        self._check(self._lib.usvgpu_reset_obs(self._h, C.c_void_p(mask.data_ptr()), C.c_void_p(self.obs.data_ptr()),
+                                               self._stream()))
+        torch.cuda.current_stream(self.device).synchronize()
+
+    def refresh_reset_obs(self, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """obs[:, :15] of the envs in ``mask`` (default: all) recomputed as the reset observation of their current
+        state (usvgpu_reset_obs): for a caller that edits a fresh reset through set_state()."""
+        mptr = None
+        if mask is not None:
+            mask = mask.to(device=self.device, dtype=torch.uint8).contiguous()
+            mptr = C.c_void_p(mask.data_ptr())
+        self._check(self._lib.usvgpu_reset_obs(self._h, mptr, C.c_void_p(self.obs.data_ptr()), self._stream()))
+        return self.obs
+
+    # ------------------------------------------------------------------ per-step info (simple_env.py:102-115,189-199)
+    def step_info_tensor(self, indices=None) -> torch.Tensor:
+        """float64 CUDA tensor [K, 24]: the reference's info dict as columns (include/usvgpu.h UsvInfoCol), recomputed by
+        usvgpu_step_info from the current state of the envs in ``indices`` (default: all)."""
+        if indices is None:
+            idx, k = None, self.num_envs
+        else:
+            idx = torch.as_tensor(indices, dtype=torch.int64, device=self.device).reshape(-1).contiguous()
+            k = int(idx.numel())
+        out = torch.empty((k, nat.INFO_DIM), dtype=torch.float64, device=self.device)
+        if k:
+            self._check(self._lib.usvgpu_step_info(self._h, C.c_void_p(idx.data_ptr()) if idx is not None else None, k,
+                                                   C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    def step_info(self, indices=None) -> List[dict]:
+        """The info dicts UsvSimpleEnv.step returns (``info = _get_info(reward, action); info.update(reward_info)``,
+        simple_env.py:341-342) for the envs in ``indices``, materialised on request from the device matrix."""
+        rows = self.step_info_tensor(indices).cpu().numpy()
+        sel = np.arange(self.num_envs) if indices is None else np.asarray(indices).reshape(-1)
+        rew = self.reward[torch.as_tensor(sel, device=self.device)].cpu().numpy() if rows.shape[0] else []
+        out = []
+        for k in range(rows.shape[0]):
+            d = {name: (rows[k, c0:c0 + w].copy() if w > 1 else float(rows[k, c0])) for name, (c0, w) in nat.INFO_KEYS.items()}
+            d.update(reward=float(rew[k]), left_thruster=0, right_thruster=0)
+            out.append(d)
+        return out
 
     def step_async(self, actions) -> None:
         self._slot ^= 1
@@ -261,6 +383,16 @@ class UsvGpuVecEnv:
                 payload = [{"TimeLimit.truncated": tl[k], "episode": {"r": er[k], "l": el[k]}}
                            for k in range(done_idx.size)]
         self._check(self._lib.usvgpu_stream_sync(self._h, self._stream()))  # the observations are on the host
+        if self._host_auto_reset and done_idx.size:
+            # a custom experiment is installed (constructor options): the finished envs are reset here, through the
+            # same edits as reset(), and get SB3's terminal_observation from the rows the step just wrote
+            for k, i in enumerate(done_idx):
+                payload[k]["terminal_observation"] = hb["obs"][i].copy()
+            mask = torch.zeros(self.num_envs, dtype=torch.uint8, device=self.device)
+            mask[torch.as_tensor(done_idx, device=self.device)] = 1
+            self.reset_tensor(mask)
+            self._apply_reset_edits(done_idx, None)
+            hb["obs"][done_idx] = self.obs[torch.as_tensor(done_idx, device=self.device)].cpu().numpy()
         obs = hb["obs"].copy() if self.copy_host_outputs else hb["obs"]
         if self.info_mode == "lazy":
             infos: Any = LazyInfos(self.num_envs, done_idx, payload)
@@ -362,7 +494,8 @@ class UsvGpuVecEnv:
     # name -> (field id, dtype, leading dims before N, trailing dims after N)
     _FIELDS = {"dyn": (nat.FIELD_DYN, np.float64, (nat.DYN_ROWS,), ()), "epi": (nat.FIELD_EPI, np.float64, (nat.EPI_ROWS,), ()),
                "obstacles": (nat.FIELD_OBSTACLES, None, (), (3, nat.MAX_OBSTACLES)),
-               "n_obs": (nat.FIELD_N_OBS, np.int32, (), ()), "steps": (nat.FIELD_STEPS, np.int32, (), ()),
+               "n_obs": (nat.FIELD_N_OBS, np.int32, (), ()), "target0": (nat.FIELD_TARGET0, np.float32, (), (2,)),
+               "steps": (nat.FIELD_STEPS, np.int32, (), ()),
                "episode": (nat.FIELD_EPISODE, np.int32, (), ()), "ep_return": (nat.FIELD_EP_RETURN, np.float64, (), ())}
     _LEGACY_FIELDS = {"legacy": (nat.FIELD_LEGACY, np.float32, (nat.LEGACY_ROWS,), ()),
                       "target": (nat.FIELD_LEGACY_TARGET, np.float64, (6,), ()),

@@ -122,7 +122,11 @@ typedef enum UsvField {
     /* USV_ENV_ASMC_CA_V0, float64 [31][N]: target x y | previous action (2, denormalised) | obstacle x[9] | y[9] |
      * radius[9] (usv_asmc_ca_env.py:341-356) */
     USV_FIELD_CA = 11,
-    USV_FIELD_CA_N_OBS = 12 /* int32 [N] obstacles left after the reset's deletions (:379-399) */
+    USV_FIELD_CA_N_OBS = 12, /* int32 [N] obstacles left after the reset's deletions (:379-399) */
+    /* float32 [N][2]: the random target_position a reset draws (simple_env.py:245).  It is what the reset observation,
+     * reset()'s info and the renderer show for an env that has not stepped yet (USV_FIELD_STEPS == 0); the first
+     * step replaces it by the closest point of the path (:328).  Simple envs only. */
+    USV_FIELD_TARGET0 = 13
 } UsvField;
 
 #define USV_LEGACY_ROWS 19
@@ -263,6 +267,33 @@ int usvgpu_frame_stack_push(int device, int64_t n, int32_t obs_dim, int32_t n_st
  * index outside [0, N) is left untouched. */
 int usvgpu_render(usvgpu_handle h, const int64_t* index, int64_t n_frames, const float* obs, int32_t size,
                   uint8_t* frames, void* stream);
+
+/* Replaces the `info` dict UsvSimpleEnv.step / .reset return (gym_usv/envs/simple_env.py:102-115 _get_info and the
+ * reward_info of :189-199 merged at :341-342): out float64 [n_index][USVGPU_INFO_DIM] DEVICE, row k for env index[k]
+ * (int64 DEVICE, or NULL for envs 0 .. n_index - 1), recomputed from the env's current state with the reference's
+ * formulas -- nothing is stored per step.  Columns: UsvInfoCol.  'reward' is what usvgpu_step wrote; 'left_thruster' /
+ * 'right_thruster' are the constant 0 of :112-113.  An env that finished in the last step has been reset already: its
+ * row describes the new episode, like reset()'s info (:305).  USV_ENV_ASMC_SIMPLE and USV_ENV_SIMPLE only. */
+#define USVGPU_INFO_DIM 24
+typedef enum UsvInfoCol {
+    USV_INFO_POSITION = 0,     /* x y psi                                  */
+    USV_INFO_VELOCITY = 3,     /* u v r                                    */
+    USV_INFO_PATH_START = 6, USV_INFO_PATH_END = 8,
+    USV_INFO_ACTION0 = 10, USV_INFO_ACTION1 = 11,
+    USV_INFO_YE = 12, USV_INFO_ANGLE_TO_TARGET = 13,
+    USV_INFO_YE_REWARD = 14, USV_INFO_ANGLE_TO_TARGET_REWARD = 15, USV_INFO_ANGLE_ACTION_REWARD = 16,
+    USV_INFO_DELTA_ACTION_REWARD = 17, USV_INFO_DELTA_ACTION = 18, USV_INFO_VELOCITY_TRACK_REWARD = 19,
+    USV_INFO_REFERENCE_VELOCITY = 20, USV_INFO_REWARD_VELOCITY = 21, USV_INFO_REFERENCE_VELOCITY_ERROR = 22,
+    USV_INFO_PROGRESS = 23     /* self.progress (simple_env.py:53), not part of the reference's dict */
+} UsvInfoCol;
+int usvgpu_step_info(usvgpu_handle h, const int64_t* index, int64_t n_index, double* out, void* stream);
+
+/* obs[i][0..14] <- the reset observation _get_obs(zeros(3)) of simple_env.py:302 recomputed from the CURRENT state of
+ * every env with mask[i] != 0 (mask uint8 [N] DEVICE or NULL for all): for a reset whose state the caller then edited
+ * through usvgpu_set_state -- the reference's reset options (simple_env.py:276-288 'place_obstacles_on_path') and the
+ * constructor's custom experiment (:292-300) are host-side edits of a fresh reset.  The 128 sensor columns are left as
+ * they are (the reference shows stale sensor_data there).  USV_ENV_ASMC_SIMPLE and USV_ENV_SIMPLE only. */
+int usvgpu_reset_obs(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream);
 
 /* Replaces stable_baselines3 RolloutBuffer.compute_returns_and_advantage (what PPO.learn of
  * train_test/config.py:3-15 runs after every n_steps = 2048 rollout) on device-resident buffers: rewards, values,
