@@ -431,8 +431,7 @@ def run_ours(args, rank, local_rank, world):
     wl = Workload(usv, torch, dev, local_rank, hi - lo, lo, args, args.env, args.no_obstacles, args.obstacles_f32,
                   args.batches, args.seed)
     envs, acts, A = wl.envs, wl.acts, wl.A
-    fused = (not legacy) and args.env == "usv-asmc-simple" and os.environ.get("USVGPU_STEP", "fused") != "split"
-    launches_per_step = 1 if (legacy or fused) else 2
+    launches_per_step = 1 if legacy else 2
 
     wl.preroll(args.preroll)
     wl.loop(args.warmup)  # W untimed warm-up steps through the public per-step call
@@ -550,8 +549,12 @@ def run_ours(args, rank, local_rank, world):
         if legacy:
             abytes = survey_bytes = legacy_bytes(args.env)
             kb = {legacy_kernel(args.env): abytes, "-": 0}
-        elif fused:
-            kb = {"usv::step_fused_kernel": survey_bytes, "-": 0}
+        elif args.env == "usv-asmc-simple":
+            # SURVEY.md 8d's bytes shared out over the two kernels: the sensor kernel moves the obstacle table, n_obs,
+            # the observation row, reward and flags (966 B with obstacles, 578 B without), the dynamics kernel the rest;
+            # the hand-over between them exists only because the step is two kernels and is not counted
+            sens = (32 * 3 * (4 if args.obstacles_f32 else 8) + 4 if not args.no_obstacles else 0) + 143 * 4 + 4 + 2
+            kb = {"usv::dynamics_kernel": survey_bytes - (966 if not args.no_obstacles else 578), "usv::sensor_kernel": sens}
         knames = list(kb)
         dom = 0 if kms[0] >= kms[1] else 1
         dom_s = kms[dom] * 1e-3
@@ -562,8 +565,8 @@ def run_ours(args, rank, local_rank, world):
             "warmup": args.warmup, "ms_per_step": ms_block / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": dtype_of(args),
             "data": "synthetic", "config": workload_config(args, world),
-            "timing": {"mode": "the K-step block replayed as one CUDA graph (one host call per block; one kernel launch per "
-                               "step inside it); CUDA events around the block, barrier + synchronize on both sides, max "
+            "timing": {"mode": "the K-step block replayed as one CUDA graph (one host call per block; every step is its own "
+                               "kernel launches inside it); CUDA events around the block, barrier + synchronize on both sides, max "
                                "over ranks, median of `repeats` blocks",
                        "repeats": R, "block_ms_max_over_ranks": ms_graph, "block_ms_rank0": ms_graph_own,
                        "host_enqueue_us_per_step": 1e6 * statistics.median(host_graph) / K,
@@ -579,7 +582,11 @@ def run_ours(args, rank, local_rank, world):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic(knames[dom], n), "peak_source": peak_src, "kernel": knames[dom],
                          "algorithmic_bytes_per_env_step": kb[knames[dom]],
-                         "bytes_source": "SURVEY.md 8d, float64 state" if (fused or legacy) else "per-kernel share, DESIGN.md 6",
+                         "bytes_source": ("SURVEY.md 8d (float64 state), shared out over the kernels without the hand-over; "
+                                          "kernels_moved_bytes_per_env_step counts what each kernel really moves")
+                         if args.env == "usv-asmc-simple" else "DESIGN.md 6",
+                         "kernels_moved_bytes_per_env_step": kernel_bytes(not args.no_obstacles, bool(args.obstacles_f32),
+                                                                          args.env == "usv-simple") if not legacy else None,
                          "launch_us": dom_s * 1e6,
                          "kernels_us": {knames[0]: kms[0] * 1e3, knames[1]: kms[1] * 1e3},
                          "kernels_bytes_per_env_step": kb,

@@ -8,5 +8,5 @@ while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
   nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -shared -Xcompiler -fPIC -Xptxas -v $flags \
        -o build_variants/$name.so gym_usv_b200/csrc/usvgpu.cu 2> build_variants/$name.log
-  echo "== $name ($flags)"; grep -A2 "step_fused_kernelILb1EfEE" build_variants/$name.log | grep -E "registers|spill"
+  echo "== $name ($flags)"; grep -A2 -E "sensor_kernelILb1EfEE|dynamics_kernelILb0EE" build_variants/$name.log | grep -E "registers|spill" || true
 done
