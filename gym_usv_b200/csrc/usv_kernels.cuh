@@ -24,9 +24,6 @@ namespace usv {
 #define USV_DYN_SUBSTEPS 20  // 2 x UsvAsmc.compute; other values only for timing experiments (tools/time_step.py)
 #endif
 #ifndef USV_DYN_UNROLL
-#define USV_DYN_UNROLL 1
-#endif
-#ifndef USV_DYN_UNROLL
 #define USV_DYN_UNROLL 2
 #endif
 constexpr int DYN_UNROLL = USV_DYN_UNROLL;  // sub-steps per trip of the loop in dyn_env: two, so that the loop-carried state
