@@ -480,6 +480,13 @@ def run_ours(args, rank, local_rank, world):
     e2e_variants = {"staged_d2h": e2e_run(False)}
     if args.mapped_obs or args.e2e_all:
         e2e_variants["mapped_obs_stores"] = e2e_run(True)
+    # not the headline: the same call with host_obs=False -- actions from the host, reward / flags / infos back to the
+    # host, the observation rows left on the device for a GPU-resident policy (6 instead of 578 bytes per env-step D2H)
+    for e in envs:
+        e.host_obs = False
+    e2e_variants["obs_left_on_device"] = e2e_run(False)
+    for e in envs:
+        e.host_obs = True
     for e in envs:
         e.mapped_obs = bool(args.mapped_obs)
     e2e_value = e2e_variants["mapped_obs_stores" if args.mapped_obs else "staged_d2h"]

@@ -517,8 +517,8 @@ int usvgpu_reset_host(usvgpu_handle h, const uint8_t* mask_host, float* obs_host
 int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host, float* reward_host,
                      uint8_t* terminated_host, uint8_t* truncated_host, int32_t mapped_obs, void* stream) {
     if (!h) return USV_ERR_INVALID;
-    if (!actions_host || !obs_host || !reward_host || !terminated_host || !truncated_host)
-        return fail(h, USV_ERR_INVALID, "NULL buffer");
+    if (!actions_host || !reward_host || !terminated_host || !truncated_host) return fail(h, USV_ERR_INVALID, "NULL buffer");
+    if (!obs_host && mapped_obs) return fail(h, USV_ERR_INVALID, "mapped_obs needs a host observation buffer");
     DeviceGuard dev_guard(h->device);
     CU_TRY(h, dev_guard.err);
     int rc = ensure_staging(h);
@@ -556,8 +556,9 @@ int usvgpu_step_host(usvgpu_handle h, const float* actions_host, float* obs_host
                 CU_TRY(h, cudaMemcpyAsync(truncated_host, h->d_flags + n, n, cudaMemcpyDeviceToHost, h->copy));
                 CU_TRY(h, cudaEventRecord(h->ev_flags, h->copy));
             }
-            CU_TRY(h, cudaMemcpyAsync(obs_host + lo * h->obs_dim, h->d_obs + lo * h->obs_dim, m * h->obs_dim * sizeof(float),
-                                      cudaMemcpyDeviceToHost, h->copy));
+            if (obs_host)  // NULL: the rows stay on the device, only reward / flags go home
+                CU_TRY(h, cudaMemcpyAsync(obs_host + lo * h->obs_dim, h->d_obs + lo * h->obs_dim, m * h->obs_dim * sizeof(float),
+                                          cudaMemcpyDeviceToHost, h->copy));
             lo = hi;
         }
         CU_TRY(h, cudaEventRecord(h->ev_copied, h->copy));

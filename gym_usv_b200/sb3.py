@@ -194,8 +194,8 @@ def register_envs(namespace: Optional[str] = None, force: bool = False) -> list:
     ``b200/usv-asmc-simple`` etc. instead, to live beside an imported ``gym_usv``.  Ids that are already registered are
     left alone unless ``force``.  Returns the ids registered; [] when gymnasium is not installed."""
     gymnasium = _import_gymnasium()
-    if gymnasium is None:
-        return []
+    if gymnasium is None or not hasattr(gymnasium, "registry") or not hasattr(gymnasium, "register"):
+        return []  # not installed (or an import-only stand-in, as the oracle harness installs)
     done = []
     for env_id, limit in REGISTRY.items():
         full = f"{namespace}/{env_id}" if namespace else env_id

@@ -191,7 +191,11 @@ int usvgpu_rollout(usvgpu_handle h, const float* actions, int32_t n_steps, int32
  * pin_memory) so that the copies run asynchronously on `stream`; pageable memory works but is staged by the
  * driver.  usvgpu_step_host only ENQUEUES (H2D actions, the two kernels, D2H reward / flags / observations):
  * read the outputs after usvgpu_stream_sync().  mapped_obs != 0: obs_host must come from usvgpu_host_alloc; the
- * sensor kernel then stores the observation rows straight into it over PCIe (no staging copy of the 572 B rows). */
+ * sensor kernel then stores the observation rows straight into it over PCIe (no staging copy of the 572 B rows).
+ * obs_host == NULL: the observation rows stay on the device (in the staging tensor of usvgpu_use_staging, i.e. the
+ * caller's own CUDA tensor) and only reward / flags cross PCIe -- for a caller whose policy reads the observations on
+ * the GPU but whose bookkeeping (episode statistics, terminal observations of the finished envs through
+ * usvgpu_terminal_obs_host) lives on the host: 6 bytes per env-step over the bus instead of 578. */
 /* Optional: make the host-buffer face stage through the CALLER's device buffers (actions [N][2], obs [N][143],
  * reward [N] float32, flags uint8 [2][N] = terminated then truncated, terminal_obs [N][143]) instead of
  * handle-owned ones, so that a caller mixing usvgpu_step and usvgpu_step_host sees one set of buffers. */

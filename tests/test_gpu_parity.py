@@ -505,6 +505,32 @@ def test_host_face_equals_tensor_face(usv, mapped_obs, host_chunks, N):
     eh.close()
 
 
+def test_host_face_with_observations_left_on_the_device(usv):
+    """host_obs=False (usvgpu_step_host with obs_host == NULL): numpy actions in, reward / dones / infos on the host, the
+    observation rows as the env's CUDA tensor -- same numbers as the full host face, terminal observations included."""
+    N, T = 5000, 30
+    full = usv.UsvGpuVecEnv(N, device=0, seed=4, max_episode_steps=9, info_mode="lazy")
+    light = usv.UsvGpuVecEnv(N, device=0, seed=4, max_episode_steps=9, info_mode="lazy", host_obs=False)
+    assert np.array_equal(full.reset(), light.reset())
+    n_done = 0
+    for t in range(T):
+        a = action_stream(N, seed=300 + t)
+        obs, rew, dones, infos = full.step(a)
+        obs_d, rew_l, dones_l, infos_l = light.step(a)
+        assert isinstance(obs_d, torch.Tensor) and obs_d.is_cuda and obs_d.data_ptr() == light.obs.data_ptr()
+        assert np.array_equal(obs_d.cpu().numpy(), obs) and np.array_equal(rew_l, rew) and np.array_equal(dones_l, dones)
+        for i in np.flatnonzero(dones)[:50]:
+            n_done += 1
+            assert np.array_equal(infos_l[i]["terminal_observation"], infos[i]["terminal_observation"])
+            assert infos_l[i]["episode"] == infos[i]["episode"]
+    assert n_done > 100
+    with pytest.raises(usv.UsvError):
+        usv.UsvGpuVecEnv(2, device=0, env_id="usv-simple", host_obs=False,
+                         options={"run_custom_experiment": True, "experiment": {}})
+    full.close()
+    light.close()
+
+
 def test_rollout_entry_matches_step_loop(usv):
     N, K = 4096, 12
     dev = torch.device("cuda", 0)
