@@ -29,9 +29,12 @@ namespace usv {
 constexpr int DYN_UNROLL = USV_DYN_UNROLL;  // sub-steps per trip of the loop in dyn_env: two, so that the loop-carried state
                                             // changes registers inside the trip instead of being moved back at its end
                                             // (45 -> 20 register moves per sub-step, 128 registers, no spill; r02f: -0.5 %)
-constexpr int DYN_B = 32;        // threads (= envs) per CTA of the dynamics kernel: one warp, so that the 2048 warps of a
+#ifndef USV_DYN_B
+#define USV_DYN_B 32
+#endif
+constexpr int DYN_B = USV_DYN_B; // threads (= envs) per CTA of the dynamics kernel: one warp, so that the 2048 warps of a
                                  // 65 536-env shard spread evenly over the 148 SMs (13.8 per SM)
-constexpr int DYN_MIN_CTAS = 16; // all of them resident at once (<= 128 registers): no second, nearly empty wave
+constexpr int DYN_MIN_CTAS = 512 / DYN_B; // all of them resident at once (<= 128 registers): no second, nearly empty wave
 #ifndef USV_SENS_WARPS
 #define USV_SENS_WARPS 8
 #endif

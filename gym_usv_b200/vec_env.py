@@ -36,13 +36,32 @@ LEGACY_IDS = ("usv-asmc-v0", "usv-asmc-ye-int-v0", "usv-pid-v0")  # UsvAsmcEnv's
 
 
 class LazyInfos(Sequence):
-    """infos of one step without building N dicts: only done envs carry content."""
+    """infos of one step without building N dicts -- or any dict before it is asked for: only the envs that finished
+    carry content (SB3's ``episode`` / ``TimeLimit.truncated`` / ``terminal_observation``), kept as arrays over the done
+    envs and turned into a dict on access."""
 
-    def __init__(self, n, done_idx, payload):
-        self._n, self._payload = n, {int(i): p for i, p in zip(done_idx, payload)}
+    def __init__(self, n, done_idx, time_limit, ep_return, ep_length, terminal_obs=None):
+        self._n, self._idx = n, np.asarray(done_idx, dtype=np.int64)  # ascending (np.flatnonzero)
+        self._tl, self._er, self._el, self._tob = time_limit, ep_return, ep_length, terminal_obs
+        self._extra = {}
 
     def __len__(self):
         return self._n
+
+    def _payload(self, k):
+        d = {"TimeLimit.truncated": bool(self._tl[k]), "episode": {"r": float(self._er[k]), "l": int(self._el[k])}}
+        if self._tob is not None:
+            d["terminal_observation"] = self._tob[k]
+        d.update(self._extra.get(k, {}))
+        return d
+
+    def set_extra(self, k, key, value):
+        """attach ``key`` to the k-th done env's dict (used by the host-side resets of a custom experiment)"""
+        self._extra.setdefault(k, {})[key] = value
+
+    def done_items(self):
+        """(env index, info dict) of the envs that finished in the step"""
+        return [(int(i), self._payload(k)) for k, i in enumerate(self._idx)]
 
     def __getitem__(self, i):
         if isinstance(i, slice):
@@ -51,7 +70,10 @@ class LazyInfos(Sequence):
             i += self._n
         if not 0 <= i < self._n:
             raise IndexError(i)
-        return self._payload.get(i, {})
+        k = int(np.searchsorted(self._idx, i))
+        if k < self._idx.size and self._idx[k] == i:
+            return self._payload(k)
+        return {}
 
 
 class UsvGpuVecEnv:
@@ -373,29 +395,24 @@ class UsvGpuVecEnv:
         trunc = hb["trunc"].view(np.bool_)
         dones = term | trunc
         done_idx = np.flatnonzero(dones)
-        payload = []
+        tob = None
+        tl = trunc[done_idx] & ~term[done_idx]
+        epi = np.empty((done_idx.size, 2), dtype=np.float64)
         if done_idx.size:
             # terminal observations and the (return, length) of the finished episodes, both kept on the device
             idx32 = done_idx.astype(np.int32)
             tob = np.empty((done_idx.size, self.obs_dim), dtype=np.float32)
-            epi = np.empty((done_idx.size, 2), dtype=np.float64)
             self._check(self._lib.usvgpu_terminal_obs_host(self._h, idx32.ctypes.data_as(C.c_void_p), idx32.size,
                                                            tob.ctypes.data_as(C.c_void_p),
                                                            epi.ctypes.data_as(C.c_void_p)))
-            tl = (trunc[done_idx] & ~term[done_idx]).tolist()
-            er, el = epi[:, 0].tolist(), epi[:, 1].astype(np.int64).tolist()
-            if self.cfg.auto_reset:
-                payload = [{"TimeLimit.truncated": tl[k], "episode": {"r": er[k], "l": el[k]},
-                            "terminal_observation": tob[k]} for k in range(done_idx.size)]
-            else:
-                payload = [{"TimeLimit.truncated": tl[k], "episode": {"r": er[k], "l": el[k]}}
-                           for k in range(done_idx.size)]
+            if not self.cfg.auto_reset and not self._host_auto_reset:
+                tob = None  # nothing was reset: SB3's key would be misleading
+        lazy = LazyInfos(self.num_envs, done_idx, tl, epi[:, 0], epi[:, 1], tob)
         self._check(self._lib.usvgpu_stream_sync(self._h, self._stream()))  # the observations are on the host
         if self._host_auto_reset and done_idx.size:
             # a custom experiment is installed (constructor options): the finished envs are reset here, through the
             # same edits as reset(), and get SB3's terminal_observation from the rows the step just wrote
-            for k, i in enumerate(done_idx):
-                payload[k]["terminal_observation"] = hb["obs"][i].copy()
+            lazy._tob = hb["obs"][done_idx].copy()
             mask = torch.zeros(self.num_envs, dtype=torch.uint8, device=self.device)
             mask[torch.as_tensor(done_idx, device=self.device)] = 1
             self.reset_tensor(mask)
@@ -405,11 +422,11 @@ class UsvGpuVecEnv:
         if not self.host_obs:
             obs = self.obs  # device-resident rows (the staging tensor of the host face is this very tensor)
         if self.info_mode == "lazy":
-            infos: Any = LazyInfos(self.num_envs, done_idx, payload)
+            infos: Any = lazy
         else:
             infos = [{} for _ in range(self.num_envs)]
-            for i, p in zip(done_idx, payload):
-                infos[int(i)] = p
+            for i, p in lazy.done_items():
+                infos[i] = p
         return obs, rew, dones, infos
 
     def step(self, actions):

@@ -83,9 +83,15 @@ def test_spaces_match_reference_definitions():
 
 def test_lazy_infos():
     from gym_usv_b200.vec_env import LazyInfos
-    li = LazyInfos(5, [1, 4], [{"a": 1}, {"b": 2}])
-    assert len(li) == 5 and li[1] == {"a": 1} and li[4] == {"b": 2} and li[0] == {} and li[-1] == {"b": 2}
-    assert li[0:2] == [{}, {"a": 1}]
+    tob = np.arange(6, dtype=np.float32).reshape(2, 3)
+    li = LazyInfos(5, [1, 4], np.array([True, False]), np.array([1.5, -2.0]), np.array([10.0, 3.0]), tob)
+    a = {"TimeLimit.truncated": True, "episode": {"r": 1.5, "l": 10}}
+    b = {"TimeLimit.truncated": False, "episode": {"r": -2.0, "l": 3}}
+    assert len(li) == 5 and li[0] == {} and li[2] == {}
+    for got, want, row in ((li[1], a, tob[0]), (li[4], b, tob[1]), (li[-1], b, tob[1])):
+        assert np.array_equal(got.pop("terminal_observation"), row) and got == want
+    assert li[0:1] == [{}] and [i for i, _ in li.done_items()] == [1, 4]
+    assert "terminal_observation" not in LazyInfos(5, [1], [True], [0.0], [1.0])[1]  # nothing was reset: no SB3 key
     with pytest.raises(IndexError):
         li[5]
 
