@@ -170,6 +170,7 @@ _SIGNATURES = {
     "usvgpu_render": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "usvgpu_step_info": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "usvgpu_reset_obs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "usvgpu_reset_ca_options": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_replay_add": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_int64,
                                     C.c_void_p, C.c_int64, C.c_void_p, C.c_int64] + [C.c_void_p] * 11),
     "usvgpu_replay_sample": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int64] + [C.c_void_p] * 14),
@@ -179,6 +180,43 @@ _SIGNATURES = {
 }
 
 EXPORTS = tuple(_SIGNATURES)
+CA_MAX_OBSTACLES = 9  # USVGPU_CA_MAX_OBSTACLES
+
+
+class UsvCaResetOptions(C.Structure):  # include/usvgpu.h
+    _fields_ = [("has_obstacles", C.c_int32), ("n_obstacles", C.c_int32), ("obs_x", C.c_double * CA_MAX_OBSTACLES),
+                ("obs_y", C.c_double * CA_MAX_OBSTACLES), ("obs_r", C.c_double * CA_MAX_OBSTACLES),
+                ("has_target", C.c_int32), ("has_start", C.c_int32), ("target", C.c_double * 2), ("start", C.c_double * 2)]
+
+
+def ca_reset_options(options: dict) -> UsvCaResetOptions:
+    """The option dict of UsvAsmcCaEnv.reset (gym_usv/envs/usv_asmc_ca_env.py:358-372: 'obs_x' / 'obs_y' / 'obs_r',
+    'target_point', 'start_position'; 'renderplots' belongs to the reference's plotting and is ignored) as the C struct."""
+    import numpy as np
+    unknown = set(options) - {"obs_x", "obs_y", "obs_r", "target_point", "start_position", "renderplots"}
+    if unknown:
+        raise UsvError(f"usv-asmc-ca-v0 reset options: unknown key(s) {sorted(unknown)}")
+    opt = UsvCaResetOptions()
+    if "obs_x" in options:
+        try:
+            ox, oy, orr = (np.asarray(options[k], dtype=np.float64).reshape(-1) for k in ("obs_x", "obs_y", "obs_r"))
+        except KeyError as e:
+            raise UsvError(f"reset options: 'obs_x' needs 'obs_y' and 'obs_r' beside it (missing {e})") from None
+        if not (len(ox) == len(oy) == len(orr)):
+            raise UsvError("reset options: obs_x / obs_y / obs_r differ in length")
+        if len(ox) > CA_MAX_OBSTACLES:
+            raise UsvError(f"reset options: {len(ox)} obstacles; this build holds {CA_MAX_OBSTACLES} per env")
+        opt.has_obstacles, opt.n_obstacles = 1, len(ox)
+        for j in range(len(ox)):
+            opt.obs_x[j], opt.obs_y[j], opt.obs_r[j] = float(ox[j]), float(oy[j]), float(orr[j])
+    for key, flag, dst in (("target_point", "has_target", opt.target), ("start_position", "has_start", opt.start)):
+        if key in options:
+            v = np.asarray(options[key], dtype=np.float64).reshape(-1)
+            if len(v) < 2:
+                raise UsvError(f"reset options: '{key}' needs at least x and y")
+            setattr(opt, flag, 1)
+            dst[0], dst[1] = float(v[0]), float(v[1])
+    return opt
 
 
 def lib():

@@ -18,7 +18,7 @@ namespace usv {
 
 constexpr int CA_SENS = 16;                 // usv_asmc_ca_env.py:44
 constexpr int CA_OBS = USVGPU_CA_OBS_DIM;   // :99  7 + sensor_num
-constexpr int CA_MAX_OBST = 9;              // :349 int(uniform(2, 10)) -> 2..9
+constexpr int CA_MAX_OBST = USVGPU_CA_MAX_OBSTACLES;  // :349 int(uniform(2, 10)) -> 2..9
 constexpr int CA_ROWS = USV_CA_ROWS;        // target x y | previous action (2) | obstacle x[9] y[9] radius[9]
 #ifndef USV_CA_B
 #define USV_CA_B 64
@@ -179,8 +179,9 @@ __device__ __forceinline__ void ca_step_core(const CaPtrs& s, long long i, Pose&
 // reset() (:327-403) with Philox draws keyed by (seed, GLOBAL env id, episode): block 0 -> x, y | 1 -> theta, target x |
 // 2 -> target y, num_obs | 3 + 2 j -> radius of candidate j | 4 + 2 j -> Box-Muller pair of its (x, y).  Leaves the
 // fresh pose / controller in p, c and the target / obstacles in HBM; the caller then runs step([-1, 0]) (:402).
+// opt: reset(options=...) (:358-372), has_* all 0 for a plain reset; applied after the draws, as in the reference.
 __device__ __forceinline__ void ca_reset_draws(const CaPtrs& s, long long i, Pose& p, Ctrl& c, double& pa0, double& pa1,
-                                               double& tx, double& ty, int& nob) {
+                                               double& tx, double& ty, int& nob, const UsvCaResetOptions& opt) {
     const long long n = s.n;
     const int ep = s.episode[i] + 1;
     s.episode[i] = ep;
@@ -196,22 +197,36 @@ __device__ __forceinline__ void ca_reset_draws(const CaPtrs& s, long long i, Pos
     tx = lin(-10.0, (30.0 - 10) - -10.0, b);                 // :343-346
     dk.pair(2, a, b);
     ty = lin(10.0 - 5, (10.0 - 1) - (10.0 - 5), a);
-    const int num_obs = (int)lin(2.0, 10 - 2, b);            // :349
-    const double cx = (x + tx) / 2, cy = (y + ty) / 2;      // :353
+    int num_obs = (int)lin(2.0, 10 - 2, b);                  // :349
+    const double cx = (x + tx) / 2, cy = (y + ty) / 2;      // :353 (the drawn target)
+    if (opt.has_obstacles) num_obs = opt.n_obstacles;       // :361-365
+    if (opt.has_target) {                                   // :367-368
+        tx = opt.target[0];
+        ty = opt.target[1];
+    }
+    const double px = opt.has_start ? opt.start[0] : x, py = opt.has_start ? opt.start[1] : y;  // :370-372 self.position
     double* ca = s.ca + i;
     int kept = 0;
     for (int j = 0; j < num_obs; ++j) {
-        double ur, unused, u1, u2;
-        dk.pair(3 + 2 * j, ur, unused);
-        dk.pair(4 + 2 * j, u1, u2);
-        const double rr = lin(1.0, 2 - 1, ur);              // :354
-        const double rad = sqrt(-2.0 * log(1.0 - u1));
-        double sa, ca_;
-        sincos(2.0 * PI * u2, &sa, &ca_);
-        const double ox = lin(cx, 10.0, __dmul_rn(rad, ca_)), oy = lin(cy, 10.0, __dmul_rn(rad, sa));  // :355-356
-        const double margin = 0.1 + (0.3 + 0.35);           // :379-399
-        if (hypot(ox - x, oy - y) - rr - margin < 0) continue;
-        if (hypot(ox - tx, oy - ty) - rr - margin < 0) continue;
+        double rr, ox, oy;
+        if (opt.has_obstacles) {
+            rr = opt.obs_r[j];
+            ox = opt.obs_x[j];
+            oy = opt.obs_y[j];
+        } else {
+            double ur, unused, u1, u2;
+            dk.pair(3 + 2 * j, ur, unused);
+            dk.pair(4 + 2 * j, u1, u2);
+            rr = lin(1.0, 2 - 1, ur);                       // :354
+            const double rad = sqrt(-2.0 * log(1.0 - u1));
+            double sa, ca_;
+            sincos(2.0 * PI * u2, &sa, &ca_);
+            ox = lin(cx, 10.0, __dmul_rn(rad, ca_));        // :355-356
+            oy = lin(cy, 10.0, __dmul_rn(rad, sa));
+        }
+        const double margin = 0.3 + 0.35;  // :374-399 hypot - r - boat_radius - (safety_radius + 0.35), left to right
+        if (((hypot(ox - px, oy - py) - rr) - 0.1) - margin < 0) continue;
+        if (((hypot(ox - tx, oy - ty) - rr) - 0.1) - margin < 0) continue;
         ca[(long long)(C_OX + kept) * n] = ox;
         ca[(long long)(C_OY + kept) * n] = oy;
         ca[(long long)(C_OR + kept) * n] = rr;
@@ -238,7 +253,7 @@ template <bool RESET>
 __global__ void __launch_bounds__(CA_B, CA_MIN_CTAS)
 ca_kernel(CaPtrs s, StepFlags fl, const uint8_t* __restrict__ mask, const float* __restrict__ actions,
           float* __restrict__ obs, float* __restrict__ reward, uint8_t* __restrict__ terminated,
-          uint8_t* __restrict__ truncated, float* __restrict__ terminal_obs) {
+          uint8_t* __restrict__ truncated, float* __restrict__ terminal_obs, const UsvCaResetOptions opt) {
     __shared__ CaGeo geo;
     const long long n = s.n;
     const long long i = fl.lo + (long long)blockIdx.x * CA_B + threadIdx.x;
@@ -291,7 +306,7 @@ ca_kernel(CaPtrs s, StepFlags fl, const uint8_t* __restrict__ mask, const float*
         }
     }
     if (finished) {  // reset: draws, then the observation of step([-1, 0]) with Python ints -> action [-1.0, 0.0]
-        ca_reset_draws(s, i, p, c, pa0, pa1, tx, ty, nob);
+        ca_reset_draws(s, i, p, c, pa0, pa1, tx, ty, nob, opt);
         ca_step_core(s, i, p, c, pa0, pa1, tx, ty, nob, -1.0, 0.0, geo, out);
         steps = 0;
         s.ep_return[i] = 0.0;

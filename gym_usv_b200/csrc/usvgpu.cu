@@ -134,7 +134,7 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
     const StepFlags fl = {h->cfg.do_perturb, h->cfg.skip_kinematic, h->cfg.max_episode_steps, h->cfg.auto_reset, lo, hi};
     if (h->ca) {  // 'usv-asmc-ca-v0': one kernel, thread per env
         ca_kernel<false><<<(unsigned)((hi - lo + CA_B - 1) / CA_B), CA_B, 0, st>>>(h->cp, fl, nullptr, actions, obs, reward, term,
-                                                                                  trunc, tobs);
+                                                                                  trunc, tobs, UsvCaResetOptions{});
         cudaError_t ce = cudaGetLastError();
         if (ce != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("ca step launch: ") + cudaGetErrorString(ce));
         if (mid) cudaEventRecord(mid, st);
@@ -385,10 +385,26 @@ int usvgpu_reset(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream)
     if (h->ca) {
         const StepFlags fl = {0, 0, h->cfg.max_episode_steps, h->cfg.auto_reset, 0, h->sp.n};
         ca_kernel<true><<<(unsigned)((h->sp.n + CA_B - 1) / CA_B), CA_B, 0, st>>>(h->cp, fl, mask, nullptr, obs, nullptr, nullptr,
-                                                                                 nullptr, nullptr);
+                                                                                 nullptr, nullptr, UsvCaResetOptions{});
     } else if (h->legacy) legacy_reset_kernel<<<blocks, threads, 0, st>>>(h->lp, mask, obs);
     else if (h->cfg.obstacles_f32) reset_kernel<float><<<blocks, threads, 0, st>>>(h->sp, mask, obs);
     else reset_kernel<double><<<blocks, threads, 0, st>>>(h->sp, mask, obs);
+    CU_TRY(h, cudaGetLastError());
+    return USV_OK;
+}
+
+int usvgpu_reset_ca_options(usvgpu_handle h, const uint8_t* mask, const UsvCaResetOptions* options, float* obs,
+                            void* stream) {
+    if (!h) return USV_ERR_INVALID;
+    if (!h->ca) return fail(h, USV_ERR_INVALID, "usvgpu_reset_ca_options: the handle is not a usv-asmc-ca-v0 env");
+    if (!options) return fail(h, USV_ERR_INVALID, "usvgpu_reset_ca_options: NULL options (usvgpu_reset is the plain reset)");
+    if (options->has_obstacles && (options->n_obstacles < 0 || options->n_obstacles > USVGPU_CA_MAX_OBSTACLES))
+        return fail(h, USV_ERR_INVALID, "usvgpu_reset_ca_options: n_obstacles outside 0..USVGPU_CA_MAX_OBSTACLES");
+    DeviceGuard dev_guard(h->device);
+    CU_TRY(h, dev_guard.err);
+    const StepFlags fl = {0, 0, h->cfg.max_episode_steps, h->cfg.auto_reset, 0, h->sp.n};
+    ca_kernel<true><<<(unsigned)((h->sp.n + CA_B - 1) / CA_B), CA_B, 0, (cudaStream_t)stream>>>(
+        h->cp, fl, mask, nullptr, obs, nullptr, nullptr, nullptr, nullptr, *options);
     CU_TRY(h, cudaGetLastError());
     return USV_OK;
 }

@@ -215,13 +215,19 @@ class UsvGpuVecEnv:
         return self._host
 
     # ------------------------------------------------------------------ device-resident face
-    def reset_tensor(self, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def reset_tensor(self, mask: Optional[torch.Tensor] = None, options: Optional[dict] = None) -> torch.Tensor:
         """Env.reset() for all envs (or those with mask != 0).  Returns the device obs tensor [N,143]
-        (columns 15.. keep their previous content: simple_env.py:302 reuses stale sensor data)."""
+        (columns 15.. keep their previous content: simple_env.py:302 reuses stale sensor data).  ``options``: for
+        'usv-asmc-ca-v0' the option dict of UsvAsmcCaEnv.reset (usv_asmc_ca_env.py:358-372), applied in the kernel."""
         mptr = None
         if mask is not None:
             mask = mask.to(device=self.device, dtype=torch.uint8).contiguous()
             mptr = C.c_void_p(mask.data_ptr())
+        if options and self.ca:
+            opt = nat.ca_reset_options(options)
+            self._check(self._lib.usvgpu_reset_ca_options(self._h, mptr, C.byref(opt), C.c_void_p(self.obs.data_ptr()),
+                                                          self._stream()))
+            return self.obs
         self._check(self._lib.usvgpu_reset(self._h, mptr, C.c_void_p(self.obs.data_ptr()), self._stream()))
         return self.obs
 
@@ -262,14 +268,20 @@ class UsvGpuVecEnv:
 
     # ------------------------------------------------------------------ SB3 VecEnv face (host numpy)
     def reset(self, seed: Optional[int] = None, options: Optional[dict] = None) -> np.ndarray:
-        """VecEnv.reset().  ``options`` are the reset options of the reference env (UsvSimpleEnv.reset(seed, options),
-        simple_env.py:228,276-288: ``{'place_obstacles_on_path': n}``), applied to every env; 'usv-asmc-simple' drops
-        them like the reference does (simple_env_asmc.py:14-16 passes only the seed on)."""
+        """VecEnv.reset().  ``options`` are the reset options of the reference env, applied to every env: for
+        'usv-simple' UsvSimpleEnv.reset(seed, options) (simple_env.py:228,276-288: ``{'place_obstacles_on_path': n}``),
+        for 'usv-asmc-ca-v0' UsvAsmcCaEnv.reset(options=...) (usv_asmc_ca_env.py:358-372: obs_x / obs_y / obs_r,
+        target_point, start_position); 'usv-asmc-simple' drops them like the reference does (simple_env_asmc.py:14-16
+        passes only the seed on), the legacy envs take none."""
         if seed is not None:
             self.seed(seed)
         if options is None and getattr(self, "_next_reset_options", None):
             options, self._next_reset_options = self._next_reset_options, None
         hb = self._host_buffers()[self._slot]
+        if self.ca and options:  # usv_asmc_ca_env.py:358-372, applied inside the reset kernel
+            self.reset_tensor(options=options)
+            hb["obs"][...] = self.obs.cpu().numpy()
+            return hb["obs"].copy() if self.copy_host_outputs else hb["obs"]
         if self.env_id != "usv-simple":
             options = None
         if options or self._experiment is not None:

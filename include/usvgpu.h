@@ -299,6 +299,28 @@ int usvgpu_step_info(usvgpu_handle h, const int64_t* index, int64_t n_index, dou
  * they are (the reference shows stale sensor_data there).  USV_ENV_ASMC_SIMPLE and USV_ENV_SIMPLE only. */
 int usvgpu_reset_obs(usvgpu_handle h, const uint8_t* mask, float* obs, void* stream);
 
+/* UsvAsmcCaEnv.reset(options=...) (gym_usv/envs/usv_asmc_ca_env.py:358-372; tools/test_env.py:8-21 builds such a
+ * dict): usvgpu_reset for USV_ENV_ASMC_CA_V0 with the option dict of the reference applied to every masked env, in
+ * the reference's order -- the draws (:331-356), then the options replace the obstacle candidates / the target /
+ * self.position, then the deletion rule (:374-399), then the internal step([-1, 0]) (:402).  As in the reference,
+ * 'start_position' moves self.position for the deletion rule only: the model was built from the drawn pose (:336) and
+ * step() reads the model (:199-204).  At most USVGPU_CA_MAX_OBSTACLES obstacles (what the observation model of this
+ * build holds per env; tools/test_env.py's second layout, 78 circles, is refused by the host side). */
+#define USVGPU_CA_MAX_OBSTACLES 9
+typedef struct UsvCaResetOptions {
+    int32_t has_obstacles;   /* 'obs_x' in options */
+    int32_t n_obstacles;     /* <= USVGPU_CA_MAX_OBSTACLES */
+    double obs_x[USVGPU_CA_MAX_OBSTACLES];
+    double obs_y[USVGPU_CA_MAX_OBSTACLES];
+    double obs_r[USVGPU_CA_MAX_OBSTACLES];
+    int32_t has_target;      /* 'target_point' */
+    int32_t has_start;       /* 'start_position' */
+    double target[2];
+    double start[2];
+} UsvCaResetOptions;
+int usvgpu_reset_ca_options(usvgpu_handle h, const uint8_t* mask, const UsvCaResetOptions* options, float* obs,
+                            void* stream);
+
 /* Replaces stable_baselines3 RolloutBuffer.compute_returns_and_advantage (what PPO.learn of
  * train_test/config.py:3-15 runs after every n_steps = 2048 rollout) on device-resident buffers: rewards, values,
  * episode_starts, advantages, returns float32 [n_steps][N]; last_values float32 [N]; last_dones uint8 [N].

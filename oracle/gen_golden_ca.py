@@ -30,6 +30,7 @@ class ShimDynamicModel:
     def __init__(self, x=0.0, y=0.0, psi=0.0):
         self.position = np.array([x, y, psi], dtype=np.float64)
         self.velocity = np.zeros(3)
+        self.init_pose = self.position.copy()  # what reset() drew (:331-336), before its internal step([-1, 0])
 
 
 class ShimASMC:
@@ -105,9 +106,56 @@ def rollout(Env, np_seed, act_seed, steps, hold, steer=False):
     return out, len(resets), int(done.sum()), int(trunc.sum())
 
 
+# reset(options=...) (usv_asmc_ca_env.py:358-372).  O0 is experiment_1_options() of tools/test_env.py:8-16 (that file
+# imports pygame and cannot be imported here; its second layout has 78 circles, more than the 9 a drawn scene can hold).
+# O1: circles inside the deletion radius of start_position / target_point (:374-399) and a start_position far from the
+# drawn pose -- the boat does NOT start there (the model keeps the drawn pose, :336 vs :370-372).  O2: obstacles only;
+# the deletion rule then runs against the drawn pose and the drawn target.
+OPTION_CASES = [
+    dict(obs_x=np.array([-6, 0, 6, 3, -3]), obs_y=np.array([0, 0, 0, 4, 4]), obs_r=np.array([1.5, 1.5, 1.5, 1.5, 1.5]),
+         start_position=np.array([0, -8, 0]), target_point=np.array([0, 8, 0]), renderplots=False),
+    dict(obs_x=np.array([2.0, 2.5, 14.0, 20.0, 21.0, 8.0]), obs_y=np.array([-7.0, -3.0, 2.0, 6.5, 3.0, -1.0]),
+         obs_r=np.array([1.0, 1.2, 1.8, 1.0, 1.5, 2.0]), start_position=np.array([2.0, -8.5, 0.3]),
+         target_point=np.array([20.0, 7.0, 0.0]), renderplots=False),
+    dict(obs_x=np.array([0.0, 5.0, 10.0, 15.0, 20.0, 25.0, -5.0, 12.0, 3.0]),
+         obs_y=np.array([-8.0, -7.0, 0.0, 4.0, 7.0, -7.5, -9.0, 8.0, 6.5]),
+         obs_r=np.array([1.0, 1.5, 2.0, 1.0, 1.5, 2.0, 1.0, 1.5, 2.0]), renderplots=False),
+]
+
+
+def options_rollout(Env, np_seed, act_seed, steps, options):
+    np.random.seed(np_seed)
+    rng = np.random.default_rng(act_seed)
+    env = Env()
+    o, _ = env.reset(options=options)
+    out = {"reset_" + k: np.asarray(v)[None] for k, v in snapshot(env).items()}  # same layout as rollout(): [resets, ...]
+    out["reset_obs"] = np.array(o, np.float32)[None]
+    out["reset_init_pose"] = env.model.init_pose.copy()[None]
+    out["reset_step"] = np.array([0])
+    obs, rew, done, trunc, pos, vel, acts = [], [], [], [], [], [], []
+    for t in range(steps):
+        a = np.array([0.8, (obs[-1] if obs else o)[4]], np.float32) if t % 3 else rng.uniform(-1, 1, 2).astype(np.float32)
+        o2, r, d, tr, _ = env.step(a)
+        acts.append(a), obs.append(np.array(o2, np.float32)), rew.append(r), done.append(d), trunc.append(tr)
+        pos.append(np.array(env.position)), vel.append(np.array(env.velocity))
+        if d or tr:
+            break
+    out.update(actions=np.array(acts, np.float32), obs=np.array(obs, np.float32), reward=np.array(rew),
+               done=np.array(done, np.uint8), trunc=np.array(trunc, np.uint8), pos=np.array(pos), vel=np.array(vel))
+    for k in ("obs_x", "obs_y", "obs_r", "start_position", "target_point"):
+        if k in options:
+            out["opt_" + k] = np.asarray(options[k], dtype=np.float64)
+    return out
+
+
 if __name__ == "__main__":
     Env = load_ca_env()
     out = {}
+    for k, opt in enumerate(OPTION_CASES):
+        o = options_rollout(Env, 60 + k, 70 + k, 400, opt)
+        print(f"ca O{k}: kept {int(o['reset_n_obs'][0])} of {len(opt['obs_x'])} obstacles, {len(o['obs'])} steps, "
+              f"done {int(o['done'].sum())} truncated {int(o['trunc'].sum())}")
+        out.update({f"O{k}_{name}": v for name, v in o.items()})
     for k, (np_seed, act_seed, steps, hold, steer) in enumerate([(40, 41, 1500, 1, False), (42, 43, 3000, 40, False),
                                                                  (44, 45, 3000, 1, True)]):
         o, nres, nd, nt = rollout(Env, np_seed, act_seed, steps, hold, steer)

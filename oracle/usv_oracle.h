@@ -163,8 +163,26 @@ typedef struct UsvOracleCa {
     int32_t pad_;
 } UsvOracleCa;
 int  usv_oracle_sizeof_ca(void);
+/* reset(options=...) (usv_asmc_ca_env.py:358-372; tools/test_env.py:8-44 builds such dicts): every part is optional */
+typedef struct UsvOracleCaOptions {
+    int32_t has_obstacles;  /* 'obs_x' in options: obs_x / obs_y / obs_r replace the drawn candidates */
+    int32_t n_obstacles;    /* <= USV_ORACLE_CA_MAX_OBS */
+    double obs_x[USV_ORACLE_CA_MAX_OBS];
+    double obs_y[USV_ORACLE_CA_MAX_OBS];
+    double obs_r[USV_ORACLE_CA_MAX_OBS];
+    int32_t has_target;     /* 'target_point' */
+    int32_t has_start;      /* 'start_position': moves self.position for the deletion rule only -- the DynamicModel was
+                               built from the drawn pose before (:336) and step() reads the model (:199-204) */
+    double target[2];
+    double start[2];
+} UsvOracleCaOptions;
+
 void usv_oracle_ca_init(UsvOracleCa* e);
 void usv_oracle_ca_reset(UsvOracleCa* e, uint64_t seed, uint64_t global_id, float obs[USV_ORACLE_CA_OBS_DIM]);
+void usv_oracle_ca_reset_opt(UsvOracleCa* e, uint64_t seed, uint64_t global_id, const UsvOracleCaOptions* opt,
+                             float obs[USV_ORACLE_CA_OBS_DIM]);
+void usv_oracle_ca_vec_reset_opt(UsvOracleCa* envs, int64_t n, uint64_t seed, int64_t global_offset,
+                                 const UsvOracleCaOptions* opt, float* obs, int n_threads);
 void usv_oracle_ca_step(UsvOracleCa* e, const float action_in[2], float obs[USV_ORACLE_CA_OBS_DIM], double* reward,
                         uint8_t* done, uint8_t* trunc, int max_episode_steps);
 void usv_oracle_ca_vec_reset(UsvOracleCa* envs, int64_t n, uint64_t seed, int64_t global_offset, float* obs,

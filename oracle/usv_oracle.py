@@ -160,7 +160,8 @@ def lib():
         L.usv_oracle_sizeof_ca.restype = C.c_int
         L.usv_oracle_ca_vec_reset.argtypes = [vp, i64, u64, i64, vp, i32]
         L.usv_oracle_ca_vec_step.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, i32, i32, u64, i64, i32]
-        L.usv_oracle_ca_vec_reset.restype = L.usv_oracle_ca_vec_step.restype = None
+        L.usv_oracle_ca_vec_reset_opt.argtypes = [vp, i64, u64, i64, vp, vp, i32]
+        L.usv_oracle_ca_vec_reset.restype = L.usv_oracle_ca_vec_step.restype = L.usv_oracle_ca_vec_reset_opt.restype = None
         assert L.usv_oracle_sizeof_ca() == CA_DTYPE.itemsize, (L.usv_oracle_sizeof_ca(), CA_DTYPE.itemsize)
         L.usv_oracle_render_frame.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, dbl, i32, vp]
         L.usv_oracle_render_frame.restype = None
@@ -287,6 +288,26 @@ class OracleLegacyVecEnv:
         return self.obs, self.reward, self.done
 
 
+class CaOptions(C.Structure):  # UsvOracleCaOptions, usv_oracle.h
+    _fields_ = [("has_obstacles", C.c_int32), ("n_obstacles", C.c_int32), ("obs_x", C.c_double * 9),
+                ("obs_y", C.c_double * 9), ("obs_r", C.c_double * 9), ("has_target", C.c_int32), ("has_start", C.c_int32),
+                ("target", C.c_double * 2), ("start", C.c_double * 2)]
+
+
+def ca_options(options) -> CaOptions:
+    opt = CaOptions()
+    if "obs_x" in options:  # usv_asmc_ca_env.py:361-365
+        ox, oy, orr = (np.asarray(options[k], dtype=np.float64).reshape(-1) for k in ("obs_x", "obs_y", "obs_r"))
+        assert len(ox) == len(oy) == len(orr) <= 9
+        opt.has_obstacles, opt.n_obstacles = 1, len(ox)
+        opt.obs_x[:len(ox)], opt.obs_y[:len(ox)], opt.obs_r[:len(ox)] = ox.tolist(), oy.tolist(), orr.tolist()
+    if "target_point" in options:
+        opt.has_target, opt.target[:] = 1, [float(v) for v in options["target_point"][:2]]
+    if "start_position" in options:
+        opt.has_start, opt.start[:] = 1, [float(v) for v in options["start_position"][:2]]
+    return opt
+
+
 class OracleCaVecEnv:
     """N UsvAsmcCaEnv instances ('usv-asmc-ca-v0', in-repo UsvAsmc substituted for usv_libs_py) in lock-step,
     SB3 auto-reset semantics; TimeLimit 5000 (gym_usv/__init__.py:18-22)."""
@@ -303,8 +324,14 @@ class OracleCaVecEnv:
         self.done = np.zeros(self.n, dtype=np.uint8)
         self.trunc = np.zeros(self.n, dtype=np.uint8)
 
-    def reset(self):
-        lib().usv_oracle_ca_vec_reset(_p(self.envs), self.n, self.seed, self.global_offset, _p(self.obs), self.n_threads)
+    def reset(self, options=None):
+        """options: the dict of UsvAsmcCaEnv.reset (usv_asmc_ca_env.py:358-372), applied to every env."""
+        if options:
+            opt = ca_options(options)
+            lib().usv_oracle_ca_vec_reset_opt(_p(self.envs), self.n, self.seed, self.global_offset, C.addressof(opt),
+                                              _p(self.obs), self.n_threads)
+        else:
+            lib().usv_oracle_ca_vec_reset(_p(self.envs), self.n, self.seed, self.global_offset, _p(self.obs), self.n_threads)
         return self.obs
 
     def step(self, actions):

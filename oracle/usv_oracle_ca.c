@@ -148,6 +148,13 @@ static void ca_pair(uint64_t seed, uint64_t gid, uint32_t episode, uint32_t bloc
  * 4 + 2 j -> Box-Muller pair for its (x, y).  Ends, like the reference, with step([-1, 0]) whose observation is the
  * reset observation. */
 void usv_oracle_ca_reset(UsvOracleCa* e, uint64_t seed, uint64_t global_id, float obs[USV_ORACLE_CA_OBS_DIM]) {
+    usv_oracle_ca_reset_opt(e, seed, global_id, NULL, obs);
+}
+
+/* The same with reset(options=...) (:358-372): the draws are made first, as in the reference, then the options replace
+ * the obstacle candidates / the target / self.position, then the deletion rule (:374-399) runs on whatever is there. */
+void usv_oracle_ca_reset_opt(UsvOracleCa* e, uint64_t seed, uint64_t global_id, const UsvOracleCaOptions* opt,
+                             float obs[USV_ORACLE_CA_OBS_DIM]) {
     e->episode += 1;
     const uint32_t ep = (uint32_t)e->episode;
     double a, b;
@@ -156,11 +163,19 @@ void usv_oracle_ca_reset(UsvOracleCa* e, uint64_t seed, uint64_t global_id, floa
     const double y = CA_MIN_Y + ((CA_MIN_Y + 5) - CA_MIN_Y) * b;           /* :332 */
     ca_pair(seed, global_id, ep, 1, &a, &b);
     const double theta = -M_PI / 4 + (M_PI / 4 - -M_PI / 4) * a;           /* :333 */
-    const double tx = CA_MIN_X + ((CA_MAX_X - 10) - CA_MIN_X) * b;         /* :343-346 */
+    double tx = CA_MIN_X + ((CA_MAX_X - 10) - CA_MIN_X) * b;               /* :343-346 */
     ca_pair(seed, global_id, ep, 2, &a, &b);
-    const double ty = (CA_MAX_Y - 5) + ((CA_MAX_Y - 1) - (CA_MAX_Y - 5)) * a;
-    const int num_obs = (int)(2 + (10 - 2) * b);                           /* :349 int(uniform(2, 10)) */
-    const double cx = (x + tx) / 2, cy = (y + ty) / 2;                     /* :353 np.average of two */
+    double ty = (CA_MAX_Y - 5) + ((CA_MAX_Y - 1) - (CA_MAX_Y - 5)) * a;
+    int num_obs = (int)(2 + (10 - 2) * b);                                 /* :349 int(uniform(2, 10)) */
+    const double cx = (x + tx) / 2, cy = (y + ty) / 2;                     /* :353 np.average of two (drawn target) */
+    const int given = opt && opt->has_obstacles;
+    if (given) num_obs = opt->n_obstacles;                                 /* :361-365 */
+    if (opt && opt->has_target) {                                          /* :367-368 */
+        tx = opt->target[0];
+        ty = opt->target[1];
+    }
+    const double px = (opt && opt->has_start) ? opt->start[0] : x;         /* :370-372 self.position (not the model) */
+    const double py = (opt && opt->has_start) ? opt->start[1] : y;
     usv_oracle_asmc_init(&e->asmc);                                        /* :336, 385 fresh model and controller */
     e->asmc.eta[0] = x;
     e->asmc.eta[1] = y;
@@ -170,16 +185,24 @@ void usv_oracle_ca_reset(UsvOracleCa* e, uint64_t seed, uint64_t global_id, floa
     e->prev_action[0] = e->prev_action[1] = 0.0;                           /* :341 */
     int kept = 0;
     for (int j = 0; j < num_obs; ++j) {
-        double ur, unused, u1, u2;
-        ca_pair(seed, global_id, ep, 3 + 2 * j, &ur, &unused);
-        ca_pair(seed, global_id, ep, 4 + 2 * j, &u1, &u2);
-        const double rr = 1 + (2 - 1) * ur;                                /* :354 */
-        const double rad = sqrt(-2.0 * log(1.0 - u1)), ang = 2.0 * M_PI * u2;
-        const double ox = cx + 10 * (rad * cos(ang)), oy = cy + 10 * (rad * sin(ang)); /* :355-356 */
+        double rr, ox, oy;
+        if (given) {
+            rr = opt->obs_r[j];
+            ox = opt->obs_x[j];
+            oy = opt->obs_y[j];
+        } else {
+            double ur, unused, u1, u2;
+            ca_pair(seed, global_id, ep, 3 + 2 * j, &ur, &unused);
+            ca_pair(seed, global_id, ep, 4 + 2 * j, &u1, &u2);
+            rr = 1 + (2 - 1) * ur;                                         /* :354 */
+            const double rad = sqrt(-2.0 * log(1.0 - u1)), ang = 2.0 * M_PI * u2;
+            ox = cx + 10 * (rad * cos(ang));                               /* :355-356 */
+            oy = cy + 10 * (rad * sin(ang));
+        }
         /* :379-399 obstacles too close to the boat or to the target are deleted */
-        const double margin = CA_BOAT_RADIUS + (CA_SAFETY + 0.35);
-        if (hypot(ox - x, oy - y) - rr - margin < 0) continue;
-        if (hypot(ox - tx, oy - ty) - rr - margin < 0) continue;
+        const double margin = CA_SAFETY + 0.35; /* hypot - r - boat_radius - (safety_radius + 0.35), left to right */
+        if (((hypot(ox - px, oy - py) - rr) - CA_BOAT_RADIUS) - margin < 0) continue;
+        if (((hypot(ox - tx, oy - ty) - rr) - CA_BOAT_RADIUS) - margin < 0) continue;
         e->obs_x[kept] = ox;
         e->obs_y[kept] = oy;
         e->obs_r[kept] = rr;
@@ -208,6 +231,14 @@ void usv_oracle_ca_vec_reset(UsvOracleCa* envs, int64_t n, uint64_t seed, int64_
 #pragma omp parallel for schedule(static) num_threads(n_threads > 0 ? n_threads : 1)
     for (int64_t i = 0; i < n; ++i)
         usv_oracle_ca_reset(&envs[i], seed, (uint64_t)(global_offset + i), obs + USV_ORACLE_CA_OBS_DIM * i);
+}
+
+void usv_oracle_ca_vec_reset_opt(UsvOracleCa* envs, int64_t n, uint64_t seed, int64_t global_offset,
+                                 const UsvOracleCaOptions* opt, float* obs, int n_threads) {
+    (void)n_threads;
+#pragma omp parallel for schedule(static) num_threads(n_threads > 0 ? n_threads : 1)
+    for (int64_t i = 0; i < n; ++i)
+        usv_oracle_ca_reset_opt(&envs[i], seed, (uint64_t)(global_offset + i), opt, obs + USV_ORACLE_CA_OBS_DIM * i);
 }
 
 /* N envs, SB3 VecEnv auto-reset semantics; terminated = done, truncated = collision / TimeLimit (both may be set) */

@@ -43,7 +43,7 @@ def _ca_inject(env, k_env, g, prefix, k):
     env.set_state(st)
 
 
-@pytest.mark.parametrize("prefix", ["R0_", "R1_", "R2_"])
+@pytest.mark.parametrize("prefix", ["R0_", "R1_", "R2_", "O0_", "O1_", "O2_"])
 def test_ca_env_golden_replay(usv, prefix):
     from test_oracle_golden import ca_replay
     g = load_golden("ca_env.npz")
@@ -145,6 +145,88 @@ def test_ca_vec_env_lockstep_vs_oracle_with_autoreset(usv, mode):
     stats = env.episode_stats()
     assert stats["nonfinite"] == 0 and stats["env_steps"] == N * T and stats["episodes"] >= n_term
     env.close()
+
+
+@pytest.mark.parametrize("prefix", ["O0_", "O1_", "O2_"])
+def test_ca_reset_options_vs_oracle_and_reference(usv, prefix):
+    """UsvAsmcCaEnv.reset(options=...) (usv_asmc_ca_env.py:358-372) inside the reset kernel (usvgpu_reset_ca_options),
+    with the option dicts the reference goldens were generated with (O0 = experiment_1_options of tools/test_env.py:8-16):
+    the same Philox draws as the pinned restatement, so scene, counters and observation agree with it env for env (the
+    restatement is checked against the reference's own reset(options) in tests/test_oracle_golden.py); where the options
+    fix both start and target, the surviving obstacles are the reference's slot for slot.  Then a masked options reset,
+    and free-running steps whose auto-resets draw random scenes again (a later reset() has no options, :358)."""
+    from test_oracle_golden import ca_golden_options
+    g = load_golden("ca_env.npz")
+    opt = ca_golden_options(g, prefix)
+    N = 512
+    env = usv.UsvGpuVecEnv(N, device=0, seed=11, env_id="usv-asmc-ca-v0", max_episode_steps=120)
+    ov = uo.OracleCaVecEnv(N, seed=11, n_threads=4, max_episode_steps=120)
+    o0 = ov.reset(options=opt).copy()
+    g0 = env.reset(options=dict(opt, renderplots=False)).copy()
+    st = env.get_state()
+    assert np.array_equal(st["n_obs"], ov.envs["n_obs"])
+    assert np.array_equal(st["ca"][0:2].T, ov.envs["target"])
+    for rows, name in ((slice(4, 13), "obs_x"), (slice(13, 22), "obs_y"), (slice(22, 31), "obs_r")):
+        assert np.array_equal(st["ca"][rows].T, ov.envs[name]), name
+    assert np.abs(g0 - o0).max() < CA_OBS_ATOL, float(np.abs(g0 - o0).max())
+    assert np.abs(st["dyn"][:22] - _dyn_from_oracle(ov.envs["asmc"])[:22]).max() < 1e-9
+    n_ref = int(g[prefix + "reset_n_obs"][0])
+    if "start_position" in opt and "target_point" in opt:
+        assert np.all(st["n_obs"] == n_ref)
+        assert np.array_equal(st["ca"][4:4 + n_ref, 7], g[prefix + "reset_ox"][0][:n_ref])
+        assert np.array_equal(st["ca"][22:22 + n_ref, 7], g[prefix + "reset_orad"][0][:n_ref])
+    else:  # the rule runs against each env's own drawn pose and target: counts vary
+        assert len(np.unique(st["n_obs"])) > 1 and st["n_obs"].max() <= len(opt["obs_x"])
+    # steps, with auto-resets into random scenes
+    rng = np.random.default_rng(2)
+    worst, grazes = 0.0, 0
+    for t in range(150):
+        a = rng.uniform(-1, 1, (N, 2)).astype(np.float32)
+        obs, rew, term, trunc = [x.cpu().numpy() for x in env.step_tensor(torch.tensor(a, device=env.device))]
+        oc, rc, dc, tc = ov.step(a)
+        ok = (term.astype(bool) == dc.astype(bool)) & (trunc.astype(bool) == tc.astype(bool))
+        assert ok.sum() >= N - 2, t
+        d = np.abs(obs[ok] - oc[ok]).max(axis=1)
+        grazes += int((d >= 0.01).sum())  # a grazing ray (discriminant ~ 0) flips one reading to max range
+        worst = max(worst, float(d[d < 0.01].max()))
+    assert worst < CA_OBS_ATOL and grazes <= 4, (worst, grazes)
+    st = env.get_state(["n_obs", "episode"])
+    assert st["episode"].min() >= 1 and np.array_equal(st["episode"], ov.envs["episode"])  # TimeLimit 120: everyone reset
+    # masked options reset on the device face: the other envs keep their state
+    mask = torch.zeros(N, dtype=torch.uint8, device=env.device)
+    mask[::3] = 1
+    before = env.get_state(["ca", "n_obs"])
+    env.reset_tensor(mask, options=opt)
+    after = env.get_state(["ca", "n_obs"])
+    m = mask.cpu().numpy().astype(bool)
+    assert np.array_equal(before["ca"][:, ~m], after["ca"][:, ~m]) and np.array_equal(before["n_obs"][~m], after["n_obs"][~m])
+    if "target_point" in opt:
+        assert np.all(after["ca"][0, m] == opt["target_point"][0]) and np.all(after["ca"][1, m] == opt["target_point"][1])
+    assert after["n_obs"][m].max() <= len(opt["obs_x"])
+    env.close()
+
+
+def test_ca_reset_options_errors_and_single_env_view(usv):
+    """More circles than the per-env table holds (tools/test_env.py's second layout has 78) and unknown keys are refused
+    with a message; options on the gym.Env view (reset(seed, options) -> (obs, info))."""
+    env = usv.UsvGpuVecEnv(4, device=0, seed=0, env_id="usv-asmc-ca-v0")
+    with pytest.raises(usv.UsvError, match="obstacles"):
+        env.reset(options=dict(obs_x=np.zeros(10), obs_y=np.zeros(10), obs_r=np.ones(10)))
+    with pytest.raises(usv.UsvError, match="unknown"):
+        env.reset(options=dict(obstacles=3))
+    with pytest.raises(usv.UsvError, match="obs_y"):
+        env.reset(options=dict(obs_x=np.zeros(2)))
+    env.close()
+    one = usv.UsvGpuEnv("usv-asmc-ca-v0", seed=3)
+    opt = dict(obs_x=np.array([-6, 0, 6, 3, -3]), obs_y=np.array([0, 0, 0, 4, 4]), obs_r=np.full(5, 1.5),
+               start_position=np.array([0, -8, 0]), target_point=np.array([0, 8, 0]), renderplots=False)
+    obs, info = one.reset(seed=3, options=opt)
+    assert obs.shape == (23,) and info == {}
+    st = one.vec.get_state(["ca", "n_obs"])
+    assert int(st["n_obs"][0]) == 5 and np.array_equal(st["ca"][4:9, 0], opt["obs_x"]) and tuple(st["ca"][0:2, 0]) == (0.0, 8.0)
+    obs2, r, term, trunc, info = one.step(np.array([0.5, 0.0], np.float32))
+    assert obs2.shape == (23,) and np.isfinite(r)
+    one.close()
 
 
 def test_asmc_compute_heading_error_beyond_pi(usv):

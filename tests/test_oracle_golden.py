@@ -415,6 +415,64 @@ def ca_replay(g, prefix, step_fn, inject_fn):
     return worst
 
 
+def ca_golden_options(g, prefix):
+    """The option dict a golden O-case was generated with (oracle/gen_golden_ca.py OPTION_CASES)."""
+    return {k[len(prefix) + 4:]: g[k] for k in g.keys() if k.startswith(prefix + "opt_")}
+
+
+@pytest.mark.parametrize("prefix", ["O0_", "O1_", "O2_"])
+def test_ca_reset_options_oracle_vs_reference(prefix):
+    """UsvAsmcCaEnv.reset(options=...) (usv_asmc_ca_env.py:358-372).  The reference draws its pose from numpy's global
+    generator, the restatement from Philox, so the reference's drawn pose (recorded by the generator's DynamicModel shim)
+    and, where the options do not give one, its drawn target are installed before the comparison:
+      * the scene that survives the deletion rule (:374-399) -- slot for slot;
+      * the reset observation = the internal step([-1, 0]) from the drawn pose (:402; start_position does not move the
+        boat, :336 vs :370-372);
+      * the rollout that follows, flags exact."""
+    g = load_golden("ca_env.npz")
+    opt = ca_golden_options(g, prefix)
+    ov = uo.OracleCaVecEnv(1, seed=3, auto_reset=False, max_episode_steps=0)
+    ov.reset(options=opt)
+    e = ov.envs[0]
+    init_pose, target = g[prefix + "reset_init_pose"][0], g[prefix + "reset_target"][0]
+    if "start_position" in opt and "target_point" in opt:  # the deletion rule then sees nothing random
+        n = int(g[prefix + "reset_n_obs"][0])
+        assert int(e["n_obs"]) == n
+        for name, key in (("obs_x", "reset_ox"), ("obs_y", "reset_oy"), ("obs_r", "reset_orad")):
+            assert np.array_equal(e[name][:n], g[prefix + key][0][:n])
+        assert np.array_equal(e["target"], target)
+    # the rule itself, in numpy as the reference writes it, on the reference's own draws
+    ox, oy, orr = (np.asarray(opt[k], dtype=np.float64) for k in ("obs_x", "obs_y", "obs_r"))
+    ref_pos = np.asarray(opt["start_position"][:2]) if "start_position" in opt else init_pose[:2]
+    keep = np.hypot(ox - ref_pos[0], oy - ref_pos[1]) - orr - 0.1 - (0.3 + 0.35) >= 0
+    keep &= np.hypot(ox - target[0], oy - target[1]) - orr - 0.1 - (0.3 + 0.35) >= 0
+    n = int(g[prefix + "reset_n_obs"][0])
+    assert int(keep.sum()) == n and np.array_equal(ox[keep], g[prefix + "reset_ox"][0][:n])
+    if prefix != "O0_":
+        assert n < len(ox)  # the case exercises the deletion
+    # the restatement on the reference's draws: a second env whose Philox pose / target are overwritten by them
+    ov2 = uo.OracleCaVecEnv(1, seed=3, auto_reset=False, max_episode_steps=0)
+    ov2.reset(options=dict(opt, start_position=ref_pos, target_point=target))
+    e2 = ov2.envs[0]
+    assert int(e2["n_obs"]) == n and np.array_equal(e2["obs_x"][:n], g[prefix + "reset_ox"][0][:n])
+    fresh = np.zeros((), dtype=uo.ASMC_DTYPE)
+    e2["asmc"] = fresh
+    e2["asmc"]["eta"] = init_pose
+    e2["prev_action"] = 0.0
+    obs, rew, done, trunc = ov2.step(np.array([[-1.0, 0.0]], np.float32))  # denormalises to [-1.0, 0.0] exactly
+    np.testing.assert_allclose(obs[0], g[prefix + "reset_obs"][0], rtol=0, atol=1e-7)
+    np.testing.assert_allclose(e2["asmc"]["eta"], g[prefix + "reset_position"][0], rtol=0, atol=1e-12)
+
+    def step(a):
+        o, r, d, t = ov2.step(a[None])
+        a_ = ov2.envs[0]["asmc"]
+        return o[0].copy(), r[0], d[0], t[0], a_["eta"].copy(), a_["nu"].copy()
+
+    w = ca_replay(g, prefix, step, lambda k: ca_inject(ov2.envs[0], g, prefix, k))
+    print(prefix, w)
+    assert w["pos"] < 1e-7 and w["vel"] < 1e-7 and w["rew"] < 1e-8 and w["obs"] < 1e-6, w
+
+
 @pytest.mark.parametrize("prefix", ["R0_", "R1_", "R2_"])
 def test_ca_env_oracle_vs_reference_rollout(prefix):
     g = load_golden("ca_env.npz")
