@@ -13,8 +13,6 @@
 // independent tests (many thin threads).  The hand-over (pose, heading cos/sin, partial reward, flags: 48 B,
 // and the 64 B observation header row) is written and re-read through L2 within one launch pair.
 #pragma once
-#include <cuda_pipeline.h>
-
 #include "usv_reset.cuh"
 #include "usv_sensor.cuh"
 
@@ -41,6 +39,25 @@ constexpr int DYN_MIN_CTAS = 512 / DYN_B; // all of them resident at once (<= 12
 #ifndef USV_SENS_MIN_CTAS
 #define USV_SENS_MIN_CTAS 4   // 32 warps per SM at 64 registers (no spill with the float32 table); 3 x 8 warps at 76: +1 % time (r02f)
 #endif
+// Programmatic dependent launch between the kernels of consecutive launches (build knob, 0 = off): 1 = the launches carry
+// cudaLaunchAttributeProgrammaticStreamSerialization and every kernel runs griddepcontrol.wait before it touches anything
+// another kernel wrote (its own prologue -- parameters, indices, the ray table -- overlaps the previous kernel's drain);
+// 2 = the kernels also signal griddepcontrol.launch_dependents once their main loop is behind them.
+// Measured at 65 536 envs (r02m, us per step): off 68.63, 1: 67.83, 2: 68.03.  (An early trigger -- at kernel start,
+// r02d -- made it 92: dependents that become resident early only sit in the wait.)
+#ifndef USV_PDL
+#define USV_PDL 1
+#endif
+__device__ __forceinline__ void pdl_wait() {
+#if USV_PDL
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+#endif
+}
+__device__ __forceinline__ void pdl_trigger() {
+#if USV_PDL >= 2
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
 constexpr int SENS_WARPS = USV_SENS_WARPS;    // warps (= envs) per CTA of the sensor kernel
 constexpr int SENS_MIN_CTAS = USV_SENS_MIN_CTAS; // resident CTAs per SM the persistent grid is sized for
 
@@ -150,6 +167,20 @@ __device__ __forceinline__ void store_handover(const StatePtrs& s, const long lo
     for (int k = 0; k < 4; ++k) dst[k] = hrow[k];
 }
 
+// The per-env scalars of the step as they are when the sensors find nothing (no collision, nearest obstacle not inside
+// 0.05 m): reward without the collision term, terminated = 0, truncated from the flags, episode return += reward.
+// Written here, one THREAD per env and coalesced (4 stores + 1 load per 32 envs), because the same work in the sensor
+// kernel is one WARP per env: 32 warp-instructions per env for the common case (r02c source table).  The sensor kernel
+// only revisits the envs that collided, terminated or were truncated (finish_env).
+__device__ __forceinline__ void store_step_scalars(const StatePtrs& s, const long long i, const Hand& hd,
+                                                   float* __restrict__ reward, uint8_t* __restrict__ terminated,
+                                                   uint8_t* __restrict__ truncated) {
+    reward[i] = (float)hd.rew_part;
+    terminated[i] = 0;
+    truncated[i] = hd.flags ? 1 : 0;
+    s.ep_return[i] += hd.rew_part;
+}
+
 // ---------------------------------------------------------------------------------------------
 // One env's share of dynamics_kernel / of the fused kernel's dynamics role: load the SoA columns, 2 x UsvAsmc.compute
 // = 20 sub-steps (simple_env_asmc.py:19-25), wrapper_tail, store the columns.  The hand-over comes back in registers.
@@ -194,6 +225,7 @@ __device__ __forceinline__ void dyn_env(const StatePtrs& s, const StepFlags& fl,
     sincos(p.psi, &sn, &cs);  // carried through the sub-steps by small rotations (usv_math.cuh)
 #pragma unroll DYN_UNROLL
     for (int k = 0; k < USV_DYN_SUBSTEPS; ++k) asmc_substep<PERTURB, false>(p, c, a0, a1, cs, sn, pstep0 + k, nullptr);
+    pdl_trigger();
 
     double progress;
     wrapper_tail<false>(s, fl, i, n, p, cs, sn, progress, steps, 0.0, 0.0, hd, hrow);
@@ -228,13 +260,16 @@ __device__ __forceinline__ void dyn_env(const StatePtrs& s, const StepFlags& fl,
 
 template <bool PERTURB>
 __global__ void __launch_bounds__(DYN_B, DYN_MIN_CTAS)
-dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
+dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions, float* __restrict__ reward,
+                uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated) {
     const long long i = fl.lo + (long long)blockIdx.x * DYN_B + threadIdx.x;
     if (i >= fl.hi) return;
+    pdl_wait();
     Hand hd;
     float4 hrow[4];
     dyn_env<PERTURB>(s, fl, actions, i, hd, hrow);
     store_handover(s, i, hd, hrow);
+    store_step_scalars(s, i, hd, reward, terminated, truncated);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -247,7 +282,8 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
 #endif
 constexpr int KIN_B = USV_KIN_B;
 __global__ void __launch_bounds__(KIN_B)
-kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
+kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions, float* __restrict__ reward,
+                 uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated) {
     const long long n = s.n;
     const long long i = fl.lo + (long long)blockIdx.x * KIN_B + threadIdx.x;
     if (i >= fl.hi) return;
@@ -268,6 +304,7 @@ kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions) {
     float4 hrow[4];
     wrapper_tail<true>(s, fl, i, n, p, cs, sn, progress, steps, (double)af.x, (double)af.y, hd, hrow);
     store_handover(s, i, hd, hrow);
+    store_step_scalars(s, i, hd, reward, terminated, truncated);
     if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.psi))) atomicAdd(&s.stats->nonfinite, 1ull);
     dyn[(long long)D_X * n] = p.x;
     dyn[(long long)D_Y * n] = p.y;
@@ -292,28 +329,31 @@ __device__ __forceinline__ void finish_env(const StatePtrs& s, const StepFlags& 
                                            const double rew_part, const unsigned flags, float* __restrict__ obs,
                                            float* __restrict__ reward, uint8_t* __restrict__ terminated,
                                            uint8_t* __restrict__ truncated, float* __restrict__ terminal_obs) {
-    const bool oob = flags & FLG_OOB, tlimit = flags & FLG_TLIMIT;
-    const bool trunc = oob || tlimit;
+    // reward, terminated = 0, truncated and the episode return of the common case were written by the first kernel
+    // (store_step_scalars); only an env that collided, terminated or was truncated is revisited here
+    const bool trunc = flags != 0;
     const bool done = term || trunc;
-    const double rew = (collided ? -20.0 : 0.0) + rew_part;
-    if (lane == 0) {
-        reward[i] = (float)rew;
-        terminated[i] = term ? 1 : 0;
-        truncated[i] = trunc ? 1 : 0;
-        if (done) {
-            const double ep_ret = s.ep_return[i] + rew;
-            DeviceStats* ds = s.stats;
-            const double ep_len = (double)s.steps[i];
-            s.ep_done[i] = make_double2(ep_ret, ep_len);
-            atomicAdd(&ds->return_sum, ep_ret);
-            atomicAdd(&ds->length_sum, ep_len);
-            atomicAdd(&ds->episodes, 1ull);
-            if (term) atomicAdd(&ds->terminated, 1ull);
-            if (oob) atomicAdd(&ds->out_of_bounds, 1ull);
-            if (tlimit && !term && !oob) atomicAdd(&ds->time_limit, 1ull);
-            if (!fl.auto_reset) s.ep_return[i] = ep_ret;  // the reset below zeroes it otherwise
-        } else {
-            atomicAdd(&s.ep_return[i], rew);  // result unused: a fire-and-forget reduction, no load to wait for
+    if (done || collided) {
+        if (lane == 0) {
+            const bool oob = flags & FLG_OOB, tlimit = flags & FLG_TLIMIT;
+            const double coll = collided ? -20.0 : 0.0;
+            if (collided) reward[i] = (float)(coll + rew_part);
+            if (term) terminated[i] = 1;
+            const double ep_ret = s.ep_return[i] + coll;  // rew_part is already in
+            if (done) {
+                DeviceStats* ds = s.stats;
+                const double ep_len = (double)s.steps[i];
+                s.ep_done[i] = make_double2(ep_ret, ep_len);
+                atomicAdd(&ds->return_sum, ep_ret);
+                atomicAdd(&ds->length_sum, ep_len);
+                atomicAdd(&ds->episodes, 1ull);
+                if (term) atomicAdd(&ds->terminated, 1ull);
+                if (oob) atomicAdd(&ds->out_of_bounds, 1ull);
+                if (tlimit && !term && !oob) atomicAdd(&ds->time_limit, 1ull);
+                if (!fl.auto_reset) s.ep_return[i] = ep_ret;  // the reset below zeroes it otherwise
+            } else {
+                s.ep_return[i] = ep_ret;
+            }
         }
     }
     float* orow = obs + (size_t)i * OBS_DIM;
@@ -347,29 +387,45 @@ struct alignas(16) SensorStage {
 static_assert(sizeof(SensorStage<float>) == sizeof(float) * OBST_ROW + SIN_TAIL_BYTES, "stage == sensor-input row");
 static_assert(sizeof(SensorStage<double>) == sizeof(double) * OBST_ROW + SIN_TAIL_BYTES, "stage == sensor-input row");
 
-// The stage has the layout of the env's sensor-input row (usv_state.cuh): the prefetch is a straight 16-byte-chunk
-// copy, one cp.async per lane for a float32 table.  Without obstacles only the 128-byte tail is fetched.
-// cp.async as plain PTX: the cuda_pipeline wrappers expand to the same LDGSTS plus three dummy `@!PT LDS` per call
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+// The stage has the layout of the env's sensor-input row (usv_state.cuh), so the prefetch is ONE bulk copy
+// (cp.async.bulk, the 1-D form of TMA: UBLKCP in SASS) of the 512-byte row -- 16-byte aligned at both ends -- issued by
+// one lane and completed on the warp's own mbarrier, which the warp polls before it reads the stage.  (Round 1 used one
+// 16-byte cp.async per lane + commit / wait groups: 15 warp-instructions per env against 8 now.)  Without obstacles only
+// the 128-byte tail is fetched.
+__device__ __forceinline__ void mbar_init(const uint32_t bar, const uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(const uint32_t bar, const uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+// one lane: announce `bytes` on the barrier, then start the copy that will complete them
+__device__ __forceinline__ void bulk_fetch(const uint32_t smem_dst, const void* gmem_src, const uint32_t bytes, const uint32_t bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
+                 "l"(gmem_src), "r"(bytes), "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 template <bool OBST, typename ObT>
-__device__ __forceinline__ void sensor_prefetch(SensorStage<ObT>& st, const StatePtrs& s, unsigned i, int lane) {
-    constexpr int TABLE_CHUNKS = (int)(sizeof(ObT) * OBST_ROW / 16);  // 24 (float32 table) or 48 (float64)
-    constexpr int ROW_CHUNKS = TABLE_CHUNKS + SIN_TAIL_BYTES / 16;    // 32 or 56
+__device__ __forceinline__ void sensor_prefetch(const uint32_t stage_addr, const uint32_t bar, const StatePtrs& s, unsigned i,
+                                                int lane) {
+    constexpr uint32_t TABLE_BYTES = (uint32_t)(sizeof(ObT) * OBST_ROW);  // 384 (float32 table) or 768 (float64)
     const char* row = reinterpret_cast<const char*>(obst_row<ObT>(s, i));
-    char* dst = reinterpret_cast<char*>(&st);
-    if (OBST) {
-#pragma unroll
-        for (int c = lane; c < ROW_CHUNKS; c += 32) cp_async16(dst + 16 * c, row + 16 * c);
-    } else {
-        if (lane < SIN_TAIL_BYTES / 16) cp_async16(dst + 16 * (TABLE_CHUNKS + lane), row + 16 * (TABLE_CHUNKS + lane));
+    if (lane == 0) {
+        if (OBST) bulk_fetch(stage_addr, row, TABLE_BYTES + SIN_TAIL_BYTES, bar);
+        else bulk_fetch(stage_addr + TABLE_BYTES, row + TABLE_BYTES, SIN_TAIL_BYTES, bar);
     }
-    cp_async_commit();
 }
 
 // Persistent: the grid is sized to the machine (SENS_MIN_CTAS CTAs per SM) and every warp walks envs
@@ -381,36 +437,57 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
     __shared__ double2 raytab[N_SENS];
     __shared__ SensorScratch<float> scratch[OBST ? SENS_WARPS : 1];
     __shared__ SensorStage<ObT> stage[SENS_WARPS];
+    __shared__ alignas(8) unsigned long long stage_bar[SENS_WARPS];  // one mbarrier per warp: "the stage holds the next env"
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned n = (unsigned)fl.hi;
     const unsigned stride = gridDim.x * SENS_WARPS;
     unsigned i = (unsigned)fl.lo + blockIdx.x * SENS_WARPS + warp;
     SensorStage<ObT>& st = stage[warp];
-    if (i < n) sensor_prefetch<OBST, ObT>(st, s, i, lane);
+    const uint32_t bar = opaque_u32((uint32_t)__cvta_generic_to_shared(&stage_bar[warp]));
+    const uint32_t stage_addr = (uint32_t)__cvta_generic_to_shared(&st);
+    if (lane == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");  // visible to the copy engine before the first fetch
+    }
+    __syncwarp();
+#if USV_PDL
+    if (OBST) {
+        if (tid < N_SENS) raytab[tid] = s.raytab[tid];  // written once at usvgpu_create: safe before the wait
+        if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<float>::no_hit();
+    }
+    pdl_wait();
+    if (i < n) sensor_prefetch<OBST, ObT>(stage_addr, bar, s, i, lane);
+    if (OBST) __syncthreads();
+#else
+    if (i < n) sensor_prefetch<OBST, ObT>(stage_addr, bar, s, i, lane);
     if (OBST) {
         if (tid < N_SENS) raytab[tid] = s.raytab[tid];
         if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<float>::no_hit();  // the "no hit" slot
         __syncthreads();
     }
+#endif
     if (i >= n) return;
+    const uint32_t ray_addr = opaque_u32((uint32_t)__cvta_generic_to_shared(raytab));
+    uint32_t parity = 0;
 
     for (;;) {
         // ---- this env's inputs: stage -> registers, then the stage is free for the next env -------
-        cp_async_wait_all();
-        __syncwarp();
+        mbar_wait(bar, parity);
+        parity ^= 1u;
         const Hand hd = st.hd;
         const float head = st.head[lane & (HDR_PAD - 1)];
         const int nob = OBST ? st.nob : 0;
         const double ox = (double)st.obst[lane], oy = (double)st.obst[MAX_OBST + lane];
         const double rr = (double)st.obst[2 * MAX_OBST + lane];
-        __syncwarp();
+        __syncwarp();  // every lane has read the stage: the copy engine may overwrite it
         const unsigned i_next = i + stride;
-        if (i_next < n) sensor_prefetch<OBST, ObT>(st, s, i_next, lane);  // in flight during this env's pass
+        if (i_next < n) sensor_prefetch<OBST, ObT>(stage_addr, bar, s, i_next, lane);  // in flight during this env's pass
+        else pdl_trigger();
 
         // ---- sensors, simple_env.py:203-226 ----------------------------------------------------
         float sens[4] = {1.0f, 1.0f, 1.0f, 1.0f};  // max range / 100 (simple_env.py:83); ignore_obstacles: all rays (:222-224)
         bool term = false, collided = false;
-        if (OBST) sensor_warp<float>(scratch[warp], raytab, lane, nob, hd.x, hd.y, hd.cs, hd.sn, ox, oy, rr, sens, 0.05, term, collided);
+        if (OBST) sensor_warp<float>(scratch[warp], ray_addr, lane, nob, hd.x, hd.y, hd.cs, hd.sn, ox, oy, rr, sens, 0.05, term, collided);
         finish_env<ObT>(s, fl, i, lane, head, sens, term, collided, hd.rew_part, hd.flags, obs, reward, terminated, truncated,
                         terminal_obs);
         if (i_next >= n) break;
@@ -685,7 +762,8 @@ sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const dou
     }
     double o[4];
     bool a, b;
-    sensor_warp<double>(scratch[warp], raytab, lane, nob, x, y, cps, sps, ox, oy, rr, o, 0.05, a, b);
+    const uint32_t ray_addr = opaque_u32((uint32_t)__cvta_generic_to_shared(raytab));  // after the barrier: the loads follow it
+    sensor_warp<double>(scratch[warp], ray_addr, lane, nob, x, y, cps, sps, ox, oy, rr, o, 0.05, a, b);
 #pragma unroll
     for (int p = 0; p < 4; ++p) out[(long long)(lane + 32 * p) * n + i] = o[p];
 }

@@ -96,13 +96,26 @@ __device__ __forceinline__ bool ray_test(const double2 t, const double bx, const
     return h < SENSOR_MAX_RANGE;                        // :458
 }
 
-// ox, oy, rr: this lane's obstacle (ignored when lane >= nob).  cps/sps = cos/sin(psi).
+// Entry k of the ray table (cos phi_k, sin phi_k) in shared memory, addressed by the table's 32-bit shared-window address:
+// the caller computes that address once per kernel and keeps it in a register (opaque_u32), where the compiler would
+// otherwise rebuild it from the CTA's window base at every use (S2UR + UMOV + ULEA per pass of phase B, r02 final SASS).
+__device__ __forceinline__ double2 ray_of(const uint32_t ray_addr, const int k) {
+    double2 t;
+    asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(t.x), "=d"(t.y) : "r"(ray_addr + 16u * (uint32_t)k));
+    return t;
+}
+__device__ __forceinline__ uint32_t opaque_u32(uint32_t v) {  // a value the compiler keeps instead of rematerialising
+    asm volatile("mov.u32 %0, %0;" : "+r"(v));
+    return v;
+}
+
+// ox, oy, rr: this lane's obstacle (ignored when lane >= nob).  cps/sps = cos/sin(psi).  ray_addr: see ray_of.
 // The caller sets sc.hpair[PAIR_SLOTS - 1] = Reading<HT>::no_hit() once (the "no hit" slot).
 // out[p]: reading of ray (lane + 32 p) in the form of Reading<HT>.
 // min_key_lt: warp-uniform "min over obstacles of key < key_thr" (simple_env.py:334); min_hit_lt: warp-uniform "min over
 // rays of reading < 0.2" (simple_env.py:153-156).
 template <typename HT>
-__device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2* __restrict__ raytab, const int lane,
+__device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const uint32_t ray_addr, const int lane,
                                             const int nob, const double x, const double y, const double cps,
                                             const double sps, const double ox, const double oy, const double rr,
                                             HT out[4], const double key_thr, bool& min_key_lt, bool& min_hit_lt) {
@@ -168,6 +181,7 @@ __device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2
     // pairs: bit k of `starts` marks an obstacle whose list starts at pair base + k, `before` counts those that
     // started earlier, so the owner of pair base + q is entry before + popc(starts & bits 0..q) - 1.
     bool ambiguous = total > PAIR_SLOTS - 1;  // out of pair slots (boat inside circles): exact path
+    uint32_t tie = 0xFFFFFFFFu;               // min over this lane's hits of (previous winner word ^ own word)
     if (!ambiguous) {
         const unsigned le_mask = 0xFFFFFFFFu >> (31 - lane);
         int before = -1;
@@ -182,15 +196,16 @@ __device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2
                 const double2 bxy = *reinterpret_cast<const double2*>(&sc.geo[j]);
                 const double rr2 = sc.geo[j].z;
                 double h;
-                if (ray_test(raytab[ri], bxy.x, bxy.y, rr2, h)) {
+                if (ray_test(ray_of(ray_addr, ri), bxy.x, bxy.y, rr2, h)) {
                     const uint32_t v = (uint32_t)rc.w | (uint32_t)t;
                     const uint32_t old = atomicMin(&sc.best[ri], v);
-                    ambiguous = ambiguous || ((old ^ v) < 256u);  // same ray, equal key bits: order undecided
+                    tie = min(tie, old ^ v);  // < 256: same ray, equal key bits -- order undecided
                     sc.hpair[t] = Reading<HT>::of(h);
                 }
             }
             before += __popc(starts);
         }
+        ambiguous = tie < 256u;
     }
     __syncwarp();
 
@@ -213,7 +228,7 @@ __device__ __forceinline__ void sensor_warp(SensorScratch<HT>& sc, const double2
         // (the lower slot wins a tie, as the reference's stable argsort does)
         double hmin = SENSOR_MAX_RANGE;
         for (int p = 0; p < 4; ++p) {
-            const double2 tb = raytab[lane + 32 * p];
+            const double2 tb = ray_of(ray_addr, lane + 32 * p);
             double bkey = INFINITY, bh = SENSOR_MAX_RANGE;
             for (int j = 0; j < n_cand; ++j) {
                 const double4 g = sc.geo[j];

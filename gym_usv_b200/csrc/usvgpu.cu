@@ -118,13 +118,32 @@ static int check_device(UsvGpu* h, int device) {
     return USV_OK;
 }
 
+// <<<grid, block, 0, st>>>, or the same launch with programmatic stream serialisation allowed (USV_PDL, usv_kernels.cuh)
+template <typename... KArgs, typename... Args>
+static void launch_k(void (*kern)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args... args) {
+#if USV_PDL
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+#else
+    kern<<<grid, block, 0, st>>>(KArgs(args)...);
+#endif
+}
+
 template <bool OBST, typename ObT>
 static void launch_sensor(UsvGpu* h, const StepFlags& fl, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
                           float* tobs, cudaStream_t st) {
     const long long need = (fl.hi - fl.lo + SENS_WARPS - 1) / SENS_WARPS;
     const long long resident = (long long)h->sm_count * SENS_MIN_CTAS;  // persistent: one wave, warps loop over envs
     const unsigned blocks = (unsigned)(need < resident ? need : resident);
-    sensor_kernel<OBST, ObT><<<blocks, SENS_WARPS * 32, 0, st>>>(h->sp, fl, obs, reward, term, trunc, tobs);
+    launch_k(sensor_kernel<OBST, ObT>, blocks, SENS_WARPS * 32, st, h->sp, fl, obs, reward, term, trunc, tobs);
 }
 
 // One VecEnv.step(): dynamics_kernel (thread per env) then sensor_kernel (warp per env), stream-ordered.
@@ -159,9 +178,9 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
     }
     const unsigned dblocks = (unsigned)((hi - lo + DYN_B - 1) / DYN_B);
     if (h->cfg.env_kind == USV_ENV_SIMPLE)
-        kinematic_kernel<<<(unsigned)((hi - lo + KIN_B - 1) / KIN_B), KIN_B, 0, st>>>(h->sp, fl, actions);
-    else if (h->cfg.do_perturb) dynamics_kernel<true><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
-    else dynamics_kernel<false><<<dblocks, DYN_B, 0, st>>>(h->sp, fl, actions);
+        kinematic_kernel<<<(unsigned)((hi - lo + KIN_B - 1) / KIN_B), KIN_B, 0, st>>>(h->sp, fl, actions, reward, term, trunc);
+    else if (h->cfg.do_perturb) launch_k(dynamics_kernel<true>, dblocks, DYN_B, st, h->sp, fl, actions, reward, term, trunc);
+    else launch_k(dynamics_kernel<false>, dblocks, DYN_B, st, h->sp, fl, actions, reward, term, trunc);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("dynamics launch: ") + cudaGetErrorString(e));
     if (mid) cudaEventRecord(mid, st);
