@@ -258,6 +258,7 @@ ca_kernel(CaPtrs s, StepFlags fl, const uint8_t* __restrict__ mask, const float*
     const long long n = s.n;
     const long long i = fl.lo + (long long)blockIdx.x * CA_B + threadIdx.x;
     if (i >= fl.hi) return;
+    pdl_wait();  // usv_state.cuh
     if (RESET && mask && !mask[i]) return;
     Pose p;
     Ctrl c;

@@ -39,25 +39,6 @@ constexpr int DYN_MIN_CTAS = 512 / DYN_B; // all of them resident at once (<= 12
 #ifndef USV_SENS_MIN_CTAS
 #define USV_SENS_MIN_CTAS 4   // 32 warps per SM at 64 registers (no spill with the float32 table); 3 x 8 warps at 76: +1 % time (r02f)
 #endif
-// Programmatic dependent launch between the kernels of consecutive launches (build knob, 0 = off): 1 = the launches carry
-// cudaLaunchAttributeProgrammaticStreamSerialization and every kernel runs griddepcontrol.wait before it touches anything
-// another kernel wrote (its own prologue -- parameters, indices, the ray table -- overlaps the previous kernel's drain);
-// 2 = the kernels also signal griddepcontrol.launch_dependents once their main loop is behind them.
-// Measured at 65 536 envs (r02m, us per step): off 68.63, 1: 67.83, 2: 68.03.  (An early trigger -- at kernel start,
-// r02d -- made it 92: dependents that become resident early only sit in the wait.)
-#ifndef USV_PDL
-#define USV_PDL 1
-#endif
-__device__ __forceinline__ void pdl_wait() {
-#if USV_PDL
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-#endif
-}
-__device__ __forceinline__ void pdl_trigger() {
-#if USV_PDL >= 2
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-#endif
-}
 constexpr int SENS_WARPS = USV_SENS_WARPS;    // warps (= envs) per CTA of the sensor kernel
 constexpr int SENS_MIN_CTAS = USV_SENS_MIN_CTAS; // resident CTAs per SM the persistent grid is sized for
 
@@ -287,6 +268,7 @@ kinematic_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions, f
     const long long n = s.n;
     const long long i = fl.lo + (long long)blockIdx.x * KIN_B + threadIdx.x;
     if (i >= fl.hi) return;
+    pdl_wait();
     double* dyn = s.dyn + i;
     Pose p;
     p.x = dyn[(long long)D_X * n];

@@ -395,6 +395,7 @@ legacy_step_kernel(LegacyPtrs s, StepFlags fl, const float* __restrict__ actions
     const long long n = s.n;
     const long long i = fl.lo + (long long)blockIdx.x * LEG_B + threadIdx.x;
     if (i >= fl.hi) return;
+    pdl_wait();  // usv_state.cuh
     float* st = s.st + i;
     float f[LEG_ROWS];
 #pragma unroll
@@ -475,6 +476,7 @@ legacy64_step_kernel(LegacyPtrs s, StepFlags fl, const float* __restrict__ actio
     const long long n = s.n;
     const long long i = fl.lo + (long long)blockIdx.x * LEG_B + threadIdx.x;
     if (i >= fl.hi) return;
+    pdl_wait();  // usv_state.cuh
     double* st = s.st64 + i;
     double f[LEG64_ROWS];
 #pragma unroll

@@ -118,7 +118,7 @@ static int check_device(UsvGpu* h, int device) {
     return USV_OK;
 }
 
-// <<<grid, block, 0, st>>>, or the same launch with programmatic stream serialisation allowed (USV_PDL, usv_kernels.cuh)
+// <<<grid, block, 0, st>>>, or the same launch with programmatic stream serialisation allowed (USV_PDL, usv_state.cuh)
 template <typename... KArgs, typename... Args>
 static void launch_k(void (*kern)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args... args) {
 #if USV_PDL
@@ -152,8 +152,8 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
     if (hi < 0) hi = h->sp.n;
     const StepFlags fl = {h->cfg.do_perturb, h->cfg.skip_kinematic, h->cfg.max_episode_steps, h->cfg.auto_reset, lo, hi};
     if (h->ca) {  // 'usv-asmc-ca-v0': one kernel, thread per env
-        ca_kernel<false><<<(unsigned)((hi - lo + CA_B - 1) / CA_B), CA_B, 0, st>>>(h->cp, fl, nullptr, actions, obs, reward, term,
-                                                                                  trunc, tobs, UsvCaResetOptions{});
+        launch_k(ca_kernel<false>, (unsigned)((hi - lo + CA_B - 1) / CA_B), CA_B, st, h->cp, fl, (const uint8_t*)nullptr, actions,
+                 obs, reward, term, trunc, tobs, UsvCaResetOptions{});
         cudaError_t ce = cudaGetLastError();
         if (ce != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("ca step launch: ") + cudaGetErrorString(ce));
         if (mid) cudaEventRecord(mid, st);
@@ -164,11 +164,11 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
     if (h->legacy) {  // 'usv-asmc-v0' and its float64 siblings: one kernel, thread per env
         const unsigned lblocks = (unsigned)((hi - lo + LEG_B - 1) / LEG_B);
         if (h->lp.variant == LEG_YE_INT)
-            legacy64_step_kernel<LEG_YE_INT><<<lblocks, LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term, trunc, tobs);
+            launch_k(legacy64_step_kernel<LEG_YE_INT>, lblocks, LEG_B, st, h->lp, fl, actions, obs, reward, term, trunc, tobs);
         else if (h->lp.variant == LEG_PID)
-            legacy64_step_kernel<LEG_PID><<<lblocks, LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term, trunc, tobs);
+            launch_k(legacy64_step_kernel<LEG_PID>, lblocks, LEG_B, st, h->lp, fl, actions, obs, reward, term, trunc, tobs);
         else
-            legacy_step_kernel<<<lblocks, LEG_B, 0, st>>>(h->lp, fl, actions, obs, reward, term, trunc, tobs);
+            launch_k(legacy_step_kernel, lblocks, LEG_B, st, h->lp, fl, actions, obs, reward, term, trunc, tobs);
         cudaError_t le = cudaGetLastError();
         if (le != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("legacy step launch: ") + cudaGetErrorString(le));
         if (mid) cudaEventRecord(mid, st);
@@ -178,7 +178,7 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
     }
     const unsigned dblocks = (unsigned)((hi - lo + DYN_B - 1) / DYN_B);
     if (h->cfg.env_kind == USV_ENV_SIMPLE)
-        kinematic_kernel<<<(unsigned)((hi - lo + KIN_B - 1) / KIN_B), KIN_B, 0, st>>>(h->sp, fl, actions, reward, term, trunc);
+        launch_k(kinematic_kernel, (unsigned)((hi - lo + KIN_B - 1) / KIN_B), KIN_B, st, h->sp, fl, actions, reward, term, trunc);
     else if (h->cfg.do_perturb) launch_k(dynamics_kernel<true>, dblocks, DYN_B, st, h->sp, fl, actions, reward, term, trunc);
     else launch_k(dynamics_kernel<false>, dblocks, DYN_B, st, h->sp, fl, actions, reward, term, trunc);
     cudaError_t e = cudaGetLastError();
