@@ -166,6 +166,7 @@ _SIGNATURES = {
     "usvgpu_asmc_compute": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64,
                                       C.c_int32, C.c_void_p, C.c_void_p]),
     "usvgpu_sensors": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "usvgpu_sensors_noalloc": (C.c_int, [C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "usvgpu_frame_stack_push": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 7),
     "usvgpu_render": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "usvgpu_step_info": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
@@ -181,6 +182,7 @@ _SIGNATURES = {
 
 EXPORTS = tuple(_SIGNATURES)
 CA_MAX_OBSTACLES = 9  # USVGPU_CA_MAX_OBSTACLES
+NOALLOC_MAX_ENVS = 8192  # USVGPU_NOALLOC_MAX_ENVS
 
 
 class UsvCaResetOptions(C.Structure):  # include/usvgpu.h

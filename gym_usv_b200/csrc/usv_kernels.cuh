@@ -751,6 +751,59 @@ sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const dou
 }
 
 // ---------------------------------------------------------------------------------------------
+// usvgpu_sensors_noalloc (include/usvgpu.h): the same sensor pass as sensors_unit_kernel with the obstacle table first
+// re-laid in library-owned scratch as one 768-byte row per env (x[32] y[32] radius[32], the layout of the step's
+// sensor-input rows), so that a warp reads its env's obstacles as three coalesced 256-byte loads instead of 96 loads
+// that are n doubles apart.  Two kernels, stream-ordered; the scratch is the caller's (the entry point's) to provide.
+// ---------------------------------------------------------------------------------------------
+constexpr int STAGE_ENVS = 32;  // envs per CTA of the staging transpose
+// obstacles [32][3][n] -> rows [n][3][32]; slots >= n_obs[i] are written as 0: no byte of a row outlives the call that
+// wrote it, whatever an earlier (larger) call left there
+__global__ void __launch_bounds__(256)
+sensors_stage_kernel(long long n, const double* __restrict__ obstacles, const int* __restrict__ n_obs,
+                     double* __restrict__ rows) {
+    __shared__ double tile[OBST_ROW][STAGE_ENVS + 1];
+    __shared__ int nob[STAGE_ENVS];
+    const long long i0 = (long long)blockIdx.x * STAGE_ENVS;
+    const int tid = threadIdx.x, e = tid & (STAGE_ENVS - 1);
+    if (tid < STAGE_ENVS) nob[tid] = (i0 + tid < n) ? n_obs[i0 + tid] : 0;
+    for (int k = tid >> 5; k < OBST_ROW; k += 8) {  // k = slot * 3 + component: one 256-byte segment of input row k
+        const int slot = k / 3, comp = k - 3 * slot;
+        tile[comp * MAX_OBST + slot][e] = (i0 + e < n) ? obstacles[(long long)k * n + i0 + e] : 0.0;
+    }
+    __syncthreads();
+    for (int q = tid; q < STAGE_ENVS * OBST_ROW; q += 256) {  // the CTA's 32 rows are contiguous: 24 KB written in order
+        const int env = q / OBST_ROW, col = q - env * OBST_ROW;
+        if (i0 + env < n) rows[(i0 + env) * OBST_ROW + col] = ((col & (MAX_OBST - 1)) < nob[env]) ? tile[col][env] : 0.0;
+    }
+}
+
+__global__ void __launch_bounds__(SENS_WARPS * 32)
+sensors_rows_kernel(long long n, const double2* __restrict__ g_raytab, const double* __restrict__ pose,
+                    const double* __restrict__ rows, const int* __restrict__ n_obs, double* __restrict__ out) {
+    __shared__ double2 raytab[N_SENS];
+    __shared__ SensorScratch<double> scratch[SENS_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < N_SENS) raytab[tid] = g_raytab[tid];
+    if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<double>::no_hit();
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
+    if (i >= n) return;
+    const double x = pose[i], y = pose[n + i], psi = pose[2 * n + i];
+    double sps, cps;
+    sincos(psi, &sps, &cps);
+    const int nob = n_obs[i];
+    const double* row = rows + i * OBST_ROW;
+    const double ox = row[lane], oy = row[MAX_OBST + lane], rr = row[2 * MAX_OBST + lane];
+    double o[4];
+    bool a, b;
+    const uint32_t ray_addr = opaque_u32((uint32_t)__cvta_generic_to_shared(raytab));
+    sensor_warp<double>(scratch[warp], ray_addr, lane, nob, x, y, cps, sps, ox, oy, rr, o, 0.05, a, b);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) out[(long long)(lane + 32 * p) * n + i] = o[p];
+}
+
+// ---------------------------------------------------------------------------------------------
 // probes (include/usvgpu.h: usvgpu_math_probe, usvgpu_fp64_peak)
 // ---------------------------------------------------------------------------------------------
 __global__ void math_probe_kernel(int which, long long n, const double* __restrict__ in, double* __restrict__ out) {

@@ -14,6 +14,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -771,6 +772,61 @@ int usvgpu_sensors(int device, int64_t n, const double* pose, const double* obst
     const unsigned blocks = (unsigned)((n + SENS_WARPS - 1) / SENS_WARPS);
     sensors_unit_kernel<<<blocks, SENS_WARPS * 32, 0, (cudaStream_t)stream>>>(n, g_raytab[device & 63], pose, obstacles,
                                                                             n_obs, out);
+    CU_TRY(nullptr, cudaGetLastError());
+    return USV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// usvgpu_sensors_noalloc: the scratch of the no-allocation sensor entry point lives in the module image, not on the heap.
+// Every GPU that loads this library holds the array (6 MiB + 2 KiB) until the process exits.  Layout: the staged
+// obstacle rows of up to USVGPU_NOALLOC_MAX_ENVS envs (96 doubles each), then the 128-entry ray table.
+// In HOST code the name `g_noalloc_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, once per device with that device current (noalloc_setup), and only that pointer is handed to
+// kernels.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t NOALLOC_ROW_DOUBLES = (size_t)USVGPU_NOALLOC_MAX_ENVS * OBST_ROW;
+constexpr size_t NOALLOC_DOUBLES = NOALLOC_ROW_DOUBLES + 2 * (size_t)N_SENS;
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_DOUBLES];
+static double* g_noalloc_ptr[64] = {nullptr};  // per device: device address of g_noalloc_scratch, ray table in place
+static std::mutex g_noalloc_mutex;
+
+// once per device, with that device current: symbol address, then the ray table (2 KiB, a plain copy: nothing is allocated)
+static int noalloc_setup(int device, double** out) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device & 63]) {
+        double* ptr = nullptr;
+        CU_TRY(nullptr, cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+        if (!ptr) return fail(nullptr, USV_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the no-alloc scratch");
+        double2 t[N_SENS];
+        host_raytab(t);
+        CU_TRY(nullptr, cudaMemcpy(ptr + NOALLOC_ROW_DOUBLES, t, sizeof(t), cudaMemcpyHostToDevice));
+        g_noalloc_ptr[device & 63] = ptr;
+    }
+    *out = g_noalloc_ptr[device & 63];
+    return USV_OK;
+}
+
+int usvgpu_sensors_noalloc(int device, int64_t n, const double* pose, const double* obstacles, const int32_t* n_obs,
+                           double* out, void* stream) {
+    if (!pose || !obstacles || !n_obs || !out || n <= 0) return fail(nullptr, USV_ERR_INVALID, "bad sensors arguments");
+    if (n > USVGPU_NOALLOC_MAX_ENVS)
+        return fail(nullptr, USV_ERR_INVALID,
+                    "usvgpu_sensors_noalloc: n = " + std::to_string((long long)n) + " envs exceeds the fixed scratch of " +
+                        std::to_string(USVGPU_NOALLOC_MAX_ENVS) + " envs (USVGPU_NOALLOC_MAX_ENVS); split the batch or use usvgpu_sensors");
+    if (device < 0 || device >= 64) return fail(nullptr, USV_ERR_INVALID, "usvgpu_sensors_noalloc: device index outside 0..63");
+    int rc = check_device(nullptr, device);
+    if (rc) return rc;
+    DeviceGuard dev_guard(device);
+    CU_TRY(nullptr, dev_guard.err);
+    double* scratch = nullptr;
+    rc = noalloc_setup(device, &scratch);
+    if (rc) return rc;
+    double* rows = scratch;
+    const double2* raytab = reinterpret_cast<const double2*>(scratch + NOALLOC_ROW_DOUBLES);
+    cudaStream_t st = (cudaStream_t)stream;
+    sensors_stage_kernel<<<(unsigned)((n + STAGE_ENVS - 1) / STAGE_ENVS), 256, 0, st>>>(n, obstacles, n_obs, rows);
+    CU_TRY(nullptr, cudaGetLastError());
+    sensors_rows_kernel<<<(unsigned)((n + SENS_WARPS - 1) / SENS_WARPS), SENS_WARPS * 32, 0, st>>>(n, raytab, pose, rows, n_obs, out);
     CU_TRY(nullptr, cudaGetLastError());
     return USV_OK;
 }

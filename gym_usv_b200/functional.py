@@ -53,6 +53,23 @@ def sensor_distances(pose: torch.Tensor, obstacles: torch.Tensor, n_obs: torch.T
     return out
 
 
+def sensor_distances_noalloc(pose: torch.Tensor, obstacles: torch.Tensor, n_obs: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """sensor_distances through usvgpu_sensors_noalloc (no counterpart in the reference; include/usvgpu.h): the library
+    allocates nothing -- its scratch is a fixed static device array -- and the caller brings ``out`` (float64 [128, n]).
+    At most ``NOALLOC_MAX_ENVS`` envs per call; calls that overlap on the GPU race on the shared scratch."""
+    if not pose.is_cuda:
+        raise nat.UsvError("sensor_distances_noalloc needs CUDA tensors: there is no CPU fallback")
+    n = pose.shape[1]
+    assert pose.dtype == torch.float64 and pose.is_contiguous() and pose.shape[0] == 3
+    assert obstacles.dtype == torch.float64 and obstacles.is_contiguous() and tuple(obstacles.shape) == (32, 3, n)
+    assert n_obs.dtype == torch.int32 and n_obs.is_contiguous() and n_obs.shape[0] == n
+    assert out.dtype == torch.float64 and out.is_contiguous() and tuple(out.shape) == (nat.SENSORS, n) and out.device == pose.device
+    nat.check(nat.lib().usvgpu_sensors_noalloc(nat.device_index(pose.device), n, C.c_void_p(pose.data_ptr()),
+                                               C.c_void_p(obstacles.data_ptr()), C.c_void_p(n_obs.data_ptr()),
+                                               C.c_void_p(out.data_ptr()), _stream(pose.device)))
+    return out
+
+
 def math_probe(which: str, x: torch.Tensor) -> torch.Tensor:
     """Evaluate one float64 device routine of csrc/usv_math.cuh (test surface).  which: 'sqrt' x[n] | 'div' x[2,n] |
     'asin' x[n] | 'rot' x[3,n] = (delta, cos, sin) -> [2,n]."""

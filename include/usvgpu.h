@@ -245,6 +245,21 @@ int usvgpu_asmc_compute(int device, int64_t n, double* state, const double* acti
 int usvgpu_sensors(int device, int64_t n, const double* pose, const double* obstacles, const int32_t* n_obs,
                    double* out, void* stream);
 
+/* usvgpu_sensors for callers that must not allocate (code under CUDA graph capture, serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments,
+ * same results as usvgpu_sensors (which allocates its ray table on a device's first call).  This one calls no
+ * cudaMalloc / cudaFree and no allocating library routine: its scratch -- the obstacle table re-laid as one 768-byte
+ * row per env, plus the 2 KiB ray table -- is a file-scope `static __device__` array of
+ * USVGPU_NOALLOC_MAX_ENVS * 768 + 2048 bytes (6 MiB + 2 KiB) that every GPU loading the library holds until the
+ * process exits.  n > USVGPU_NOALLOC_MAX_ENVS is refused with USV_ERR_INVALID and a message (usvgpu_last_error(NULL)).
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress) and copies the ray table in; make
+ * that call outside stream capture.  ALL calls share the one array, which keeps the last call's contents: every row a
+ * call reads it has written itself first (unused obstacle slots as 0), so nothing needs clearing between calls, but
+ * two calls that overlap on the GPU (different streams, or graphs replayed concurrently) race on it -- order them. */
+#define USVGPU_NOALLOC_MAX_ENVS 8192
+int usvgpu_sensors_noalloc(int device, int64_t n, const double* pose, const double* obstacles, const int32_t* n_obs,
+                           double* out, void* stream);
+
 /* Replaces stable_baselines3 VecFrameStack / StackedObservations.update (train_test/sb3_train_vec.py:70,
  * train_test/sb3_train.py:50-51: n_stack = 5) for device-resident observations, without moving old frames.
  * ring: float32 [N][2 * n_stack][obs_dim], zero-initialised by the caller.  Call k (k = 0 for the reset observation)
