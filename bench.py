@@ -296,10 +296,6 @@ def workload_config(args, world, reference_sample=None):
         "actions": "uniform in the action box, pre-staged on device",
         "l2": f"{args.batches} rotating env batches per GPU (consecutive steps touch different state; working set > 126 MB L2)",
     }
-    ov = getattr(args, "overlap", None)
-    if ov and not kin and args.envs_per_gpu > ov[0]:
-        cfg["overlap"] = {"chunk_envs": ov[0], "sensor_ctas_per_sm": ov[1], "dynamics_ctas_per_sm": ov[2],
-                          "what": "usvgpu_set_overlap: sensors of chunk c beside the dynamics of chunk c + 1 (two streams)"}
     if reference_sample is not None:
         cfg["reference_sample_envs"] = reference_sample
     return cfg
@@ -319,9 +315,6 @@ class Workload:
                                  ignore_obstacles=bool(no_obstacles), obstacles_f32=bool(obstacles_f32),
                                  info_mode="lazy", env_id=env_id)
             e.reset_tensor()
-            ov = getattr(args, "overlap", None)
-            if ov and env_id == "usv-asmc-simple" and n > ov[0]:
-                e.set_overlap(*ov)
             self.envs.append(e)
         self.A = 8
         gen = torch.Generator(device=dev).manual_seed(1234 + lo)
@@ -439,8 +432,6 @@ def run_ours(args, rank, local_rank, world):
                   args.batches, args.seed)
     envs, acts, A = wl.envs, wl.acts, wl.A
     launches_per_step = 1 if legacy else 2
-    if args.overlap and args.env == "usv-asmc-simple" and hi - lo > args.overlap[0]:
-        launches_per_step = 2 * ((hi - lo + args.overlap[0] - 1) // args.overlap[0])
 
     wl.preroll(args.preroll)
     wl.loop(args.warmup)  # W untimed warm-up steps through the public per-step call
@@ -672,8 +663,6 @@ def main():
     ap.add_argument("--no-obstacles", action="store_true", help="configs[1] semantics (ignore_obstacles=True)")
     ap.add_argument("--obstacles-f32", type=int, default=1)
     ap.add_argument("--seed", type=int, default=0)
-    ap.add_argument("--overlap", default="", help="chunk_envs,sensor_ctas_per_sm,dynamics_ctas_per_sm: overlapped step "
-                    "(usvgpu_set_overlap) for shards larger than chunk_envs; empty = the plain two-launch step")
     ap.add_argument("--e2e-steps", type=int, default=60)
     ap.add_argument("--mapped-obs", type=int, default=0, help="e2e: sensor kernel stores obs rows straight to mapped host memory")
     ap.add_argument("--ref-envs", type=int, default=4096, help="bounded CPU sample: lock-step envs per oracle step")
@@ -682,9 +671,6 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
-    args.overlap = tuple(int(x) for x in args.overlap.split(",")) if args.overlap else None
-    if args.overlap and len(args.overlap) != 3:
-        ap.error("--overlap takes chunk_envs,sensor_ctas_per_sm,dynamics_ctas_per_sm")
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -156,7 +156,6 @@ _SIGNATURES = {
     "usvgpu_step_host": (C.c_int, [C.c_void_p] * 6 + [C.c_int32, C.c_void_p]),
     "usvgpu_stream_sync": (C.c_int, [C.c_void_p, C.c_void_p]),
     "usvgpu_set_host_chunks": (C.c_int, [C.c_void_p, C.c_int32]),
-    "usvgpu_set_overlap": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32]),
     "usvgpu_flags_sync": (C.c_int, [C.c_void_p]),
     "usvgpu_terminal_obs_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "usvgpu_field_bytes": (C.c_int64, [C.c_void_p, C.c_int32]),

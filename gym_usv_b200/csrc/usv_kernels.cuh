@@ -253,24 +253,6 @@ dynamics_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions, fl
     store_step_scalars(s, i, hd, reward, terminated, truncated);
 }
 
-// The same per-env program with a grid of FIXED size: every warp walks 32-env groups blockIdx, blockIdx + gridDim, ...
-// Only the overlapped step (usvgpu_set_overlap, usvgpu.cu step_overlapped) launches it: there the dynamics of chunk c + 1
-// must leave part of every SM's register file to the sensor CTAs of chunk c, and a grid of (SMs x d) one-warp CTAs is how
-// the host says "d dynamics warps per SM, no more".
-template <bool PERTURB>
-__global__ void __launch_bounds__(DYN_B, DYN_MIN_CTAS)
-dynamics_walk_kernel(StatePtrs s, StepFlags fl, const float* __restrict__ actions, float* __restrict__ reward,
-                     uint8_t* __restrict__ terminated, uint8_t* __restrict__ truncated) {
-    pdl_wait();
-    for (long long i = fl.lo + (long long)blockIdx.x * DYN_B + threadIdx.x; i < fl.hi; i += (long long)gridDim.x * DYN_B) {
-        Hand hd;
-        float4 hrow[4];
-        dyn_env<PERTURB>(s, fl, actions, i, hd, hrow);
-        store_handover(s, i, hd, hrow);
-        store_step_scalars(s, i, hd, reward, terminated, truncated);
-    }
-}
-
 // ---------------------------------------------------------------------------------------------
 // 'usv-simple' (UsvSimpleEnv.step, simple_env.py:310-346; the env train_test/sb3_train_vec.py:55 trains on): the
 // action drives the kinematic update directly, no controller.  Thread per env, 9 float64 columns in, 9 out, then the

@@ -31,7 +31,6 @@
 using namespace usv;
 
 constexpr int HOST_CHUNKS_MAX = 16;
-constexpr int OVL_CHUNKS_MAX = 64;  // chunks of one overlapped step (usvgpu_set_overlap)
 
 struct UsvGpu {
     UsvConfig cfg;
@@ -64,13 +63,6 @@ struct UsvGpu {
     int host_chunks;
     cudaEvent_t ev_flags;   // reward / flags of the last usvgpu_step_host have reached the host
     bool own_staging;   // false after usvgpu_use_staging(): the caller's device buffers are used instead
-    // overlapped step (usvgpu_set_overlap): sensors of chunk c on `ovl` beside the dynamics of chunk c + 1 on the caller's stream
-    long long ovl_chunk;    // envs per chunk; 0 = off (the plain two-launch step)
-    int ovl_sens_ctas;      // sensor CTAs per SM while dynamics CTAs share the SM
-    int ovl_dyn_ctas;       // one-warp dynamics CTAs per SM while sensor CTAs share the SM
-    cudaStream_t ovl;
-    cudaEvent_t ovl_ev[OVL_CHUNKS_MAX];
-    cudaEvent_t ovl_join;
 };
 
 static thread_local std::string g_create_err;
@@ -148,70 +140,11 @@ static void launch_k(void (*kern)(KArgs...), unsigned grid, unsigned block, cuda
 
 template <bool OBST, typename ObT>
 static void launch_sensor(UsvGpu* h, const StepFlags& fl, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
-                          float* tobs, cudaStream_t st, int ctas_per_sm = SENS_MIN_CTAS) {
+                          float* tobs, cudaStream_t st) {
     const long long need = (fl.hi - fl.lo + SENS_WARPS - 1) / SENS_WARPS;
-    const long long resident = (long long)h->sm_count * ctas_per_sm;  // persistent: one wave, warps loop over envs
+    const long long resident = (long long)h->sm_count * SENS_MIN_CTAS;  // persistent: one wave, warps loop over envs
     const unsigned blocks = (unsigned)(need < resident ? need : resident);
     launch_k(sensor_kernel<OBST, ObT>, blocks, SENS_WARPS * 32, st, h->sp, fl, obs, reward, term, trunc, tobs);
-}
-
-static void launch_sensor_any(UsvGpu* h, const StepFlags& fl, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
-                              float* tobs, cudaStream_t st, int ctas_per_sm = SENS_MIN_CTAS) {
-    const bool f32 = h->cfg.obstacles_f32 != 0;
-    if (h->cfg.ignore_obstacles) {
-        if (f32) launch_sensor<false, float>(h, fl, obs, reward, term, trunc, tobs, st, ctas_per_sm);
-        else launch_sensor<false, double>(h, fl, obs, reward, term, trunc, tobs, st, ctas_per_sm);
-    } else {
-        if (f32) launch_sensor<true, float>(h, fl, obs, reward, term, trunc, tobs, st, ctas_per_sm);
-        else launch_sensor<true, double>(h, fl, obs, reward, term, trunc, tobs, st, ctas_per_sm);
-    }
-}
-
-// One VecEnv.step() of a LARGE shard as a two-stream pipeline over chunks of envs (usvgpu_set_overlap):
-//   caller's stream   D(0)      D(1)      D(2)  ...  D(C-1)             wait
-//   h->ovl (priority)       S(0)      S(1)      ...        S(C-2)  S(C-1)
-// S(c) waits for D(c) only (an event); the envs of different chunks share nothing, so D(c + 1) runs beside S(c).  The two
-// kernels are bound by different things (FP64 pipe and dependent latency / instruction issue) and each alone leaves the
-// other's resource idle.  What makes them share an SM is the register file: the sensor grid is sized to `ovl_sens_ctas`
-// CTAs per SM and the dynamics runs as dynamics_walk_kernel with `ovl_dyn_ctas` one-warp CTAs per SM (the plain dynamics
-// grid would take every register of every SM, one wave at a time).  D(0) has no partner and runs as the plain kernel; the
-// last S runs with the full grid.  Results are bit-identical to the plain step: the same per-env code on the same envs.
-static int step_overlapped(UsvGpu* h, const float* actions, float* obs, float* reward, uint8_t* term, uint8_t* trunc,
-                           float* tobs, cudaStream_t st) {
-    const long long n = h->sp.n;
-    const long long chunk = h->ovl_chunk;
-    const int C = (int)((n + chunk - 1) / chunk);
-    if (!h->ovl) {
-        int lo_pri = 0, hi_pri = 0;
-        CU_TRY(h, cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
-        CU_TRY(h, cudaStreamCreateWithPriority(&h->ovl, cudaStreamNonBlocking, hi_pri));
-        CU_TRY(h, cudaEventCreateWithFlags(&h->ovl_join, cudaEventDisableTiming));
-        for (int c = 0; c < OVL_CHUNKS_MAX; ++c) CU_TRY(h, cudaEventCreateWithFlags(&h->ovl_ev[c], cudaEventDisableTiming));
-    }
-    for (int c = 0; c < C; ++c) {
-        const long long lo = c * chunk, hi = (lo + chunk < n) ? lo + chunk : n;
-        const StepFlags fl = {h->cfg.do_perturb, h->cfg.skip_kinematic, h->cfg.max_episode_steps, h->cfg.auto_reset, lo, hi};
-        const long long groups = (hi - lo + DYN_B - 1) / DYN_B;
-        if (c == 0) {
-            if (h->cfg.do_perturb) launch_k(dynamics_kernel<true>, (unsigned)groups, DYN_B, st, h->sp, fl, actions, reward, term, trunc);
-            else launch_k(dynamics_kernel<false>, (unsigned)groups, DYN_B, st, h->sp, fl, actions, reward, term, trunc);
-        } else {
-            const long long cap = (long long)h->sm_count * h->ovl_dyn_ctas;
-            const unsigned grid = (unsigned)(groups < cap ? groups : cap);
-            if (h->cfg.do_perturb) launch_k(dynamics_walk_kernel<true>, grid, DYN_B, st, h->sp, fl, actions, reward, term, trunc);
-            else launch_k(dynamics_walk_kernel<false>, grid, DYN_B, st, h->sp, fl, actions, reward, term, trunc);
-        }
-        CU_TRY(h, cudaGetLastError());
-        CU_TRY(h, cudaEventRecord(h->ovl_ev[c], st));
-        CU_TRY(h, cudaStreamWaitEvent(h->ovl, h->ovl_ev[c], 0));
-        launch_sensor_any(h, fl, obs, reward, term, trunc, tobs, h->ovl, c == C - 1 ? SENS_MIN_CTAS : h->ovl_sens_ctas);
-        CU_TRY(h, cudaGetLastError());
-    }
-    CU_TRY(h, cudaEventRecord(h->ovl_join, h->ovl));
-    CU_TRY(h, cudaStreamWaitEvent(st, h->ovl_join, 0));
-    h->host_env_steps += (unsigned long long)n;
-    h->launches += 2ull * C;
-    return USV_OK;
 }
 
 // One VecEnv.step(): dynamics_kernel (thread per env) then sensor_kernel (warp per env), stream-ordered.
@@ -244,8 +177,6 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
         h->launches += 1;
         return USV_OK;
     }
-    if (h->ovl_chunk > 0 && h->ovl_chunk < h->sp.n && !mid && lo == 0 && hi == h->sp.n && h->cfg.env_kind != USV_ENV_SIMPLE)
-        return step_overlapped(h, actions, obs, reward, term, trunc, tobs, st);
     const unsigned dblocks = (unsigned)((hi - lo + DYN_B - 1) / DYN_B);
     if (h->cfg.env_kind == USV_ENV_SIMPLE)
         launch_k(kinematic_kernel, (unsigned)((hi - lo + KIN_B - 1) / KIN_B), KIN_B, st, h->sp, fl, actions, reward, term, trunc);
@@ -254,7 +185,14 @@ static int step_impl(UsvGpu* h, const float* actions, float* obs, float* reward,
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("dynamics launch: ") + cudaGetErrorString(e));
     if (mid) cudaEventRecord(mid, st);
-    launch_sensor_any(h, fl, obs, reward, term, trunc, tobs, st);
+    const bool f32 = h->cfg.obstacles_f32 != 0;
+    if (h->cfg.ignore_obstacles) {
+        if (f32) launch_sensor<false, float>(h, fl, obs, reward, term, trunc, tobs, st);
+        else launch_sensor<false, double>(h, fl, obs, reward, term, trunc, tobs, st);
+    } else {
+        if (f32) launch_sensor<true, float>(h, fl, obs, reward, term, trunc, tobs, st);
+        else launch_sensor<true, double>(h, fl, obs, reward, term, trunc, tobs, st);
+    }
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(h, USV_ERR_CUDA, std::string("sensor launch: ") + cudaGetErrorString(e));
     h->host_env_steps += (unsigned long long)(hi - lo);
@@ -337,11 +275,6 @@ int usvgpu_create(const UsvConfig* cfg, int device, int64_t n_envs, int64_t glob
     for (int c = 0; c < HOST_CHUNKS_MAX; ++c) h->ev_chunk[c] = nullptr;
     h->host_chunks = 2;
     h->own_staging = true;
-    h->ovl_chunk = 0;
-    h->ovl_sens_ctas = h->ovl_dyn_ctas = 0;
-    h->ovl = nullptr;
-    h->ovl_join = nullptr;
-    for (int c = 0; c < OVL_CHUNKS_MAX; ++c) h->ovl_ev[c] = nullptr;
     cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device);
     memset(&h->sp, 0, sizeof(h->sp));
     h->sp.n = n_envs;
@@ -454,10 +387,6 @@ int usvgpu_destroy(usvgpu_handle h) {
     if (h->h_ep) cudaFreeHost(h->h_ep);
     if (h->side) cudaStreamDestroy(h->side);
     if (h->copy) cudaStreamDestroy(h->copy);
-    if (h->ovl) cudaStreamDestroy(h->ovl);
-    if (h->ovl_join) cudaEventDestroy(h->ovl_join);
-    for (int c = 0; c < OVL_CHUNKS_MAX; ++c)
-        if (h->ovl_ev[c]) cudaEventDestroy(h->ovl_ev[c]);
     if (h->ev_flags) cudaEventDestroy(h->ev_flags);
     if (h->ev_copied) cudaEventDestroy(h->ev_copied);
     for (int c = 0; c < HOST_CHUNKS_MAX; ++c)
@@ -508,24 +437,6 @@ int usvgpu_step(usvgpu_handle h, const float* actions, float* obs, float* reward
     DeviceGuard dev_guard(h->device);
     CU_TRY(h, dev_guard.err);
     return step_impl(h, actions, obs, reward, terminated, truncated, terminal_obs, (cudaStream_t)stream);
-}
-
-int usvgpu_set_overlap(usvgpu_handle h, int64_t chunk_envs, int32_t sensor_ctas_per_sm, int32_t dynamics_ctas_per_sm) {
-    if (!h) return USV_ERR_INVALID;
-    if (chunk_envs == 0) {
-        h->ovl_chunk = 0;
-        return USV_OK;
-    }
-    if (h->legacy || h->ca || h->cfg.env_kind == USV_ENV_SIMPLE)
-        return fail(h, USV_ERR_INVALID, "usvgpu_set_overlap: only the two-kernel ASMC step (usv-asmc-simple) has anything to overlap");
-    if (chunk_envs < 0 || chunk_envs % 256) return fail(h, USV_ERR_INVALID, "usvgpu_set_overlap: chunk_envs must be a positive multiple of 256");
-    if ((h->sp.n + chunk_envs - 1) / chunk_envs > OVL_CHUNKS_MAX) return fail(h, USV_ERR_INVALID, "usvgpu_set_overlap: more than 64 chunks");
-    if (sensor_ctas_per_sm < 1 || sensor_ctas_per_sm > SENS_MIN_CTAS) return fail(h, USV_ERR_INVALID, "usvgpu_set_overlap: sensor CTAs per SM outside 1..4");
-    if (dynamics_ctas_per_sm < 1 || dynamics_ctas_per_sm > DYN_MIN_CTAS) return fail(h, USV_ERR_INVALID, "usvgpu_set_overlap: dynamics CTAs per SM outside 1..16");
-    h->ovl_chunk = chunk_envs;
-    h->ovl_sens_ctas = sensor_ctas_per_sm;
-    h->ovl_dyn_ctas = dynamics_ctas_per_sm;
-    return USV_OK;
 }
 
 int usvgpu_step_timed(usvgpu_handle h, const float* actions, float* obs, float* reward, uint8_t* terminated,

@@ -183,11 +183,6 @@ class UsvGpuVecEnv:
         except Exception:  # noqa: BLE001
             pass
 
-    def set_overlap(self, chunk_envs: int = 0, sensor_ctas_per_sm: int = 2, dynamics_ctas_per_sm: int = 8):
-        """Overlapped step for large shards (usvgpu_set_overlap, include/usvgpu.h): the sensor kernel of one chunk of envs
-        runs beside the dynamics kernel of the next.  Same results bit for bit; chunk_envs=0 switches it off."""
-        self._check(self._lib.usvgpu_set_overlap(self._h, int(chunk_envs), int(sensor_ctas_per_sm), int(dynamics_ctas_per_sm)))
-
     def close(self):
         if not self._closed and self._h:
             if self._host is not None:

@@ -210,16 +210,6 @@ int usvgpu_stream_sync(usvgpu_handle h, void* stream);
  * shard) and chunks - 1 even ones -- so that the copy-out of one range overlaps the kernels of the next; results do
  * not depend on it. */
 int usvgpu_set_host_chunks(usvgpu_handle h, int32_t chunks);
-/* Overlapped step for LARGE shards of the two-kernel ASMC env ('usv-asmc-simple'; no reference counterpart: the
- * reference steps one env at a time, simple_env_asmc.py:18-27).  usvgpu_step / usvgpu_rollout then run the shard as
- * chunks of `chunk_envs` envs (a multiple of 256; at most 64 chunks): the sensor kernel of chunk c runs on an internal
- * high-priority stream beside the dynamics kernel of chunk c + 1 on the caller's stream, with `sensor_ctas_per_sm`
- * (1..4) sensor CTAs and `dynamics_ctas_per_sm` (1..16) one-warp dynamics CTAs sharing each SM; the caller's stream
- * waits for the internal one before usvgpu_step returns, so stream order as seen by the caller is unchanged and so are
- * the results (same per-env code on the same envs, bit for bit).  It pays when the shard is several times larger than
- * what fills the GPU once (>= 262 144 envs on a B200); chunk_envs = 0 (the default) or
- * >= n_envs switches it off.  usvgpu_step_timed and the host-buffer face always take the plain two-launch step. */
-int usvgpu_set_overlap(usvgpu_handle h, int64_t chunk_envs, int32_t sensor_ctas_per_sm, int32_t dynamics_ctas_per_sm);
 /* Blocks until reward / terminated / truncated of the last usvgpu_step_host are on the host (the observation copy
  * may still be in flight: the caller can do its episode bookkeeping meanwhile, then usvgpu_stream_sync). */
 int usvgpu_flags_sync(usvgpu_handle h);

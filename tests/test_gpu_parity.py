@@ -550,76 +550,6 @@ def test_rollout_entry_matches_step_loop(usv):
     e2.close()
 
 
-@pytest.mark.parametrize("N,chunk,sens,dyn,perturb", [(40000 + 77, 8192, 2, 8, False), (150000, 37888, 3, 4, False),
-                                                    (20000, 4096, 1, 16, True)])
-def test_overlapped_step_is_bit_identical_to_the_plain_step(usv, N, chunk, sens, dyn, perturb):
-    """usvgpu_set_overlap: sensors of chunk c on the library's own stream beside the dynamics of chunk c + 1.  Same per-env
-    code on the same envs: observations, rewards, flags, terminal observations, episode statistics and the whole state
-    must equal the plain two-launch step bit for bit -- with a ragged last chunk, forced resets (limit 25), the K-step
-    rollout entry, and a replayed CUDA graph of the forked / joined streams."""
-    T = 30
-    dev = torch.device("cuda", 0)
-    gen = torch.Generator(device=dev).manual_seed(5)
-    acts = (torch.rand((T, N, 2), generator=gen, device=dev) * torch.tensor([0.8, 2.0], device=dev) +
-            torch.tensor([0.2, -1.0], device=dev)).contiguous()
-    e1 = usv.UsvGpuVecEnv(N, device=0, seed=9, max_episode_steps=25, do_perturb=perturb, obstacles_f32=True)
-    e2 = usv.UsvGpuVecEnv(N, device=0, seed=9, max_episode_steps=25, do_perturb=perturb, obstacles_f32=True)
-    e2.set_overlap(chunk, sens, dyn)
-    assert torch.equal(e1.reset_tensor(), e2.reset_tensor())
-    for t in range(T - 10):
-        a = e1.step_tensor(acts[t])
-        b = e2.step_tensor(acts[t])
-        for x, y in zip(a, b):
-            assert torch.equal(x, y), t
-        assert torch.equal(e1.terminal_obs, e2.terminal_obs), t
-    e1.rollout_tensor(acts[T - 10:T - 5].contiguous(), 5)
-    e2.rollout_tensor(acts[T - 10:T - 5].contiguous(), 5)
-    assert torch.equal(e1.obs, e2.obs) and torch.equal(e1.reward, e2.reward)
-    # the forked / joined pair of streams inside a captured graph (what bench.py replays)
-    s = torch.cuda.Stream(dev)
-    with torch.cuda.stream(s):
-        e2.step_tensor(acts[T - 5])  # eager once on this stream: nothing is created lazily inside the capture
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
-            for t in range(T - 4, T):
-                e2.step_tensor(acts[t])
-        g.replay()
-    torch.cuda.synchronize(dev)
-    for t in range(T - 5, T):
-        e1.step_tensor(acts[t])
-    assert torch.equal(e1.obs, e2.obs) and torch.equal(e1.reward, e2.reward)
-    s1, s2 = e1.get_state(), e2.get_state()
-    for k in s1:
-        assert np.array_equal(s1[k], s2[k]), k
-    st1, st2 = e1.episode_stats(), e2.episode_stats()
-    assert st1["env_steps"] == st2["env_steps"] == N * T and st1["episodes"] == st2["episodes"] > N
-    assert st1["terminated"] == st2["terminated"] and st1["time_limit"] == st2["time_limit"]
-    e2.set_overlap(0)  # off again: the plain step
-    a, b = e1.step_tensor(acts[0]), e2.step_tensor(acts[0])
-    for x, y in zip(a, b):
-        assert torch.equal(x, y)
-    e1.close()
-    e2.close()
-
-
-def test_overlap_arguments_are_checked(usv):
-    env = usv.UsvGpuVecEnv(4096, device=0, seed=1)
-    for bad in ((1000, 2, 8), (-256, 2, 8), (256, 0, 8), (256, 5, 8), (256, 2, 0), (256, 2, 17), (32 * 2, 2, 8)):
-        with pytest.raises(usv.UsvError):
-            env.set_overlap(*bad)
-    env.close()
-    big = usv.UsvGpuVecEnv(256 * 70, device=0, seed=1)
-    with pytest.raises(usv.UsvError, match="64 chunks"):
-        big.set_overlap(256, 2, 8)
-    big.close()
-    for env_id in ("usv-asmc-v0", "usv-simple", "usv-asmc-ca-v0"):
-        env = usv.UsvGpuVecEnv(1024, device=0, seed=1, env_id=env_id)
-        with pytest.raises(usv.UsvError, match="overlap"):
-            env.set_overlap(256, 2, 8)
-        env.set_overlap(0)
-        env.close()
-
-
 def test_errors_are_loud(usv):
     with pytest.raises(usv.UsvError):
         usv.UsvGpuVecEnv(0, device=0)
