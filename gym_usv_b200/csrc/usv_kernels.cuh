@@ -812,6 +812,7 @@ __global__ void math_probe_kernel(int which, long long n, const double* __restri
     if (which == 0) out[i] = sqrt_k(in[i]);
     else if (which == 1) out[i] = div_k(in[i], in[n + i]);
     else if (which == 2) out[i] = asin_k(in[i]);
+    else if (which == 4) out[i] = sqrt_m(in[i]);
     else {
         double cs = in[n + i], sn = in[2 * n + i];
         rot_small(in[i], cs, sn);

@@ -51,6 +51,15 @@ __device__ __forceinline__ double rcp_seed(double a) {
     return r;
 }
 
+// USV_HIWORD: the zero / subnormal guard of the sub-step's square root compares the HIGH WORD of its (never negative)
+// argument as an integer: one ISETP on the idle integer pipe instead of a DSETP on the FP64 pipe, which is what bounds the
+// sub-step (r02u: -0.2 us per step).  The same trick on the range split of asin_k (a >= 0.5) and on the small-angle bound
+// of rot_small made the kernel SLOWER (r02v: +0.35 us per step), and so did the model's exact thresholds as 64-bit integer
+// compares (r02u3: +0.9 us): those stay DSETP.
+#ifndef USV_HIWORD
+#define USV_HIWORD 1
+#endif
+
 // sqrt(a) for 0 <= a << DBL_MAX (sums of squares, |sigma|, discriminants); exactly 0 for a == 0 and for subnormal a
 // (rsqrt.approx.ftz flushes a subnormal argument to zero and returns +inf: without the guard a |sigma| or a
 // discriminant that underflows would turn into NaN and poison the env's state; sqrt of a subnormal is < 1.5e-154).
@@ -79,9 +88,42 @@ __device__ __forceinline__ double sqrt_k20(double a, double& h20) {
     h20 = h;
     return (a >= SQRT_MIN_ARG) ? g : 0.0;
 }
+#ifndef USV_SQRT_CUBIC
+#define USV_SQRT_CUBIC 1
+#endif
+#ifndef USV_ROT_SHORT
+#define USV_ROT_SHORT 1
+#endif
+// sqrt(a) with one third-order step instead of two Newton steps.  With the seed r = (1 + d) / sqrt(a), |d| ~ 2^-20, and
+// t = a r:  e = 1 - t r = 1 - a r^2 (one fma, exact up to its rounding), and sqrt(a) = t / sqrt(1 - e) =
+// t (1 + e/2 + 3 e^2 / 8 + O(e^3)); the truncation 5 e^3 / 16 is ~2^-59.  Five FP64 instructions in a chain of four
+// instead of six in a chain of five; one more live register (the sensor kernel at 64 registers spills with it).
+__device__ __forceinline__ double sqrt_cubic(double a) {
+    const double r = rsqrt_seed(a);
+    const double t = a * r;
+    const double e = fma(-t, r, 1.0);
+    const double g = fma(t * e, fma(0.375, e, 0.5), t);
+#if USV_HIWORD  // a >= DBL_MIN as an integer compare of the high word (a is never negative here)
+    return (__double2hiint(a) >= 0x00100000) ? g : 0.0;
+#else
+    return (a >= SQRT_MIN_ARG) ? g : 0.0;
+#endif
+}
 __device__ __forceinline__ double sqrt_k(double a) {
+#if USV_SQRT_CUBIC >= 2
+    return sqrt_cubic(a);
+#else
     double h;
     return sqrt_k20(a, h);
+#endif
+}
+// the three square roots of a sub-step (usv_model.cuh)
+__device__ __forceinline__ double sqrt_m(double a) {
+#if USV_SQRT_CUBIC >= 1
+    return sqrt_cubic(a);
+#else
+    return sqrt_k(a);
+#endif
 }
 
 // 1/d for a normal, finite d bounded away from 0 (no special cases)
@@ -103,6 +145,9 @@ __device__ __forceinline__ double div_k(double n, double d) {
     return fma(fma(-d, q, n), r, q);
 }
 
+#ifndef USV_ASIN_HORNER
+#define USV_ASIN_HORNER 1
+#endif
 // asin(x), |x| <= 1.  One polynomial serves both ranges: |x| <= 0.5 directly, otherwise through
 // asin(x) = pi/2 - 2 asin(sqrt((1 - |x|)/2)).
 __device__ __forceinline__ double asin_k(double x) {
@@ -119,12 +164,31 @@ __device__ __forceinline__ double asin_k(double x) {
     // degree-12 polynomial by Estrin's scheme: 4 dependent fma levels instead of Horner's 12 (the sub-step's critical
     // path runs through it); z <= 0.25, so the regrouping costs nothing in accuracy (probe: <= 2 ulp as before)
     const double* c = MATHK.asin_c;
+#if USV_ASIN_HORNER == 2  // plain Horner: 12 FP64 instructions in a chain of 12
+    double p = fma(c[12], z, c[11]);
+#pragma unroll
+    for (int k = 10; k >= 0; --k) p = fma(p, z, c[k]);
+#elif USV_ASIN_HORNER == 1  // two interleaved Horner chains in z^2 (even / odd coefficients): 13 FP64 instructions in a chain of 8
+    const double z2 = z * z;
+    double pe = fma(c[12], z2, c[10]), po = fma(c[11], z2, c[9]);
+    pe = fma(pe, z2, c[8]);
+    po = fma(po, z2, c[7]);
+    pe = fma(pe, z2, c[6]);
+    po = fma(po, z2, c[5]);
+    pe = fma(pe, z2, c[4]);
+    po = fma(po, z2, c[3]);
+    pe = fma(pe, z2, c[2]);
+    po = fma(po, z2, c[1]);
+    pe = fma(pe, z2, c[0]);
+    const double p = fma(po, z, pe);
+#else
     const double z2 = z * z, z4 = z2 * z2, z8 = z4 * z4;
     const double a0 = fma(c[1], z, c[0]), a1 = fma(c[3], z, c[2]), a2 = fma(c[5], z, c[4]);
     const double a3 = fma(c[7], z, c[6]), a4 = fma(c[9], z, c[8]), a5 = fma(c[11], z, c[10]);
     const double b0 = fma(a1, z2, a0), b1 = fma(a3, z2, a2), b2 = fma(a5, z2, a4);
     const double d0 = fma(b1, z4, b0), d1 = fma(c[12], z4, b2);
     const double p = fma(d1, z8, d0);
+#endif
     const double t = fma(s * z, p, corr);  // asin(s) - s
     double r = s + t;
     if (big) r = (MATHK.pio2_hi - 2.0 * s) - (fma(2.0, t, -MATHK.pio2_lo));
@@ -168,8 +232,12 @@ __device__ __forceinline__ void rot_small(double d, double& cs, double& sn) {
     double ps = fma(S[2], z, S[1]);
     ps = fma(ps, z, S[0]);
     const double sd = fma(d * z, ps, d);  // sin d
+#if USV_ROT_SHORT  // without the d^8 / 8! term: |d| <= 1/32 makes it < 2.3e-17 of cos d ~ 1, i.e. below half an ulp
+    double pc = fma(C[1], z, C[0]);
+#else
     double pc = fma(C[2], z, C[1]);
     pc = fma(pc, z, C[0]);
+#endif
     pc = fma(pc, z, -0.5);
     const double cm1 = z * pc;  // cos d - 1
     const double c0 = cs, s0 = sn;

@@ -48,6 +48,9 @@ constexpr double TWO_PI_LO = 2.4492935982947064e-16;   // 2*pi - double(2*pi)
 // UMOVs at every use on sm_100a, so those live in __constant__ memory (one LDCU.128 brings two of them into
 // uniform registers) and equal values share one slot to keep the whole set inside the uniform register
 // file; literals that fit the 32-bit immediate form (100, 4, -25, 32.25, 97.5, 0.03125 ...) stay literals.
+#ifndef USV_FP64_DIET
+#define USV_FP64_DIET 1
+#endif
 struct ModelK {
     double half_h;                  // h/2
     double c0001;                   // 0.001: epsilon at :72 and lambda_u
@@ -61,6 +64,7 @@ struct ModelK {
     double mi11, mi12, mi21, mi22;
     double pi, two_pi;
     double inv_beam, inv_2c, inv_bc, c_thr, half_beam;  // INFO path only
+    double yv_yvv;                  // -20000 K_YV + Yvv: the two |v| terms of -D11 (USV_FP64_DIET)
 };
 static_assert(K_U == 0.1 && MU_PSI == 0.1 && K2_PSI == 0.1 && KMIN_U == 0.05 && MU_U == 0.05 && K_PSI == 0.2 &&
               KMIN_PSI == 0.2 && K2_U == 0.02 && LAMBDA_U == 0.001 && LAMBDA_PSI == 1.0, "shared constant slots");
@@ -80,7 +84,8 @@ __constant__ ModelK MK = {
     YVV, -5.49, -8.8, NRR,
     MI11, MI12, MI21, MI22,
     PI, TWO_PI,
-    1.0 / BEAM, 1.0 / (2 * C_THR), 1.0 / (BEAM * C_THR), C_THR, 0.5 * BEAM};
+    1.0 / BEAM, 1.0 / (2 * C_THR), 1.0 / (BEAM * C_THR), C_THR, 0.5 * BEAM,
+    -20000.0 * K_YV + YVV};
 
 // numpy semantics
 __device__ __forceinline__ double np_sign(double x) { return (x > 0.0) ? 1.0 : ((x < 0.0) ? -1.0 : 0.0); }
@@ -128,7 +133,7 @@ __device__ __forceinline__ void asmc_substep(Pose& p, Ctrl& c, const double a0, 
     const double half_h = MK.half_h;
 
     // :72-77  sideslip, course, desired heading (no wrap: :74,:81 are commented out)
-    const double sp = sqrt_k(fma(u, u, v * v));  // hypot(u,v) (:72) and sqrt(u^2+v^2) (:103)
+    const double sp = sqrt_m(fma(u, u, v * v));  // hypot(u,v) (:72) and sqrt(u^2+v^2) (:103)
     const double beta = asin_k(div_k(v, MK.c0001 + sp));
     const double psi_d = (psi + beta) + a1;
 
@@ -148,12 +153,21 @@ __device__ __forceinline__ void asmc_substep(Pose& p, Ctrl& c, const double a0, 
     const bool fast = au > MK.u_switch;
     const double Xu = fast ? MK.xu_fast : -25.0;
     const double Xuu = fast ? MK.xuu_fast : 0.0;
+#if !USV_FP64_DIET
     const double Yv = MK.yv_k * av;
+#endif
     const double Yr = MK.c_yr * sp, Nv = MK.c_nv * sp, Nr = MK.c_nr * sp;
 
     // :111-116  f, g of the simplified model
+#if USV_FP64_DIET
+    // f_u g_u^-1 and f_psi g_psi^-1: the reference divides by (m - X_u_dot) / (Iz - N_r_dot) here (:113-116) and multiplies
+    // by the same numbers at :154-155; the numerators go straight into Tx / Tz below
+    const double fu_n = fma(MK.fu_vr * v, r, fma(Xuu, au, Xu * u));  // Xuu |u| + Xu u, as written at :113
+    const double fp_n = fma(MK.fpsi_uv * u, v, Nr * r);
+#else
     const double f_u = fma(MK.fu_vr * v, r, fma(Xuu, au, Xu * u)) * MK.inv_m00;  // Xuu |u| + Xu u, as written at :113
     const double f_psi = fma(MK.fpsi_uv * u, v, Nr * r) * MK.inv_m22;
+#endif
 
     // :119-130  errors
     const double e_psi = wrap_once(psi_d - psi);
@@ -174,12 +188,18 @@ __device__ __forceinline__ void asmc_substep(Pose& p, Ctrl& c, const double a0, 
     c.kadp_l = kadp;
 
     // :150-151  ua = -Ka sqrt|sigma| sign(sigma) - k2 sigma
-    const double ua_u = -fma(c.ka_u, copysign(sqrt_k(asu), sig_u), MK.c002 * sig_u);
-    const double ua_p = -fma(c.ka_psi, copysign(sqrt_k(asp), sig_p), MK.c01 * sig_p);
-
     // :154-155  control forces; dividing by g = 1/M is multiplying by M
+#if USV_FP64_DIET
+    const double nua_u = fma(c.ka_u, copysign(sqrt_m(asu), sig_u), MK.c002 * sig_u);  // -ua_u
+    const double nua_p = fma(c.ka_psi, copysign(sqrt_m(asp), sig_p), MK.c01 * sig_p);
+    const double tx = fma(32.25, fma(MK.c0001, e_u, nua_u), -fu_n);  // (lambda_u e_u - ua_u) (m - X_u_dot) - f_u (m - X_u_dot)
+    const double tz = fma(MK.m22, e_psi + nua_p, -fp_n);
+#else
+    const double ua_u = -fma(c.ka_u, copysign(sqrt_m(asu), sig_u), MK.c002 * sig_u);
+    const double ua_p = -fma(c.ka_psi, copysign(sqrt_m(asp), sig_p), MK.c01 * sig_p);
     const double tx = (fma(MK.c0001, e_u, -f_u) - ua_u) * 32.25;  // m - X_u_dot
     const double tz = ((e_psi - f_psi) - ua_p) * MK.m22;
+#endif
 
     // :158-176  thruster allocation and back: T[0] = tport + c tstbd = tx, T[2] = B/2 (tport - c tstbd) = tz
     double T0 = tx, T1 = 0.0, T2 = tz;
@@ -206,6 +226,17 @@ __device__ __forceinline__ void asmc_substep(Pose& p, Ctrl& c, const double a0, 
     // -(D nu) = (Xu + Xuu|u|) u etc.: the signs are folded instead of negating every entry
     const double c02 = fma(MK.cor_v, v, MK.cor_r * r);
     const double cu = 97.5 * u;  // m - X_u_dot m
+#if USV_FP64_DIET
+    // the same sums with the common factors of v and r taken out and the |v| terms of -D11 under one coefficient
+    const double t_vr = fma(MK.d549, av, MK.d88 * ar);
+    const double nd11 = fma(MK.yv_yvv, av, MK.d549 * ar);  // -D11
+    const double nd12 = Yr + t_vr;
+    const double nd21 = Nv + t_vr;
+    const double nd22 = Nr + fma(MK.d88, av, MK.nrr * ar);
+    const double rhs0 = fma(fma(Xuu, au, Xu), u, fma(-c02, r, T0));  // -D00 u = (Xu + Xuu |u|) u
+    const double rhs1 = PERTURB ? T1 + fma(nd11, v, (nd12 - cu) * r) : fma(nd11, v, (nd12 - cu) * r);
+    const double rhs2 = fma(nd22, r, fma(cu + nd21, v, fma(c02, u, T2)));
+#else
     const double nd11 = Yv + fma(MK.yvv, av, MK.d549 * ar);  // -D11
     const double nd12 = Yr + fma(MK.d549, av, MK.d88 * ar);
     const double nd21 = Nv + fma(MK.d549, av, MK.d88 * ar);
@@ -213,6 +244,7 @@ __device__ __forceinline__ void asmc_substep(Pose& p, Ctrl& c, const double a0, 
     const double rhs0 = fma(fma(Xuu, au, Xu), u, fma(-c02, r, T0));  // -D00 u = (Xu + Xuu |u|) u
     const double rhs1 = fma(-cu, r, T1) + fma(nd11, v, nd12 * r);
     const double rhs2 = (T2 + fma(c02, u, cu * v)) + fma(nd21, v, nd22 * r);
+#endif
     const double ud = MK.inv_m00 * rhs0;
     const double vd = fma(MK.mi11, rhs1, MK.mi12 * rhs2);
     const double rd = fma(MK.mi21, rhs1, MK.mi22 * rhs2);

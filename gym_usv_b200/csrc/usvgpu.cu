@@ -959,7 +959,7 @@ int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim
 }
 
 int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, double* out, void* stream) {
-    if (!in || !out || n <= 0 || which < 0 || which > 3) return fail(nullptr, USV_ERR_INVALID, "bad math_probe arguments");
+    if (!in || !out || n <= 0 || which < 0 || which > 4) return fail(nullptr, USV_ERR_INVALID, "bad math_probe arguments");
     int rc = check_device(nullptr, device);
     if (rc) return rc;
     DeviceGuard dev_guard(device);

@@ -71,9 +71,9 @@ def sensor_distances_noalloc(pose: torch.Tensor, obstacles: torch.Tensor, n_obs:
 
 
 def math_probe(which: str, x: torch.Tensor) -> torch.Tensor:
-    """Evaluate one float64 device routine of csrc/usv_math.cuh (test surface).  which: 'sqrt' x[n] | 'div' x[2,n] |
+    """Evaluate one float64 device routine of csrc/usv_math.cuh (test surface).  which: 'sqrt' / 'sqrt_m' x[n] | 'div' x[2,n] |
     'asin' x[n] | 'rot' x[3,n] = (delta, cos, sin) -> [2,n]."""
-    code = {"sqrt": 0, "div": 1, "asin": 2, "rot": 3}[which]
+    code = {"sqrt": 0, "div": 1, "asin": 2, "rot": 3, "sqrt_m": 4}[which]
     if not x.is_cuda:
         raise nat.UsvError("math_probe needs CUDA tensors: there is no CPU fallback")
     assert x.dtype == torch.float64 and x.is_contiguous()

@@ -376,7 +376,8 @@ int usvgpu_replay_sample(int device, int64_t n, int32_t obs_dim, int32_t act_dim
 /* Device-math probe (test / measurement surface, no reference counterpart): evaluates one of the float64
  * routines of csrc/usv_math.cuh that replace libm calls of the reference (np.sqrt, '/', np.math.asin at
  * usv_asmc.py:72,103,150; np.cos / np.sin at :179-181) on n inputs.  which: 0 sqrt_k(in[i]) | 1 div_k(in[i],
- * in[n+i]) | 2 asin_k(in[i]) | 3 rot_small(in[i]) applied to (cos, sin) = (in[n+i], in[2n+i]) -> out[i], out[n+i]. */
+ * in[n+i]) | 2 asin_k(in[i]) | 3 rot_small(in[i]) applied to (cos, sin) = (in[n+i], in[2n+i]) -> out[i], out[n+i] |
+ * 4 sqrt_m(in[i]), the square root the ASMC sub-step uses. */
 int usvgpu_math_probe(int device, int32_t which, int64_t n, const double* in, double* out, void* stream);
 
 /* Measured float64 FMA rate of this GPU (the pipe that bounds both step kernels): a grid of

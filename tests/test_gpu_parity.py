@@ -50,9 +50,10 @@ def test_device_math_probe(usv):
     n = 1 << 18
     # sqrt: sums of squares, |sigma|, discriminants -- including exact zero and tiny / huge magnitudes
     x = np.concatenate([[0.0, 1e-300, 1e-30, 4.0, 1e30], rng.uniform(0, 4, n), 10.0 ** rng.uniform(-20, 8, n)])
-    got = usv.math_probe("sqrt", torch.tensor(x, device=dev)).cpu().numpy()
-    assert got[0] == 0.0
-    assert _ulps(got[1:], np.sqrt(x[1:])).max() <= 1.0
+    for which in ("sqrt", "sqrt_m"):  # sqrt_m: the sub-step's square root (usv_model.cuh)
+        got = usv.math_probe(which, torch.tensor(x, device=dev)).cpu().numpy()
+        assert got[0] == 0.0
+        assert _ulps(got[1:], np.sqrt(x[1:])).max() <= 1.0, which
     # division by 0.001 + speed and by the squared path length
     num = rng.uniform(-3, 3, n)
     den = np.concatenate([0.001 + rng.uniform(0, 3, n // 2), rng.uniform(1e4, 1.3e4, n - n // 2)])
