@@ -1,0 +1,20 @@
+#!/bin/bash
+# r02w (8 GPUs): shards on their own devices vs the single-GPU run, bench.py as the driver launches it, the same with
+# 1 048 576 envs per GPU (the north_star's 1e10 is a whole-box figure), and the D2H placement probe for the host face
+mkdir -p gpurun_out
+N=${1:-8}
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+nvidia-smi --query-gpu=index,name --format=csv,noheader | head -8
+$TR --master-port 29517 tests/_multi_gpu_worker.py 8195 40 usv-asmc-simple 2>&1 | grep -E "ranks|MULTI_GPU_OK|MISMATCH" | tee gpurun_out/r02w_multi_gpu_worker_g$N.log
+show() {
+python - "$1" <<'PY'
+import json, sys
+d = json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
+print(d['n_gpus'], d['config']['envs_total'], 'value %.4g' % d['value'], 'e2e %.4g' % d['e2e']['value'], 'ms/step %.4f' % d['ms_per_step'],
+      'blocks', ['%.3f' % x for x in d['timing']['block_ms_max_over_ranks']], 'loop %.4g' % d['timing']['python_loop']['value'],
+      {k: '%.4g' % v['value'] for k, v in d.get('extra', {}).items()})
+PY
+}
+$TR --master-port 29511 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/r02w_bench_g$N.json 2> gpurun_out/r02w_bench_g$N.err; echo "rc $?"; show gpurun_out/r02w_bench_g$N.json
+$TR --master-port 29512 bench.py --gpus $N --steps 12 --warmup 3 --envs-per-gpu 1048576 --preroll 300 --no-extra --no-cpu-baseline --e2e-steps 3 > gpurun_out/r02w_bench_g${N}_1M_per_gpu.json 2> gpurun_out/r02w_bench_g${N}_1M_per_gpu.err; echo "rc $?"; show gpurun_out/r02w_bench_g${N}_1M_per_gpu.json
+$TR --master-port 29513 tools/d2h_numa_probe.py 2>&1 | grep -v -E "^\s*$|Legend|=|SYS |NODE |PHB |PXB |PIX |NV# " | tee gpurun_out/r02w_d2h_probe_g$N.log
