@@ -435,7 +435,7 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
 #if USV_PDL
     if (OBST) {
         if (tid < N_SENS) raytab[tid] = s.raytab[tid];  // written once at usvgpu_create: safe before the wait
-        if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<float>::no_hit();
+        sensor_scratch_init(scratch[warp], lane);
     }
     pdl_wait();
     if (i < n) sensor_prefetch<OBST, ObT>(stage_addr, bar, s, i, lane);
@@ -444,7 +444,7 @@ sensor_kernel(StatePtrs s, StepFlags fl, float* __restrict__ obs, float* __restr
     if (i < n) sensor_prefetch<OBST, ObT>(stage_addr, bar, s, i, lane);
     if (OBST) {
         if (tid < N_SENS) raytab[tid] = s.raytab[tid];
-        if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<float>::no_hit();  // the "no hit" slot
+        sensor_scratch_init(scratch[warp], lane);
         __syncthreads();
     }
 #endif
@@ -728,7 +728,7 @@ sensors_unit_kernel(long long n, const double2* __restrict__ g_raytab, const dou
     __shared__ SensorScratch<double> scratch[SENS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid < N_SENS) raytab[tid] = g_raytab[tid];
-    if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<double>::no_hit();
+    sensor_scratch_init(scratch[warp], lane);
     __syncthreads();
     const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
     if (i >= n) return;
@@ -785,7 +785,7 @@ sensors_rows_kernel(long long n, const double2* __restrict__ g_raytab, const dou
     __shared__ SensorScratch<double> scratch[SENS_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid < N_SENS) raytab[tid] = g_raytab[tid];
-    if (lane == 0) scratch[warp].hpair[PAIR_SLOTS - 1] = Reading<double>::no_hit();
+    sensor_scratch_init(scratch[warp], lane);
     __syncthreads();
     const long long i = (long long)blockIdx.x * SENS_WARPS + warp;
     if (i >= n) return;

@@ -89,7 +89,7 @@ __device__ __forceinline__ double sqrt_k20(double a, double& h20) {
     return (a >= SQRT_MIN_ARG) ? g : 0.0;
 }
 #ifndef USV_SQRT_CUBIC
-#define USV_SQRT_CUBIC 1
+#define USV_SQRT_CUBIC 2
 #endif
 #ifndef USV_ROT_SHORT
 #define USV_ROT_SHORT 1

@@ -38,6 +38,9 @@
 
 namespace usv {
 
+#ifndef USV_SENS_ASINSEL
+#define USV_SENS_ASINSEL 1
+#endif
 constexpr int PAIR_SLOTS = 256;           // slot 255 is reserved: "no hit" -> SENSOR_MAX_RANGE
 constexpr uint32_t NO_HIT = 0xFFFFFFFFu;
 
@@ -80,9 +83,18 @@ __device__ __forceinline__ float atan2_coarse(float y, float x) {
 }
 // asin(q) for 0 <= q <= 1, never more than 7.5e-5 rad below the true value
 __device__ __forceinline__ float asin_coarse(float q) {
+#if USV_SENS_ASINSEL
+    // no branch: asin is convex on [0, 1], so above 0.5 the chord through (0.5, pi / 6) and (1, pi / 2) is an upper bound
+    // (at most 0.09 rad = 3 rays too wide, and only for a circle whose centre is closer than its diameter)
+    const float s = q * q;
+    const float p = q * fmaf(s, fmaf(s, fmaf(s, 15.0f / 336, 3.0f / 40), 1.0f / 6), 1.0f);
+    const float c = fmaf(fminf(q, 1.0f), 2.0943952f, -0.52359877f);  // pi/6 + (q - 1/2) (2 pi / 3)
+    return (q > 0.5f) ? c : p;
+#else
     if (q > 0.5f) return asinf(fminf(q, 1.0f));
     const float s = q * q;
     return q * fmaf(s, fmaf(s, fmaf(s, 15.0f / 336, 3.0f / 40), 1.0f / 6), 1.0f);
+#endif
 }
 
 // the reference's test of a ray (direction t in the body frame) against an obstacle at body-frame offset (bx, by) with
@@ -109,8 +121,14 @@ __device__ __forceinline__ uint32_t opaque_u32(uint32_t v) {  // a value the com
     return v;
 }
 
+// once per warp, before its first env: the "no hit" slot
+template <typename HT>
+__device__ __forceinline__ void sensor_scratch_init(SensorScratch<HT>& sc, const int lane) {
+    if (lane == 0) sc.hpair[PAIR_SLOTS - 1] = Reading<HT>::no_hit();
+}
+
 // ox, oy, rr: this lane's obstacle (ignored when lane >= nob).  cps/sps = cos/sin(psi).  ray_addr: see ray_of.
-// The caller sets sc.hpair[PAIR_SLOTS - 1] = Reading<HT>::no_hit() once (the "no hit" slot).
+// The caller runs sensor_scratch_init(sc, lane) once.
 // out[p]: reading of ray (lane + 32 p) in the form of Reading<HT>.
 // min_key_lt: warp-uniform "min over obstacles of key < key_thr" (simple_env.py:334); min_hit_lt: warp-uniform "min over
 // rays of reading < 0.2" (simple_env.py:153-156).

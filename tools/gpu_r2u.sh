@@ -3,7 +3,7 @@
 # usage: tools/gpu_r2u.sh name [name ...]
 mkdir -p gpurun_out
 run() {
-  timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "math_probe or lockstep or golden or ragged or asmc_compute" 2>&1 | tail -1 | sed "s/^/$1 parity: /"
+  timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "math_probe or lockstep or golden or ragged or asmc_compute or sensors or tie" 2>&1 | tail -1 | sed "s/^/$1 parity: /"
   for rep in 1 2; do
     for n in 65536 1048576; do
       steps=200; [ $n -gt 100000 ] && steps=24
