@@ -32,7 +32,10 @@ constexpr int DYN_UNROLL = USV_DYN_UNROLL;  // sub-steps per trip of the loop in
 #endif
 constexpr int DYN_B = USV_DYN_B; // threads (= envs) per CTA of the dynamics kernel: one warp, so that the 2048 warps of a
                                  // 65 536-env shard spread evenly over the 148 SMs (13.8 per SM)
-constexpr int DYN_MIN_CTAS = 512 / DYN_B; // all of them resident at once (<= 128 registers): no second, nearly empty wave
+#ifndef USV_DYN_MIN_CTAS
+#define USV_DYN_MIN_CTAS (512 / USV_DYN_B)
+#endif
+constexpr int DYN_MIN_CTAS = USV_DYN_MIN_CTAS; // 16 one-warp CTAs per SM: all of a 65 536-env shard resident at once (<= 128 registers)
 #ifndef USV_SENS_WARPS
 #define USV_SENS_WARPS 8
 #endif
