@@ -606,8 +606,8 @@ def run_ours(args, rank, local_rank, world):
                         "per_gpu_needed": 1.25e9, "per_gpu_measured": value / world,
                         "met_throughput_per_gpu": bool(value / world >= 1.25e9),
                         "met_hbm_frac": bool(survey_bytes * n / step_s / 1e9 / peak >= 0.60),
-                        "note": "per-GPU throughput grows with the shard: 1.26e9 at 1 048 576 envs per GPU, 1.005e10 on "
-                                "8 GPUs x 1 048 576 envs (profiles/r02w_bench_g8_1M_per_gpu.json; --envs-per-gpu 1048576)"},
+                        "note": "per-GPU throughput grows with the shard: 1.27e9 at 1 048 576 envs per GPU, 1.012e10 on "
+                                "8 GPUs x 1 048 576 envs (profiles/r02ac_bench_8gpu_1M_per_gpu.json; --envs-per-gpu 1048576)"},
             "clocks": clocks,
             "episode_stats": stats,
             "episode_mix": {k: (stats[k] / max(stats["episodes"], 1)) for k in ("terminated", "out_of_bounds", "time_limit")},
