@@ -9,9 +9,13 @@
 //     sums of squares and bounded denominators),
 //   * the heading's cos/sin are carried through the 20 sub-steps by a small-angle rotation instead of
 //     20 full-range sincos() calls.
-// Accuracy (tests/test_gpu_parity.py::test_device_math_probe): sqrt_k, div_k <= 1 ulp, asin_k <= 2 ulp,
+// Accuracy (tests/test_gpu_parity.py::test_device_math_probe): sqrt_k, sqrt_m, div_k <= 1 ulp, asin_k <= 2 ulp,
 // rot_small <= 1 ulp per application (|d| <= 1/32) -- the same order as the libm-vs-CUDA differences the parity
 // tolerance already covers.
+// The dynamics kernel is bound by the FP64 pipe, i.e. by the NUMBER of FP64 instructions (profiles/r02_experiments.txt 11-12):
+// the build-time knobs below (USV_SQRT_CUBIC, USV_ROT_SHORT, USV_ASIN_HORNER, USV_HIWORD) each trade instructions for nothing
+// but the place of a rounding; their defaults are the measured optimum, the other values are kept for A/B builds
+// (tools/build_variants.sh).
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
